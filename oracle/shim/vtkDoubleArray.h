@@ -1,0 +1,2 @@
+/* forwards to the single stub; see vtk_stub.h */
+#include "vtk_stub.h"

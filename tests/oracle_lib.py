@@ -1,0 +1,362 @@
+"""ctypes bindings for the CPU checkers (test infrastructure only).
+
+* ``oracle/liblbm_oracle.so`` -- this repo's C restatement (oracle/lbm_oracle.c).
+* ``oracle/_ref/libref_*.so`` -- the unmodified reference compiled in place by
+  ``make -C oracle ref`` (only where /root/reference exists; the prebuilt files
+  travel to the GPU box).
+
+Nothing in the product package imports this module.
+"""
+import ctypes as C
+import os
+import tempfile
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_SO = os.path.join(ROOT, "oracle", "liblbm_oracle.so")
+REF_DIR = os.path.join(ROOT, "oracle", "_ref")
+
+dp = C.POINTER(C.c_double)
+
+
+def _p(a):
+    assert a.dtype == np.float64 and a.flags["C_CONTIGUOUS"]
+    return a.ctypes.data_as(dp)
+
+
+def ref_available(name):
+    return os.path.exists(os.path.join(REF_DIR, "libref_%s.so" % name))
+
+
+_oracle = None
+
+
+def oracle():
+    global _oracle
+    if _oracle is None:
+        if not os.path.exists(ORACLE_SO):
+            raise RuntimeError("oracle library missing: run `make -C oracle oracle` (or __graft_entry__.build())")
+        L = C.CDLL(ORACLE_SO)
+        L.lbo3_create.restype = C.c_void_p
+        L.lbo3_create.argtypes = [C.c_int, C.c_int, C.c_int, dp]
+        L.lbo3_halo.restype = dp
+        L.lbo3_halo.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_size_t)]
+        for fn in ("lbo3_destroy", "lbo3_init_fields", "lbo3_init_pops", "lbo3_after_init", "lbo3_finish",
+                   "lbo3_self_exchange_phi", "lbo3_self_exchange_step", "lbo3_init_single"):
+            getattr(L, fn).argtypes = [C.c_void_p]
+            getattr(L, fn).restype = None
+        L.lbo3_collide.argtypes = [C.c_void_p, C.c_int]
+        L.lbo3_step_single.argtypes = [C.c_void_p, C.c_int]
+        L.lbo3_set_fields.argtypes = [C.c_void_p] + [dp] * 5
+        L.lbo3_get_fields.argtypes = [C.c_void_p] + [dp] * 5
+        L.lbo3_get_pops.argtypes = [C.c_void_p, dp, dp]
+        L.lbo3_set_pops.argtypes = [C.c_void_p, dp, dp]
+        L.lbo2b_create.restype = C.c_void_p
+        L.lbo2b_create.argtypes = [C.c_int, C.c_int, dp]
+        for fn in ("lbo2b_destroy", "lbo2b_init_reference_ic", "lbo2b_init"):
+            getattr(L, fn).argtypes = [C.c_void_p]
+        L.lbo2b_set_phase.argtypes = [C.c_void_p, dp]
+        L.lbo2b_step.argtypes = [C.c_void_p, C.c_int]
+        L.lbo2b_get_fields.argtypes = [C.c_void_p] + [dp] * 4
+        L.lbo2b_get_pops.argtypes = [C.c_void_p, dp, dp]
+        L.lbo2b_set_pops.argtypes = [C.c_void_p, dp, dp]
+        L.lbosc_create.restype = C.c_void_p
+        L.lbosc_create.argtypes = [C.c_int, C.c_int, C.c_double, C.c_double, C.c_int]
+        L.lbosc_destroy.argtypes = [C.c_void_p]
+        L.lbosc_init_droplet.argtypes = [C.c_void_p, C.c_double, C.c_double, C.c_int]
+        L.lbosc_set_pops.argtypes = [C.c_void_p, dp]
+        L.lbosc_step.argtypes = [C.c_void_p, C.c_int]
+        L.lbosc_get_fields.argtypes = [C.c_void_p, dp, dp, dp]
+        L.lbosc_get_pops.argtypes = [C.c_void_p, dp]
+        L.lbomrt_create.restype = C.c_void_p
+        L.lbomrt_create.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, C.c_double]
+        L.lbomrt_destroy.argtypes = [C.c_void_p]
+        L.lbomrt_init_wave.argtypes = [C.c_void_p, C.c_double]
+        L.lbomrt_set_pops.argtypes = [C.c_void_p, dp]
+        L.lbomrt_step.argtypes = [C.c_void_p, C.c_int]
+        L.lbomrt_get_fields.argtypes = [C.c_void_p, dp, dp, dp]
+        L.lbomrt_get_pops.argtypes = [C.c_void_p, dp]
+        _oracle = L
+    return _oracle
+
+
+# QuarterChannel/main.cpp:48-62 and FullChannel/main.cpp:49-70, in the LBO3_* order
+PARAMS_QUARTER = [0.04, 0.04, 1.0, 0.0, 0.0, 0.5, 2.0, 2.5, 0.7, 0.0, 0.0, 0.00003]
+PARAMS_FULL = [0.04, 0.04, 1.0, 0.0, 0.0, 0.5, 1.0, 2.5, 0.7, 0.0, 0.0, 0.00003]
+HALO = dict(S_F_UP=0, S_G_UP=1, S_F_DOWN=2, S_G_DOWN=3,
+            R_F_FROM_BELOW=4, R_G_FROM_BELOW=5, R_F_FROM_ABOVE=6, R_G_FROM_ABOVE=7,
+            S_PHI_UP=8, S_PHI_DOWN=9, R_PHI_FROM_BELOW=10, R_PHI_FROM_ABOVE=11)
+
+
+def bubble_fields(nx, ny, nz, width):
+    """Initial condition of Microchannel3D main.cpp:83-100 (rho, phase, ux, uy, uz), node order [z][y][x]."""
+    z, y, x = np.meshgrid(np.arange(nz), np.arange(ny), np.arange(nx), indexing="ij")
+    gas = (z >= (nz - 1) // 3) & (z <= 2 * (nz - 1) // 3) & (x <= nx - width - 1) & (y <= ny - width - 1)
+    phase = np.where(gas, -1.0, 1.0).astype(np.float64).ravel()
+    n = nx * ny * nz
+    return np.ones(n), phase, np.zeros(n), np.zeros(n), np.zeros(n)
+
+
+class Oracle3D:
+    """One z-slab of the D3Q19 binary-liquid oracle."""
+
+    def __init__(self, nx, ny, nz, params):
+        self.L = oracle()
+        self.nx, self.ny, self.nz = nx, ny, nz
+        self.n = nx * ny * nz
+        p = np.asarray(params, dtype=np.float64)
+        self.h = self.L.lbo3_create(nx, ny, nz, _p(p))
+        assert self.h
+
+    def close(self):
+        if self.h:
+            self.L.lbo3_destroy(self.h)
+            self.h = None
+
+    def set_fields(self, rho, phase, ux, uy, uz):
+        arrs = [np.ascontiguousarray(a, dtype=np.float64) for a in (rho, phase, ux, uy, uz)]
+        self.L.lbo3_set_fields(self.h, *[_p(a) for a in arrs])
+
+    def init_single(self):
+        self.L.lbo3_init_single(self.h)
+
+    def step_single(self, n):
+        self.L.lbo3_step_single(self.h, n)
+
+    def fields(self):
+        out = [np.empty(self.n) for _ in range(5)]
+        self.L.lbo3_get_fields(self.h, *[_p(a) for a in out])
+        return dict(zip(("rho", "phase", "ux", "uy", "uz"), out))
+
+    def pops(self):
+        f, g = np.empty(self.n * 19), np.empty(self.n * 19)
+        self.L.lbo3_get_pops(self.h, _p(f), _p(g))
+        return f.reshape(-1, 19), g.reshape(-1, 19)
+
+    def set_pops(self, f, g):
+        f = np.ascontiguousarray(f, dtype=np.float64).ravel()
+        g = np.ascontiguousarray(g, dtype=np.float64).ravel()
+        self.L.lbo3_set_pops(self.h, _p(f), _p(g))
+
+    def halo(self, name):
+        cnt = C.c_size_t()
+        ptr = self.L.lbo3_halo(self.h, HALO[name], C.byref(cnt))
+        return np.ctypeslib.as_array(ptr, shape=(cnt.value,))
+
+
+class Ref3D:
+    """The unmodified reference Lattice/Solver (oracle/_ref/libref_{quarter,full}.so), one rank."""
+
+    def __init__(self, nx, ny, nz, params, which="quarter"):
+        L = C.CDLL(os.path.join(REF_DIR, "libref_%s.so" % which))
+        L.ref3d_create.restype = C.c_void_p
+        L.ref3d_create.argtypes = [C.c_int, C.c_int, C.c_int, dp]
+        L.ref3d_set_fields.argtypes = [C.c_void_p] + [dp] * 5
+        L.ref3d_get_fields.argtypes = [C.c_void_p] + [dp] * 5
+        L.ref3d_set_bubble.argtypes = [C.c_void_p, C.c_int]
+        L.ref3d_init.argtypes = [C.c_void_p]
+        L.ref3d_step.argtypes = [C.c_void_p, C.c_int]
+        L.ref3d_get_pops.argtypes = [C.c_void_p, dp, dp]
+        L.ref3d_set_pops.argtypes = [C.c_void_p, dp, dp]
+        L.ref3d_destroy.argtypes = [C.c_void_p]
+        self.L = L
+        self.nx, self.ny, self.nz = nx, ny, nz
+        self.n = nx * ny * nz
+        p = np.asarray(params, dtype=np.float64)
+        self.h = L.ref3d_create(nx, ny, nz, _p(p))
+
+    def close(self):
+        if self.h:
+            self.L.ref3d_destroy(self.h)
+            self.h = None
+
+    def set_fields(self, rho, phase, ux, uy, uz):
+        arrs = [np.ascontiguousarray(a, dtype=np.float64) for a in (rho, phase, ux, uy, uz)]
+        self.L.ref3d_set_fields(self.h, *[_p(a) for a in arrs])
+
+    def set_bubble(self, width):
+        self.L.ref3d_set_bubble(self.h, width)
+
+    def init(self):
+        self.L.ref3d_init(self.h)
+
+    def step(self, n):
+        self.L.ref3d_step(self.h, n)
+
+    def fields(self):
+        out = [np.empty(self.n) for _ in range(5)]
+        self.L.ref3d_get_fields(self.h, *[_p(a) for a in out])
+        return dict(zip(("rho", "phase", "ux", "uy", "uz"), out))
+
+    def pops(self):
+        f, g = np.empty(self.n * 19), np.empty(self.n * 19)
+        self.L.ref3d_get_pops(self.h, _p(f), _p(g))
+        return f.reshape(-1, 19), g.reshape(-1, 19)
+
+
+def bulk_mask_3d(nx, ny, nz):
+    z, y, x = np.meshgrid(np.arange(nz), np.arange(ny), np.arange(nx), indexing="ij")
+    return ((x >= 1) & (x <= nx - 2) & (y >= 1) & (y <= ny - 2)).ravel()
+
+
+def nonwall_mask_3d(nx, ny, nz):
+    z, y, x = np.meshgrid(np.arange(nz), np.arange(ny), np.arange(nx), indexing="ij")
+    return ((x <= nx - 2) & (y <= ny - 2)).ravel()
+
+
+# ---------------- 2-D programs ----------------
+# FreeEnergy/binary.cpp:29-41: aconst,kconst,gammaconst,wall_gradient,tau_gas,tau_liq,omega_phi
+PARAMS_BINARY2D = [0.04, 0.04, 1.0, -0.15, 1.0, 1.0, 1.0]
+
+
+class OracleBinary2D:
+    def __init__(self, nx, ny, params=PARAMS_BINARY2D):
+        self.L = oracle()
+        self.nx, self.ny, self.n = nx, ny, nx * ny
+        p = np.asarray(params, dtype=np.float64)
+        self.h = self.L.lbo2b_create(nx, ny, _p(p))
+
+    def close(self):
+        if self.h:
+            self.L.lbo2b_destroy(self.h)
+            self.h = None
+
+    def init_reference(self):
+        self.L.lbo2b_init_reference_ic(self.h)
+        self.L.lbo2b_init(self.h)
+
+    def init_phase(self, phase):
+        a = np.ascontiguousarray(phase, dtype=np.float64).ravel()
+        self.L.lbo2b_set_phase(self.h, _p(a))
+        self.L.lbo2b_init(self.h)
+
+    def step(self, n):
+        self.L.lbo2b_step(self.h, n)
+
+    def fields(self):
+        out = [np.empty(self.n) for _ in range(4)]
+        self.L.lbo2b_get_fields(self.h, *[_p(a) for a in out])
+        return dict(zip(("phase", "rho", "ux", "uy"), out))
+
+    def pops(self):
+        f, g = np.empty(self.n * 9), np.empty(self.n * 9)
+        self.L.lbo2b_get_pops(self.h, _p(f), _p(g))
+        return f.reshape(-1, 9), g.reshape(-1, 9)
+
+    def set_pops(self, f, g):
+        f = np.ascontiguousarray(f, dtype=np.float64).ravel()
+        g = np.ascontiguousarray(g, dtype=np.float64).ravel()
+        self.L.lbo2b_set_pops(self.h, _p(f), _p(g))
+
+
+class OracleShanChen:
+    def __init__(self, nx, ny, tau=1.0, g=-5.0, use_libm_exp=False):
+        self.L = oracle()
+        self.nx, self.ny, self.n = nx, ny, nx * ny
+        self.h = self.L.lbosc_create(nx, ny, tau, g, int(use_libm_exp))
+
+    def close(self):
+        if self.h:
+            self.L.lbosc_destroy(self.h)
+            self.h = None
+
+    def init_droplet(self, rhol=1.95, rhog=0.15, radius=20):
+        self.L.lbosc_init_droplet(self.h, rhol, rhog, radius)
+
+    def set_pops(self, f):
+        f = np.ascontiguousarray(f, dtype=np.float64).ravel()
+        self.L.lbosc_set_pops(self.h, _p(f))
+
+    def step(self, n):
+        self.L.lbosc_step(self.h, n)
+
+    def fields(self):
+        out = [np.empty(self.n) for _ in range(3)]
+        self.L.lbosc_get_fields(self.h, *[_p(a) for a in out])
+        return dict(zip(("rho", "u1", "u2"), out))
+
+    def pops(self):
+        f = np.empty(self.n * 9)
+        self.L.lbosc_get_pops(self.h, _p(f))
+        return f.reshape(-1, 9)
+
+
+class OracleMRT:
+    def __init__(self, variant, nx, ny, omega, omega_bulk, force_ampl=0.002):
+        self.L = oracle()
+        self.nx, self.ny, self.n = nx, ny, nx * ny
+        self.h = self.L.lbomrt_create(variant, nx, ny, omega, omega_bulk, force_ampl)
+
+    def close(self):
+        if self.h:
+            self.L.lbomrt_destroy(self.h)
+            self.h = None
+
+    def init_wave(self, ampl=0.001):
+        self.L.lbomrt_init_wave(self.h, ampl)
+
+    def set_pops(self, f):
+        f = np.ascontiguousarray(f, dtype=np.float64).ravel()
+        self.L.lbomrt_set_pops(self.h, _p(f))
+
+    def step(self, n):
+        self.L.lbomrt_step(self.h, n)
+
+    def fields(self):
+        out = [np.empty(self.n) for _ in range(3)]
+        self.L.lbomrt_get_fields(self.h, *[_p(a) for a in out])
+        return dict(zip(("rho", "ux", "uy"), out))
+
+    def pops(self):
+        f = np.empty(self.n * 9)
+        self.L.lbomrt_get_pops(self.h, _p(f))
+        return f.reshape(-1, 9)
+
+
+def _scratch():
+    return tempfile.mkdtemp(prefix="lbmref_")
+
+
+def ref_shanchen_run(last_step, shared_exp=True, outdir=None):
+    """Run the unmodified shanchen.cpp through step `last_step`; returns rho,u1,u2,f(next)."""
+    L = C.CDLL(os.path.join(REF_DIR, "libref_shanchen%s.so" % ("_sharedexp" if shared_exp else "")))
+    L.ref_shanchen_run.argtypes = [C.c_int, C.c_char_p, dp, dp, dp, dp]
+    nx, ny = L.ref_shanchen_nx(), L.ref_shanchen_ny()
+    n = nx * ny
+    rho, u1, u2, f = np.empty(n), np.empty(n), np.empty(n), np.empty(n * 9)
+    rc = L.ref_shanchen_run(last_step, (outdir or _scratch()).encode(), _p(rho), _p(u1), _p(u2), _p(f))
+    assert rc in (0, 1), rc
+    return dict(nx=nx, ny=ny, rho=rho, u1=u1, u2=u2, f=f.reshape(-1, 9))
+
+
+def ref_binary_run(last_step, noutput=0, outdir=None):
+    L = C.CDLL(os.path.join(REF_DIR, "libref_binary.so"))
+    L.ref_binary_run.argtypes = [C.c_int, C.c_int, C.c_char_p] + [dp] * 6
+    nx, ny = L.ref_binary_nx(), L.ref_binary_ny()
+    n = nx * ny
+    ph, rho, ux, uy = (np.empty(n) for _ in range(4))
+    f, g = np.empty(n * 9), np.empty(n * 9)
+    rc = L.ref_binary_run(last_step, noutput, (outdir or _scratch()).encode(), _p(ph), _p(rho), _p(ux), _p(uy), _p(f), _p(g))
+    assert rc == 0, rc
+    return dict(nx=nx, ny=ny, phase=ph, rho=rho, ux=ux, uy=uy, f=f.reshape(-1, 9), g=g.reshape(-1, 9))
+
+
+def ref_mrt_run(variant, arg1=10, arg2=10, outdir=None):
+    name = "mrt" if variant == 0 else "another_mrt"
+    L = C.CDLL(os.path.join(REF_DIR, "libref_%s.so" % name))
+    run = getattr(L, "ref_%s_run" % name)
+    run.argtypes = [C.c_int, C.c_int, C.c_char_p, dp, dp, dp, dp]
+    nx, ny = getattr(L, "ref_%s_nx" % name)(), getattr(L, "ref_%s_ny" % name)()
+    nsteps = getattr(L, "ref_%s_nsteps" % name)()
+    n = nx * ny
+    rho, ux, uy, f = np.empty(n), np.empty(n), np.empty(n), np.empty(n * 9)
+    rc = run(arg1, arg2, (outdir or _scratch()).encode(), _p(rho), _p(ux), _p(uy), _p(f))
+    assert rc == 0, rc
+    return dict(nx=nx, ny=ny, nsteps=nsteps, rho=rho, ux=ux, uy=uy, f=f.reshape(-1, 9))
+
+
+def ndiff(a, b):
+    """number of entries whose values differ (NaN == NaN; -0.0 == 0.0)"""
+    a, b = np.asarray(a), np.asarray(b)
+    return int(np.count_nonzero(~((a == b) | (np.isnan(a) & np.isnan(b)))))
