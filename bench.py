@@ -1,0 +1,350 @@
+#!/usr/bin/env python
+"""bench.py -- MLUPS of the D3Q19 binary-liquid collide-stream on B200, with roofline, CPU baseline,
+end-to-end figure and clocks, one JSON line per run (see DESIGN.md "Measurement").
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload quarter|full] [--impl ours|reference]
+
+Workload (default `quarter`): the QuarterChannel program (Microchannel3D/QuarterChannel/main.cpp: parameters
+:48-62, bubble initial condition :83-100) scaled to 512 x 512 x (512 per GPU) nodes, z-slab per GPU --
+BASELINE.json configs[4], the weak-scaling case; `full` is FullChannel at its own 92x52x1500 (configs[3]).
+A "step" is one lattice update of the whole grid.  Under torchrun every rank owns one z-slab.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+B_ALG = 608.0  # algorithmic bytes per lattice update: 2 sets x 19 populations x 8 B, read once + written once
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="quarter", choices=["quarter", "full"])
+    ap.add_argument("--nx", type=int, default=512)
+    ap.add_argument("--ny", type=int, default=512)
+    ap.add_argument("--nz-per-gpu", type=int, default=512)
+    ap.add_argument("--variant", type=int, default=0, help="kernel_variant (0 default, 1 plain two-kernel path)")
+    ap.add_argument("--e2e-steps", type=int, default=100, help="lattice steps per end-to-end segment (QuarterChannel NUMOUTPUT)")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=15.0)
+    return ap.parse_args()
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ------------------------------------------------------------------ reference on the host cores
+def ref_binary():
+    p = os.path.join(ROOT, "oracle", "_ref", "ref_quarter")
+    return p if os.path.exists(p) else None
+
+
+def run_reference_cpu(nx, ny, nz, warm, steps, ranks, width=6):
+    """The unmodified reference Lattice/Solver (oracle/_ref/ref_quarter) on `ranks` forked mini-MPI ranks."""
+    env = dict(os.environ, LBM_MINIMPI_RANKS=str(ranks))
+    out = subprocess.run([ref_binary(), str(nx), str(ny), str(nz), str(warm), str(steps), str(width)], env=env,
+                         capture_output=True, text=True, timeout=1200)
+    if out.returncode != 0:
+        raise RuntimeError("reference run failed: " + out.stderr[-400:])
+    return json.loads(out.stdout.strip().splitlines()[-1])
+
+
+def host_ranks():
+    n = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    return max(1, min(n, 32))   # the reference's own job script asks for 32 ranks (FullChannel/binary.pbs:6)
+
+
+def cpu_sample_grid(ranks):
+    # a bounded sample of the workload: same program, same parameters, 128x128 cross-section, >= 8 planes per rank
+    return 128, 128, max(64, 8 * ranks)
+
+
+def cpu_baseline(seconds):
+    """Reference (or, without oracle/_ref, the C port) timed on the host for about `seconds`."""
+    if ref_binary():
+        ranks = host_ranks()
+        nx, ny, nz = cpu_sample_grid(ranks)
+        probe = run_reference_cpu(nx, ny, nz, 0, 2, ranks)
+        steps = max(3, int(seconds / max(probe["seconds"] / 2, 1e-3)))
+        r = run_reference_cpu(nx, ny, nz, 1, steps, ranks)
+        return {"value": r["mlups"], "unit": "MLUPS", "cores": ranks, "kind": "reference",
+                "sample": "unmodified Microchannel3D/QuarterChannel Lattice/Solver on %d mini-MPI z-slab ranks, %dx%dx%d, %d steps, %.1f s"
+                          % (ranks, nx, ny, nz, steps, r["seconds"])}
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib as ol
+    nx, ny, nz = 64, 64, 64
+    o = ol.Oracle3D(nx, ny, nz, ol.PARAMS_QUARTER)
+    o.set_fields(*ol.bubble_fields(nx, ny, nz, 6))
+    o.init_single()
+    o.step_single(1)
+    t0 = time.time()
+    steps = 0
+    while time.time() - t0 < seconds:
+        o.step_single(2)
+        steps += 2
+    dt = time.time() - t0
+    return {"value": nx * ny * nz * steps / dt / 1e6, "unit": "MLUPS", "cores": 1, "kind": "port",
+            "sample": "oracle/lbm_oracle.c, %dx%dx%d, %d steps, %.1f s" % (nx, ny, nz, steps, dt)}
+
+
+def reference_arm(args, rank):
+    if rank != 0:
+        return
+    ranks = host_ranks()
+    nx, ny, nz = cpu_sample_grid(ranks)
+    cfg = {"workload": "QuarterChannel D3Q19 binary liquid, bounded sample %dx%dx%d of the %dx%dx%d-per-GPU job" % (nx, ny, nz, args.nx, args.ny, args.nz_per_gpu),
+           "precision": "fp64", "host_ranks": ranks}
+    if ref_binary():
+        r = run_reference_cpu(nx, ny, nz, args.warmup, args.steps, ranks)
+        kind, val, sec = "reference", r["mlups"], r["seconds"]
+    else:
+        cb = cpu_baseline(max(5.0, args.steps * 0.2))
+        kind, val, sec, ranks = cb["kind"], cb["value"], None, cb["cores"]
+    line = {"impl": "reference", "metric": "MLUPS (aggregate), D3Q19 binary-liquid collide-stream, fp64", "value": val, "unit": "MLUPS",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": (sec * 1e3 / args.steps) if sec else None, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": cfg,
+            "cpu_baseline": {"value": val, "unit": "MLUPS", "cores": ranks, "kind": kind,
+                             "sample": "%dx%dx%d, %d steps" % (nx, ny, nz, args.steps)},
+            "e2e": {"value": val, "unit": "MLUPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------ clocks
+class ClockSampler:
+    def __init__(self, device_index):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._thr = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(device_index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _loop(self):
+        nv = self.nv
+        names = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20,
+                 "hw_power_brake": 0x80, "sync_boost": 0x10, "applications_clocks": 0x2}
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for k, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(k)
+            except Exception:
+                pass
+            self._stop.wait(0.02)
+
+    def start(self):
+        if self.nv:
+            self._thr = threading.Thread(target=self._loop, daemon=True)
+            self._thr.start()
+
+    def stop(self):
+        if self._thr:
+            self._stop.set()
+            self._thr.join()
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+# ------------------------------------------------------------------ our arm
+def slab_initial_fields(api, nx, ny, nz_global, z_begin, nz_local, width, np):
+    """main.cpp:83-100 for one slab, built plane-wise to stay light on host memory."""
+    x = np.arange(nx)[None, :] <= nx - width - 1
+    y = np.arange(ny)[:, None] <= ny - width - 1
+    inxy = (x & y)
+    phase = np.ones((nz_local, ny, nx))
+    zlo, zhi = (nz_global - 1) // 3, 2 * (nz_global - 1) // 3
+    for zl in range(nz_local):
+        z = z_begin + zl
+        if zlo <= z <= zhi:
+            phase[zl][inxy] = -1.0
+    return phase.reshape(-1)
+
+
+def ours(args, rank, world, local_rank):
+    import numpy as np
+    import torch
+    from latticeboltzmannmethod_b200 import api
+
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    if args.workload == "full":
+        nx, ny, nz, width, which = 92, 52, 1500, 8, "full"
+        wl = "Microchannel3D/FullChannel 92x52x1500 (BASELINE.json configs[3]), z-slabs over %d GPU(s)" % world
+        scaling = "strong"
+    else:
+        nx, ny, nz, which = args.nx, args.ny, args.nz_per_gpu * world, "quarter"
+        width = max(1, round(nx * 6 / 27))
+        wl = "Microchannel3D/QuarterChannel scaled to %dx%dx%d (%d planes per GPU; BASELINE.json configs[4])" % (nx, ny, nz, args.nz_per_gpu)
+        scaling = "weak"
+    cfg = api.microchannel_config(which, nx, ny, nz, device=local_rank, slab_rank=rank, slab_count=world)
+    cfg.kernel_variant = args.variant
+    ctx = api.Context(cfg)
+    z_begin, nz_local = ctx.slab_extent()
+    nloc = ctx.local_nodes
+    if world > 1:
+        uid = [api.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        ctx.comm_attach(uid[0])
+
+    # pinned host buffers: initial fields in, result fields out (the e2e leg copies through them every segment)
+    L = api.load_library()
+    import ctypes as C
+    host = {}
+    for name in ("rho", "phase", "ux", "uy", "uz"):
+        ptr = L.lbm_host_alloc(nloc * 8)
+        if not ptr:
+            raise RuntimeError("pinned host allocation failed")
+        host[name] = (ptr, np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_double)), shape=(nloc,)))
+    host["rho"][1][:] = 1.0
+    host["phase"][1][:] = slab_initial_fields(api, nx, ny, nz, z_begin, nz_local, width, np)
+    for k in ("ux", "uy", "uz"):
+        host[k][1][:] = 0.0
+
+    def upload_and_init():
+        for name in ("rho", "phase", "ux", "uy", "uz"):
+            ctx.set_field(name, host[name][0])
+        ctx.init()
+
+    def barrier():
+        ctx.sync()
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    upload_and_init()
+    stream = torch.cuda.ExternalStream(ctx.stream)
+    ctx.step(args.warmup)
+    barrier()
+
+    # ---- device-resident timing: K steps, CUDA events on the stream the kernels run on ----
+    clocks = ClockSampler(local_rank)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    launches0 = ctx.launch_count
+    ctx.profile(True)
+    clocks.start()
+    ev0.record(stream)
+    ctx.step(args.steps)
+    ev1.record(stream)
+    barrier()
+    clk = clocks.stop()
+    ms = ev0.elapsed_time(ev1)
+    prof = ctx.profile_report()
+    ctx.profile(False)
+    launches = ctx.launch_count - launches0
+    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max = float(t.item())
+    total_nodes = nx * ny * nz
+    value = total_nodes * args.steps / (ms_max * 1e-3) / 1e6
+
+    # dominant kernel: the one with the largest share of the profiled time
+    roof = None
+    if prof:
+        name = max(prof, key=lambda k: prof[k]["ms"])
+        per_launch_ms = prof[name]["ms"] / prof[name]["launches"]
+        peak, which_peak = peaks()
+        achieved = B_ALG * nloc / (per_launch_ms * 1e-3) / 1e9
+        traffic = None
+        tp = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tp):
+            traffic = json.load(open(tp)).get(name, {}).get("dram_bytes_per_lattice_update")
+            if traffic is not None:
+                traffic = traffic * nloc
+        roof = {"bound": "hbm", "kernel": name, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": traffic, "peak_source": which_peak, "algorithmic_bytes_per_launch": B_ALG * nloc,
+                "avg_launch_ms": per_launch_ms, "share_of_step": prof[name]["ms"] / sum(v["ms"] for v in prof.values()),
+                "kernels": prof}
+
+    # ---- end to end through the C ABI with host buffers: H2D initial fields, init, S steps, D2H result fields ----
+    e2e = None
+    if not args.no_e2e:
+        S = args.e2e_steps
+        barrier()
+        t0 = time.perf_counter()
+        upload_and_init()
+        ctx.step(S)
+        for name in ("rho", "phase", "ux", "uy", "uz"):
+            ctx.get_field(name, host[name][1])
+        barrier()
+        dt = time.perf_counter() - t0
+        tt = torch.tensor([dt], dtype=torch.float64, device="cuda")
+        if dist is not None:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        dt = float(tt.item())
+        e2e = {"value": total_nodes * S / dt / 1e6, "unit": "MLUPS", "h2d_bytes_per_step": 5 * 8 * nloc / S,
+               "d2h_bytes_per_step": 5 * 8 * nloc / S, "segment": "lbm_set_field x5 (pinned host) + lbm_init + lbm_step(%d) + lbm_get_field x5" % S,
+               "seconds": dt}
+
+    cb = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        try:
+            cb = cpu_baseline(args.cpu_seconds)
+        except Exception as e:  # the baseline is reported, never the thing measured
+            cb = {"value": None, "unit": "MLUPS", "cores": 0, "kind": "unavailable", "sample": str(e)[:200]}
+
+    if rank == 0:
+        line = {"metric": "MLUPS (aggregate), D3Q19 binary-liquid collide-stream, fp64", "value": value, "unit": "MLUPS",
+                "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_max / args.steps,
+                "higher_is_better": True, "scaling": scaling, "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": {"workload": wl, "nx": nx, "ny": ny, "nz": nz, "nodes": total_nodes, "precision": "fp64",
+                           "kernel_variant": args.variant, "l2": "inputs (%.1f GB of populations per GPU) exceed the 126 MB L2" % (nloc * 304 / 1e9),
+                           "parallelism": "z-slab x%d" % world},
+                "mlups_per_gpu": value / world, "roofline": roof, "cpu_baseline": cb, "e2e": e2e, "clocks": clk,
+                "gpu_launches": launches}
+        print(json.dumps(line), flush=True)
+    ctx.close()
+    for ptr, _ in host.values():
+        L.lbm_host_free(ptr)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        reference_arm(args, rank)
+        return
+    if world != args.gpus and world == 1 and args.gpus > 1:
+        sys.stderr.write("bench.py: --gpus %d needs torchrun (one rank per GPU); running on 1 GPU\n" % args.gpus)
+    ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

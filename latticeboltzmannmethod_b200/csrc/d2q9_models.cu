@@ -1,0 +1,320 @@
+// d2q9_models.cu -- the three D2Q9 programs on one GPU: Shan-Chen
+// (ShanChen/shanchen.cpp), binary liquid (FreeEnergy/binary.cpp) and MRT
+// (MRT/mrt.cpp, MRT/another_mrt.cpp).  Per-thread arithmetic: d2q9_threads.h.
+#include <vector>
+
+#include "d2q9_host.h"
+#include "d2q9_threads.h"
+#include "lbm_internal.h"
+
+namespace lbm {
+namespace {
+
+constexpr int kThreads = 256;
+inline unsigned blocks_for(long long n) { return (unsigned)((n + kThreads - 1) / kThreads); }
+
+// ---- Shan-Chen kernels ----
+__global__ void __launch_bounds__(kThreads) k_sc_init(lbm2::ScParams P, const double *rho, const double *u1, const double *u2, double *f)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < (long long)P.nx * P.ny) lbm2::sc_init_thread(P, rho, u1, u2, f, i);
+}
+__global__ void __launch_bounds__(kThreads) k_sc_density(lbm2::ScParams P, const double *f, double *rho, double *psi)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < (long long)P.nx * P.ny) lbm2::sc_density_thread(P, f, rho, psi, i);
+}
+__global__ void __launch_bounds__(kThreads) k_sc_collide(lbm2::ScParams P, const double *f, const double *rho, const double *psi,
+                                                          double *f2, double *u1, double *u2)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < (long long)P.nx * P.ny) lbm2::sc_collide_thread(P, f, rho, psi, f2, u1, u2, (int)(i % P.nx), (int)(i / P.nx));
+}
+// ---- binary kernels (node index i = iX*NY+iY, iY fastest) ----
+__global__ void __launch_bounds__(kThreads) k_b2_wallphase(lbm2::B2Params P, double *phase)
+{
+    const int ix = blockIdx.x * blockDim.x + threadIdx.x;   // binary.cpp:136-140
+    if (ix >= P.nx) return;
+    phase[(long long)ix * P.ny] = phase[(long long)ix * P.ny + 1] - P.wall_gradient;
+    phase[(long long)ix * P.ny + P.ny - 1] = phase[(long long)ix * P.ny + P.ny - 2] - P.wall_gradient;
+}
+__global__ void __launch_bounds__(kThreads) k_b2_init(lbm2::B2Params P, const double *phase, double *fa, double *ga, double *fb,
+                                                       double *gb, double *rho, double *ux, double *uy)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < (long long)P.nx * P.ny) lbm2::b2_init_thread(P, phase, fa, ga, fb, gb, rho, ux, uy, (int)(i / P.ny), (int)(i % P.ny));
+}
+__global__ void __launch_bounds__(kThreads) k_b2_phase(lbm2::B2Params P, const double *g, double *phase)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < (long long)P.nx * P.ny) lbm2::b2_phase_thread(P, g, phase, (int)(i / P.ny), (int)(i % P.ny));
+}
+__global__ void __launch_bounds__(kThreads) k_b2_collide(lbm2::B2Params P, const double *f, const double *g, const double *phase,
+                                                          double *f2, double *g2, double *rho, double *ux, double *uy)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < (long long)P.nx * P.ny) lbm2::b2_collide_thread(P, f, g, phase, f2, g2, rho, ux, uy, (int)(i / P.ny), (int)(i % P.ny));
+}
+// ---- MRT kernels ----
+__global__ void __launch_bounds__(kThreads) k_mrt_init(lbm2::MrtParams P, const double *rho, const double *ux, const double *uy, double *f)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < (long long)P.nx * P.ny) lbm2::mrt_init_thread(P, rho, ux, uy, f, i);
+}
+__global__ void __launch_bounds__(kThreads) k_mrt_step(lbm2::MrtParams P, const double *f, const double *force, double *f2,
+                                                        double *rho, double *ux, double *uy)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < (long long)P.nx * P.ny) lbm2::mrt_thread(P, f, force, f2, rho, ux, uy, (int)(i / P.ny), (int)(i % P.ny));
+}
+// ---- AoS <-> SoA at the boundary ----
+__global__ void __launch_bounds__(kThreads) k_aos_to_soa9(long long n, const double *aos, double *soa)
+{
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < n * 9) soa[(t % 9) * n + t / 9] = aos[t];
+}
+__global__ void __launch_bounds__(kThreads) k_soa_to_aos9(long long n, const double *soa, double *aos)
+{
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < n * 9) aos[t] = soa[(t % 9) * n + t / 9];
+}
+
+// common storage of the 2-D models
+class Model2D : public Model {
+public:
+    Model2D(Runtime &rt, const lbm_config &cfg, int nsets) : rt_(rt), cfg_(cfg), nsets_(nsets) {}
+    ~Model2D() override
+    {
+        cudaSetDevice(rt_.device);
+        for (int b = 0; b < 2; b++) { cudaFree(f_[b]); cudaFree(g_[b]); }
+        for (double *p : fields_) cudaFree(p);
+        cudaFree(aux_); cudaFree(diag_);
+    }
+    lbm_status alloc_common()
+    {
+        if (cfg_.nx < 3 || cfg_.ny < 3 || cfg_.nz != 1) return rt_.fail(LBM_EINVAL, "2-D model: need nx,ny >= 3 and nz == 1");
+        n_ = (long long)cfg_.nx * cfg_.ny;
+        for (int b = 0; b < 2; b++) {
+            LBM_CUDA(rt_, cudaMalloc(&f_[b], 9 * n_ * sizeof(double)));
+            LBM_CUDA(rt_, cudaMemsetAsync(f_[b], 0, 9 * n_ * sizeof(double), rt_.stream));
+            if (nsets_ == 2) {
+                LBM_CUDA(rt_, cudaMalloc(&g_[b], 9 * n_ * sizeof(double)));
+                LBM_CUDA(rt_, cudaMemsetAsync(g_[b], 0, 9 * n_ * sizeof(double), rt_.stream));
+            }
+        }
+        for (double *&p : fields_) {
+            LBM_CUDA(rt_, cudaMalloc(&p, n_ * sizeof(double)));
+            LBM_CUDA(rt_, cudaMemsetAsync(p, 0, n_ * sizeof(double), rt_.stream));
+        }
+        LBM_CUDA(rt_, cudaMalloc(&diag_, (size_t)(diagnostics_scratch_blocks() + 1) * 6 * sizeof(double)));
+        LBM_CUDA(rt_, cudaStreamSynchronize(rt_.stream));
+        return LBM_OK;
+    }
+    size_t local_nodes() const override { return (size_t)n_; }
+    int q() const override { return 9; }
+    int nsets() const override { return nsets_; }
+    virtual bool has_field(int field) const = 0;
+    lbm_status set_field(int field, const double *host) override
+    {
+        if (!has_field(field)) return rt_.fail(LBM_EINVAL, "this model has no such field");
+        LBM_CUDA(rt_, cudaMemcpyAsync(fields_[field], host, n_ * sizeof(double), cudaMemcpyHostToDevice, rt_.stream));
+        LBM_CUDA(rt_, cudaStreamSynchronize(rt_.stream));
+        return LBM_OK;
+    }
+    lbm_status get_field(int field, double *host) override
+    {
+        if (!has_field(field)) return rt_.fail(LBM_EINVAL, "this model has no such field");
+        LBM_CUDA(rt_, cudaMemcpyAsync(host, fields_[field], n_ * sizeof(double), cudaMemcpyDeviceToHost, rt_.stream));
+        LBM_CUDA(rt_, cudaStreamSynchronize(rt_.stream));
+        return LBM_OK;
+    }
+    lbm_status set_populations(int set, const double *host) override
+    {
+        if (set < 0 || set >= nsets_) return rt_.fail(LBM_EINVAL, "no such population set");
+        double *stage = nullptr;
+        LBM_CUDA(rt_, cudaMalloc(&stage, 9 * n_ * sizeof(double)));
+        lbm_status st = rt_.cuda(cudaMemcpyAsync(stage, host, 9 * n_ * sizeof(double), cudaMemcpyHostToDevice, rt_.stream), "H2D populations");
+        if (st == LBM_OK) {
+            k_aos_to_soa9<<<blocks_for(9 * n_), kThreads, 0, rt_.stream>>>(n_, stage, set == 0 ? f_[cur_] : g_[cur_]);
+            st = rt_.launched("k_aos_to_soa9");
+        }
+        if (st == LBM_OK) st = after_set_populations(set);
+        if (st == LBM_OK) st = rt_.cuda(cudaStreamSynchronize(rt_.stream), "sync");
+        cudaFree(stage);
+        return st;
+    }
+    virtual lbm_status after_set_populations(int) { return LBM_OK; }
+    lbm_status get_populations(int set, double *host) override
+    {
+        if (set < 0 || set >= nsets_) return rt_.fail(LBM_EINVAL, "no such population set");
+        double *stage = nullptr;
+        LBM_CUDA(rt_, cudaMalloc(&stage, 9 * n_ * sizeof(double)));
+        k_soa_to_aos9<<<blocks_for(9 * n_), kThreads, 0, rt_.stream>>>(n_, set == 0 ? f_[cur_] : g_[cur_], stage);
+        lbm_status st = rt_.launched("k_soa_to_aos9");
+        if (st == LBM_OK) st = rt_.cuda(cudaMemcpyAsync(host, stage, 9 * n_ * sizeof(double), cudaMemcpyDeviceToHost, rt_.stream), "D2H populations");
+        if (st == LBM_OK) st = rt_.cuda(cudaStreamSynchronize(rt_.stream), "sync");
+        cudaFree(stage);
+        return st;
+    }
+    lbm_status diag_common(int skip_border, double *mass, double *mom, double *phase_mass, int *has_nan)
+    {
+        DiagLayout L;
+        L.f = f_[cur_]; L.g = nsets_ == 2 ? g_[cur_] : nullptr;
+        L.stride_k = n_; L.plane_stride = 0; L.planes = 1; L.nx = cfg_.nx; L.ny = cfg_.ny; L.q = 9;
+        L.skip_border = skip_border; L.node_major_x = 0;
+        double out[6];
+        LBM_TRY(run_diagnostics(rt_, L, diag_, diagnostics_scratch_blocks(), out));
+        if (mass) *mass = out[0];
+        if (mom) { mom[0] = out[1]; mom[1] = out[2]; mom[2] = 0.0; }
+        if (phase_mass) *phase_mass = out[4];
+        if (has_nan) *has_nan = out[5] != 0.0;
+        return LBM_OK;
+    }
+
+protected:
+    Runtime &rt_;
+    lbm_config cfg_;
+    int nsets_, cur_ = 0;
+    long long n_ = 0;
+    double *f_[2] = {nullptr, nullptr}, *g_[2] = {nullptr, nullptr};
+    double *fields_[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};  // indexed by lbm_field
+    double *aux_ = nullptr, *diag_ = nullptr;
+};
+
+class ShanChen : public Model2D {
+public:
+    ShanChen(Runtime &rt, const lbm_config &cfg) : Model2D(rt, cfg, 1) {}
+    lbm_status setup()
+    {
+        LBM_TRY(alloc_common());
+        P_ = lbm2::ScParams{cfg_.nx, cfg_.ny, cfg_.tau, cfg_.g};
+        LBM_CUDA(rt_, cudaMalloc(&aux_, n_ * sizeof(double)));   // psi
+        return LBM_OK;
+    }
+    bool has_field(int f) const override { return f == LBM_RHO || f == LBM_UX || f == LBM_UY; }
+    lbm_status init() override
+    {
+        k_sc_init<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, fields_[LBM_RHO], fields_[LBM_UX], fields_[LBM_UY], f_[cur_]);
+        return rt_.launched("k_sc_init");
+    }
+    lbm_status step(int nsteps) override
+    {
+        for (int t = 0; t < nsteps; t++) {
+            rt_.about_to_launch();
+            k_sc_density<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, f_[cur_], fields_[LBM_RHO], aux_);
+            LBM_TRY(rt_.launched("k_sc_density"));
+            rt_.about_to_launch();
+            k_sc_collide<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, f_[cur_], fields_[LBM_RHO], aux_, f_[1 - cur_],
+                                                                      fields_[LBM_UX], fields_[LBM_UY]);
+            LBM_TRY(rt_.launched("k_sc_collide"));
+            cur_ = 1 - cur_;
+        }
+        return LBM_OK;
+    }
+    lbm_status diagnostics(double *m, double *mom, double *pm, int *nan) override { return diag_common(0, m, mom, pm, nan); }
+
+private:
+    lbm2::ScParams P_{};
+};
+
+class Binary2D : public Model2D {
+public:
+    Binary2D(Runtime &rt, const lbm_config &cfg) : Model2D(rt, cfg, 2) {}
+    lbm_status setup()
+    {
+        if (cfg_.ny < 4) return rt_.fail(LBM_EINVAL, "binary D2Q9: ny must be at least 4");
+        LBM_TRY(alloc_common());
+        P_ = lbm2::B2Params{cfg_.nx, cfg_.ny, cfg_.aconst, cfg_.kconst, cfg_.gammaconst, cfg_.wall_gradient,
+                            cfg_.tau_gas, cfg_.tau_liq - cfg_.tau_gas, 1.0 / cfg_.tau_phi};
+        return LBM_OK;
+    }
+    bool has_field(int f) const override { return f == LBM_RHO || f == LBM_PHASE || f == LBM_UX || f == LBM_UY; }
+    lbm_status init() override
+    {
+        k_b2_wallphase<<<blocks_for(cfg_.nx), kThreads, 0, rt_.stream>>>(P_, fields_[LBM_PHASE]);
+        LBM_TRY(rt_.launched("k_b2_wallphase"));
+        k_b2_init<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, fields_[LBM_PHASE], f_[0], g_[0], f_[1], g_[1],
+                                                               fields_[LBM_RHO], fields_[LBM_UX], fields_[LBM_UY]);
+        return rt_.launched("k_b2_init");
+    }
+    lbm_status step(int nsteps) override
+    {
+        for (int t = 0; t < nsteps; t++) {
+            rt_.about_to_launch();
+            k_b2_phase<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, g_[cur_], fields_[LBM_PHASE]);
+            LBM_TRY(rt_.launched("k_b2_phase"));
+            rt_.about_to_launch();
+            k_b2_collide<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, f_[cur_], g_[cur_], fields_[LBM_PHASE], f_[1 - cur_],
+                                                                      g_[1 - cur_], fields_[LBM_RHO], fields_[LBM_UX], fields_[LBM_UY]);
+            LBM_TRY(rt_.launched("k_b2_collide"));
+            cur_ = 1 - cur_;
+        }
+        return LBM_OK;
+    }
+    // wall rows are never streamed into, so a load must reach both buffers
+    lbm_status after_set_populations(int set) override
+    {
+        double *src = set == 0 ? f_[cur_] : g_[cur_], *dst = set == 0 ? f_[1 - cur_] : g_[1 - cur_];
+        return rt_.cuda(cudaMemcpyAsync(dst, src, 9 * n_ * sizeof(double), cudaMemcpyDeviceToDevice, rt_.stream), "copy populations");
+    }
+    lbm_status diagnostics(double *m, double *mom, double *pm, int *nan) override { return diag_common(2, m, mom, pm, nan); }
+
+private:
+    lbm2::B2Params P_{};
+};
+
+class Mrt : public Model2D {
+public:
+    Mrt(Runtime &rt, const lbm_config &cfg) : Model2D(rt, cfg, 1) {}
+    lbm_status setup()
+    {
+        LBM_TRY(alloc_common());
+        std::vector<double> force(cfg_.nx);
+        lbm2::mrt_build_tables(&P_, cfg_.model == LBM_MRT_GS_D2Q9 ? 0 : 1, cfg_.nx, cfg_.ny, cfg_.omega, cfg_.omega_bulk,
+                               cfg_.force_ampl, force.data());
+        LBM_CUDA(rt_, cudaMalloc(&aux_, cfg_.nx * sizeof(double)));
+        LBM_CUDA(rt_, cudaMemcpy(aux_, force.data(), cfg_.nx * sizeof(double), cudaMemcpyHostToDevice));
+        return LBM_OK;
+    }
+    bool has_field(int f) const override { return f == LBM_RHO || f == LBM_UX || f == LBM_UY; }
+    lbm_status init() override
+    {
+        k_mrt_init<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, fields_[LBM_RHO], fields_[LBM_UX], fields_[LBM_UY], f_[cur_]);
+        return rt_.launched("k_mrt_init");
+    }
+    lbm_status step(int nsteps) override
+    {
+        for (int t = 0; t < nsteps; t++) {
+            rt_.about_to_launch();
+            k_mrt_step<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, f_[cur_], aux_, f_[1 - cur_], fields_[LBM_RHO],
+                                                                    fields_[LBM_UX], fields_[LBM_UY]);
+            LBM_TRY(rt_.launched("k_mrt_step"));
+            cur_ = 1 - cur_;
+        }
+        return LBM_OK;
+    }
+    lbm_status diagnostics(double *m, double *mom, double *pm, int *nan) override { return diag_common(0, m, mom, pm, nan); }
+
+private:
+    lbm2::MrtParams P_{};
+};
+
+template <class T>
+Model *make(Runtime &rt, const lbm_config &cfg, lbm_status *st)
+{
+    T *m = new T(rt, cfg);
+    *st = m->setup();
+    if (*st != LBM_OK) {
+        delete m;
+        return nullptr;
+    }
+    return m;
+}
+
+}  // namespace
+
+Model *make_d2q9_shanchen(Runtime &rt, const lbm_config &cfg, lbm_status *st) { return make<ShanChen>(rt, cfg, st); }
+Model *make_d2q9_binary(Runtime &rt, const lbm_config &cfg, lbm_status *st) { return make<Binary2D>(rt, cfg, st); }
+Model *make_d2q9_mrt(Runtime &rt, const lbm_config &cfg, lbm_status *st) { return make<Mrt>(rt, cfg, st); }
+
+}  // namespace lbm

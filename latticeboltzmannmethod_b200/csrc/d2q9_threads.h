@@ -1,0 +1,375 @@
+// d2q9_threads.h -- what one thread of each D2Q9 kernel does (Shan-Chen, binary
+// liquid, MRT).  Plain C++ so the CPU unit test (tests/emu/) can run the same
+// code; the __global__ wrappers live in d2q9_models.cu.
+//
+// Storage: populations SoA [k][n]; the flat node index is the reference's own
+// (Shan-Chen: i = iY*nx+iX, shanchen.cpp:140; binary/MRT: i = iX*NY+iY,
+// binary.cpp:24, mrt.cpp:14), so fields need no transposition at the boundary.
+// Arrays hold the streamed populations, i.e. what the reference's f holds at the
+// start of a step.  Compile with -fmad=false / -ffp-contract=off.
+#ifndef LBM_D2Q9_THREADS_H
+#define LBM_D2Q9_THREADS_H
+
+#include "d3q19_node.h"  // LBM_HD
+#include "lbm_exp.h"
+
+namespace lbm2 {
+
+// shanchen.cpp:18-20, binary.cpp:44-47, mrt.cpp:63-67
+#define LBM2_CX {0, 1, 0, -1, 0, 1, -1, -1, 1}
+#define LBM2_CY {0, 0, 1, 0, -1, 1, 1, -1, -1}
+#define LBM2_W {4.0 / 9.0, 1.0 / 9.0, 1.0 / 9.0, 1.0 / 9.0, 1.0 / 9.0, 1.0 / 36.0, 1.0 / 36.0, 1.0 / 36.0, 1.0 / 36.0}
+#define LBM2_OPP {0, 3, 4, 1, 2, 7, 8, 5, 6}
+
+// ======================= Shan-Chen (ShanChen/shanchen.cpp) =======================
+struct ScParams {
+    int nx, ny;
+    double tau, g;
+};
+
+// shanchen.cpp:124-132 plus psi = 1 - exp(-rho), which the reference re-evaluates
+// for every neighbour (:152-157); same function, same argument, computed once.
+LBM_HD void sc_density_thread(const ScParams &P, const double *f, double *rho, double *psi, long long i)
+{
+    const long long n = (long long)P.nx * P.ny;
+    double r = 0;
+#pragma unroll
+    for (int k = 0; k < 9; k++) r += f[k * n + i];
+    rho[i] = r;
+    psi[i] = 1.0 - lbm_exp(-r);
+}
+
+// shanchen.cpp:136-186: force (float accumulators), shifted velocity, force
+// populations, closed-form equilibria, in-place BGK, periodic push
+LBM_HD void sc_collide_thread(const ScParams &P, const double *f, const double *rho, const double *psi, double *f2,
+                              double *u1, double *u2, int ix, int iy)
+{
+    const int nx = P.nx, ny = P.ny;
+    const long long n = (long long)nx * ny, i = (long long)iy * nx + ix;
+    const int CX[9] = LBM2_CX, CY[9] = LBM2_CY;
+    const double W[9] = LBM2_W;
+    const double dense = rho[i];
+    long long nb[9];
+#pragma unroll
+    for (int k = 0; k < 9; k++) {
+        const int x2 = (ix + CX[k] + nx) % nx, y2 = (iy + CY[k] + ny) % ny;
+        nb[k] = (long long)nx * y2 + x2;
+    }
+    float fx = 0.0, fy = 0.0;
+#pragma unroll
+    for (int k = 0; k < 9; k++) {
+        const double ps = psi[nb[k]];
+        fx += W[k] * CX[k] * ps;
+        fy += W[k] * CY[k] * ps;
+    }
+    fx = -P.g * psi[i] * fx;
+    fy = -P.g * psi[i] * fy;
+    double F[9];
+#pragma unroll
+    for (int k = 0; k < 9; k++) F[k] = f[k * n + i];
+    const double v1 = (F[1] - F[3] + F[5] - F[6] - F[7] + F[8]) / dense + fx / (2.0 * dense);
+    const double v2 = (F[2] - F[4] + F[5] + F[6] - F[7] - F[8]) / dense + fy / (2.0 * dense);
+    u1[i] = v1;
+    u2[i] = v2;
+    double fpop[9];
+#pragma unroll
+    for (int k = 0; k < 9; k++) {
+        const int cx = CX[k], cy = CY[k];
+        fpop[k] = W[k] * (1 - 0.5 / P.tau) *
+                  ((3 * (cx - v1) + 9 * cx * (cx * v1 + cy * v2)) * fx + (3 * (cy - v2) + 9 * cy * (cx * v1 + cy * v2)) * fy);
+    }
+    const float usq = v1 * v1 + v2 * v2;
+    double feq[9];
+    feq[0] = 4.0 / 9.0 * dense * (1.0 - 1.5 * usq);
+    feq[1] = 1.0 / 9.0 * dense * (1.0 + 3 * v1 + 4.5 * v1 * v1 - 1.5 * usq);
+    feq[2] = 1.0 / 9.0 * dense * (1.0 + 3 * v2 + 4.5 * v2 * v2 - 1.5 * usq);
+    feq[3] = 1.0 / 9.0 * dense * (1.0 - 3 * v1 + 4.5 * v1 * v1 - 1.5 * usq);
+    feq[4] = 1.0 / 9.0 * dense * (1.0 - 3 * v2 + 4.5 * v2 * v2 - 1.5 * usq);
+    feq[5] = 1.0 / 36.0 * dense * (1.0 + 3 * (v1 + v2) + 4.5 * (v1 + v2) * (v1 + v2) - 1.5 * usq);
+    feq[6] = 1.0 / 36.0 * dense * (1.0 + 3 * (-v1 + v2) + 4.5 * (-v1 + v2) * (-v1 + v2) - 1.5 * usq);
+    feq[7] = 1.0 / 36.0 * dense * (1.0 + 3 * (-v1 - v2) + 4.5 * (v1 + v2) * (v1 + v2) - 1.5 * usq);
+    feq[8] = 1.0 / 36.0 * dense * (1.0 + 3 * (v1 - v2) + 4.5 * (v1 - v2) * (v1 - v2) - 1.5 * usq);
+#pragma unroll
+    for (int k = 0; k < 9; k++) {
+        double fk = F[k];
+        fk += -1.0 / P.tau * (fk - feq[k]) + fpop[k];
+        f2[k * n + nb[k]] = fk;
+    }
+}
+
+// shanchen.cpp:95-113 generalised to a given (rho, u): f = feq(rho, u)
+LBM_HD void sc_init_thread(const ScParams &P, const double *rho, const double *u1, const double *u2, double *f, long long i)
+{
+    const long long n = (long long)P.nx * P.ny;
+    const double dense = rho[i], v1 = u1[i], v2 = u2[i];
+    const float usq = v1 * v1 + v2 * v2;
+    double feq[9];
+    feq[0] = 4.0 / 9.0 * dense * (1.0 - 1.5 * usq);
+    feq[1] = 1.0 / 9.0 * dense * (1.0 + 3 * v1 + 4.5 * v1 * v1 - 1.5 * usq);
+    feq[2] = 1.0 / 9.0 * dense * (1.0 + 3 * v2 + 4.5 * v2 * v2 - 1.5 * usq);
+    feq[3] = 1.0 / 9.0 * dense * (1.0 - 3 * v1 + 4.5 * v1 * v1 - 1.5 * usq);
+    feq[4] = 1.0 / 9.0 * dense * (1.0 - 3 * v2 + 4.5 * v2 * v2 - 1.5 * usq);
+    feq[5] = 1.0 / 36.0 * dense * (1.0 + 3 * (v1 + v2) + 4.5 * (v1 + v2) * (v1 + v2) - 1.5 * usq);
+    feq[6] = 1.0 / 36.0 * dense * (1.0 + 3 * (-v1 + v2) + 4.5 * (-v1 + v2) * (-v1 + v2) - 1.5 * usq);
+    feq[7] = 1.0 / 36.0 * dense * (1.0 + 3 * (-v1 - v2) + 4.5 * (v1 + v2) * (v1 + v2) - 1.5 * usq);
+    feq[8] = 1.0 / 36.0 * dense * (1.0 + 3 * (v1 - v2) + 4.5 * (v1 - v2) * (v1 - v2) - 1.5 * usq);
+    for (int k = 0; k < 9; k++) f[k * n + i] = feq[k];
+}
+
+// ======================= binary liquid (FreeEnergy/binary.cpp) =======================
+struct B2Params {
+    int nx, ny;
+    double aconst, kconst, gammaconst, wall_gradient, tau_gas, dtau, omega_phi;
+};
+
+// the float-typed tables of binary.cpp:48-59, promoted exactly as the reference promotes them
+#define LBM2_B_WXX {0.0f, (float)(1.0 / 3.0), (float)(-1.0 / 6.0), (float)(1.0 / 3.0), (float)(-1.0 / 6.0), (float)(-1.0 / 24.0), (float)(-1.0 / 24.0), (float)(-1.0 / 24.0), (float)(-1.0 / 24.0)}
+#define LBM2_B_WYY {0.0f, (float)(-1.0 / 6.0), (float)(1.0 / 3.0), (float)(-1.0 / 6.0), (float)(1.0 / 3.0), (float)(-1.0 / 24.0), (float)(-1.0 / 24.0), (float)(-1.0 / 24.0), (float)(-1.0 / 24.0)}
+#define LBM2_B_WXY {0.0f, 0.0f, 0.0f, 0.0f, 0.0f, (float)(1.0 / 4.0), (float)(-1.0 / 4.0), (float)(1.0 / 4.0), (float)(-1.0 / 4.0)}
+#define LBM2_B_GX {0.0f, (float)(4.0 / 12.0), 0.0f, (float)(-4.0 / 12.0), 0.0f, (float)(1.0 / 12.0), (float)(-1.0 / 12.0), (float)(-1.0 / 12.0), (float)(1.0 / 12.0)}
+#define LBM2_B_GY {0.0f, 0.0f, (float)(4.0 / 12.0), 0.0f, (float)(-4.0 / 12.0), (float)(1.0 / 12.0), (float)(1.0 / 12.0), (float)(-1.0 / 12.0), (float)(-1.0 / 12.0)}
+#define LBM2_B_LAP {(float)(-20.0 / 6.0), (float)(4.0 / 6.0), (float)(4.0 / 6.0), (float)(4.0 / 6.0), (float)(4.0 / 6.0), (float)(1.0 / 6.0), (float)(1.0 / 6.0), (float)(1.0 / 6.0), (float)(1.0 / 6.0)}
+
+// binary.cpp:239-250: phase = sum of g on interior rows, wall rows from their neighbour row
+LBM_HD void b2_phase_thread(const B2Params &P, const double *g, double *phase, int ix, int iy)
+{
+    const int NY = P.ny;
+    if (iy < 1 || iy > NY - 2) return;
+    const long long n = (long long)P.nx * NY, i = (long long)ix * NY + iy;
+    double ph = 0.0;
+#pragma unroll
+    for (int k = 0; k < 9; k++) ph += g[k * n + i];
+    phase[i] = ph;
+    if (iy == 1) phase[i - 1] = ph - P.wall_gradient;
+    if (iy == NY - 2) phase[i + 1] = ph - P.wall_gradient;
+}
+
+LBM_HD void b2_stencils(const B2Params &P, const double *phase, int ix, int iy, double &gx, double &gy, double &lap)
+{
+    const int CX[9] = LBM2_CX, CY[9] = LBM2_CY;
+    const float GX[9] = LBM2_B_GX, GY[9] = LBM2_B_GY, LAP[9] = LBM2_B_LAP;
+    double al = 0.0, ax = 0.0, ay = 0.0;
+#pragma unroll
+    for (int k = 0; k < 9; k++) {
+        const int x2 = (ix + CX[k] + P.nx) % P.nx, y2 = (iy + CY[k] + P.ny) % P.ny;
+        const double ph = phase[(long long)x2 * P.ny + y2];
+        al += LAP[k] * ph;
+        ax += GX[k] * ph;
+        ay += GY[k] * ph;
+    }
+    gx = ax; gy = ay; lap = al;
+}
+
+// binary.cpp:291-313 (and :169-195)
+LBM_HD void b2_equilibria(const B2Params &P, double d, double ph, double ux, double uy, double gx, double gy, double lap,
+                          double *feq, double *geq)
+{
+    const int CX[9] = LBM2_CX, CY[9] = LBM2_CY;
+    const double W[9] = LBM2_W;
+    const float WXX[9] = LBM2_B_WXX, WYY[9] = LBM2_B_WYY, WXY[9] = LBM2_B_WXY;
+    double sum = 0.0, sum_phase = 0.0;
+    const double ps = ph * ph;
+    const double pb = d / 3.0 + P.aconst * (-0.5 * ps + 3.0 / 4.0 * ps * ps) - P.kconst * ph * lap;
+    const double mu = P.gammaconst * (P.aconst * (-ph + ph * ph * ph) - P.kconst * lap);
+#pragma unroll
+    for (int k = 1; k < 9; k++) {
+        const int cx = CX[k], cy = CY[k];
+        feq[k] = W[k] * (3.0 * pb + 3.0 * d * (cx * ux + cy * uy) +
+                         4.5 * d * ((cx * cx - 1.0 / 3.0) * ux * ux + (cy * cy - 1.0 / 3.0) * uy * uy + 2.0 * ux * uy * cx * cy)) +
+                 P.kconst * (WXX[k] * gx * gx + WYY[k] * gy * gy + WXY[k] * gx * gy);
+        geq[k] = W[k] * (3.0 * mu + 3.0 * ph * (cx * ux + cy * uy) +
+                         4.5 * ph * ((cx * cx - 1.0 / 3.0) * ux * ux + (cy * cy - 1.0 / 3.0) * uy * uy + 2.0 * ux * uy * cx * cy));
+        sum += feq[k];
+        sum_phase += geq[k];
+    }
+    feq[0] = d - sum;
+    geq[0] = ph - sum_phase;
+}
+
+// binary.cpp:142-196 for one node (all nodes, wall rows included); writes both buffers so the
+// wall rows -- which the reference never streams into -- persist across the buffer swap
+LBM_HD void b2_init_thread(const B2Params &P, const double *phase, double *fa, double *ga, double *fb, double *gb,
+                           double *rho, double *ux, double *uy, int ix, int iy)
+{
+    const long long n = (long long)P.nx * P.ny, i = (long long)ix * P.ny + iy;
+    double gx, gy, lap, feq[9], geq[9];
+    b2_stencils(P, phase, ix, iy, gx, gy, lap);
+    rho[i] = 1.0; ux[i] = 0.0; uy[i] = 0.0;
+    b2_equilibria(P, 1.0, phase[i], 0.0, 0.0, gx, gy, lap, feq, geq);
+    for (int k = 0; k < 9; k++) {
+        fa[k * n + i] = feq[k]; ga[k * n + i] = geq[k];
+        fb[k * n + i] = feq[k]; gb[k * n + i] = geq[k];
+    }
+}
+
+// binary.cpp:252-327 (collide), :201-233 (bounce-back rows) and :341-350 (pull streaming) as one
+// push: a population that would enter a wall row comes back to its own node reversed
+LBM_HD void b2_collide_thread(const B2Params &P, const double *f, const double *g, const double *phase, double *f2,
+                              double *g2, double *rho, double *uxo, double *uyo, int ix, int iy)
+{
+    const int NX = P.nx, NY = P.ny;
+    if (iy < 1 || iy > NY - 2) return;
+    const long long n = (long long)NX * NY, i = (long long)ix * NY + iy;
+    const int CX[9] = LBM2_CX, CY[9] = LBM2_CY, OPP[9] = LBM2_OPP;
+    double F[9], G[9];
+    double d = 0.0, jx = 0.0, jy = 0.0;
+#pragma unroll
+    for (int k = 0; k < 9; k++) {
+        F[k] = f[k * n + i];
+        G[k] = g[k * n + i];
+        d += F[k];
+        jx += F[k] * CX[k];
+        jy += F[k] * CY[k];
+    }
+    const double ux = jx / d, uy = jy / d;
+    rho[i] = d; uxo[i] = ux; uyo[i] = uy;
+    double gx, gy, lap, feq[9], geq[9];
+    b2_stencils(P, phase, ix, iy, gx, gy, lap);
+    const double ph = phase[i];
+    b2_equilibria(P, d, ph, ux, uy, gx, gy, lap, feq, geq);
+    const double tau_rho = P.tau_gas + (ph + 1.0) / 2.0 * P.dtau;
+    const double omega_rho = 1.0 / tau_rho;
+#pragma unroll
+    for (int k = 0; k < 9; k++) {
+        const double fo = F[k] * (1.0 - omega_rho) + omega_rho * feq[k];
+        const double go = G[k] * (1.0 - P.omega_phi) + P.omega_phi * geq[k];
+        const int ty = iy + CY[k];
+        if (ty == 0 || ty == NY - 1) {
+            f2[OPP[k] * n + i] = fo;
+            g2[OPP[k] * n + i] = go;
+        } else {
+            const long long t = (long long)((ix + CX[k] + NX) % NX) * NY + ty;
+            f2[k * n + t] = fo;
+            g2[k * n + t] = go;
+        }
+    }
+}
+
+// ======================= MRT (MRT/mrt.cpp, MRT/another_mrt.cpp) =======================
+struct MrtParams {
+    int nx, ny, variant;       // 0 = Gram-Schmidt + force (mrt.cpp), 1 = Hermite (another_mrt.cpp)
+    double omegamat[9];
+    double M[9][9];
+    double B[9][9];            // GS: invM (mrt.cpp:82-91); Hermite: omegamat[m]*M[m][k] stored as B[k][m]
+    double s3, c32, c3s15;     // sqrt(3), 3/sqrt(2), 3*sqrt(1.5) (another_mrt.cpp:144-152)
+};
+
+// one node: moments, (GS) half-force shift, equilibrium moments, relaxation in moment space,
+// back-transform, periodic push.  mrt.cpp:146-251 / another_mrt.cpp:114-214.
+// forcex_of_ix: the per-column force mrt.cpp:165 evaluates with cos(); built on the host with the
+// same expression so the device needs no cos().
+LBM_HD void mrt_thread(const MrtParams &P, const double *f, const double *forcex_of_ix, double *f2, double *rho_o,
+                       double *ux_o, double *uy_o, int ix, int iy)
+{
+    const int NX = P.nx, NY = P.ny;
+    const long long n = (long long)NX * NY, i = (long long)ix * NY + iy;
+    const int CX[9] = LBM2_CX, CY[9] = LBM2_CY;
+    const double W[9] = LBM2_W;
+    double fl[9], eq[9], add[9];
+    double rho = 0.0, ux = 0.0, uy = 0.0;
+#pragma unroll
+    for (int k = 0; k < 9; k++) {
+        fl[k] = f[k * n + i];
+        rho += fl[k];
+        ux += fl[k] * CX[k];
+        uy += fl[k] * CY[k];
+    }
+    const double dense = rho;
+    ux /= dense;
+    uy /= dense;
+    if (P.variant == 0) {
+        const double forcex = forcex_of_ix[ix];
+        const double forcey = 0;
+        ux += forcex / (2.0 * dense);
+        ux += forcey / (2.0 * dense);
+        const double uxeq = ux, uyeq = uy;
+        eq[0] = dense;
+        eq[1] = -2.0 * dense + 3.0 * dense * (uxeq * uxeq + uyeq * uyeq);
+        eq[2] = dense - 3.0 * dense * (uxeq * uxeq + uyeq * uyeq);
+        eq[3] = dense * uxeq;
+        eq[4] = -dense * uxeq;
+        eq[5] = dense * uyeq;
+        eq[6] = -dense * uyeq;
+        eq[7] = dense * (uxeq * uxeq - uyeq * uyeq);
+        eq[8] = dense * uxeq * uyeq;
+        const double *om = P.omegamat;
+        double momforce[9];
+        momforce[0] = 0.0;
+        momforce[1] = (1.0 - om[1] / 2.0) * 6.0 * (uxeq * forcex + uyeq * forcey);
+        momforce[2] = 0.0;
+        momforce[3] = (1.0 - om[3] / 2.0) * forcex;
+        momforce[4] = 0.0;
+        momforce[5] = (1.0 - om[5] / 2.0) * forcey;
+        momforce[6] = 0.0;
+        momforce[7] = (1.0 - om[7] / 2.0) * 2.0 * (uxeq * forcex - uyeq * forcey);
+        momforce[8] = (1.0 - om[8] / 2.0) * (uxeq * forcey + uyeq * forcex);
+#pragma unroll
+        for (int m = 0; m < 9; m++) {
+            double a = 0.0;
+#pragma unroll
+            for (int k = 0; k < 9; k++) a = a + P.M[m][k] * (-fl[k]);
+            a += eq[m];
+            a *= om[m];
+            a += momforce[m];
+            add[m] = a;
+        }
+#pragma unroll
+        for (int k = 0; k < 9; k++) {
+            double addit = 0.0;
+#pragma unroll
+            for (int m = 0; m < 9; m++) addit = addit + P.B[k][m] * add[m];
+            fl[k] = fl[k] + addit;
+        }
+    } else {
+        const double uxeq = ux, uyeq = uy;
+        eq[0] = dense;
+        eq[1] = P.s3 * dense * uxeq;
+        eq[2] = P.s3 * dense * uyeq;
+        eq[3] = P.c32 * dense * uxeq * uxeq;
+        eq[4] = 3.0 * dense * uxeq * uyeq;
+        eq[5] = P.c32 * dense * uyeq * uyeq;
+        eq[6] = 4.5 * dense * uxeq * uxeq * uyeq * uyeq;
+        eq[7] = P.c3s15 * dense * uxeq * uyeq * uyeq;
+        eq[8] = P.c3s15 * dense * uxeq * uxeq * uyeq;
+#pragma unroll
+        for (int m = 0; m < 9; m++) {
+            double a = 0.0;
+#pragma unroll
+            for (int k = 0; k < 9; k++) a = a + P.M[m][k] * (-fl[k]);
+            a += eq[m];
+            add[m] = a;
+        }
+#pragma unroll
+        for (int k = 0; k < 9; k++) {
+            double addit = 0.0;
+#pragma unroll
+            for (int m = 0; m < 9; m++) addit = addit + P.B[k][m] * add[m];
+            fl[k] = fl[k] + W[k] * addit;
+        }
+    }
+    rho_o[i] = rho; ux_o[i] = ux; uy_o[i] = uy;
+#pragma unroll
+    for (int k = 0; k < 9; k++) {
+        const long long t = (long long)((ix + CX[k] + NX) % NX) * NY + (iy + CY[k] + NY) % NY;
+        f2[k * n + t] = fl[k];
+    }
+}
+
+// mrt.cpp:107-119 / another_mrt.cpp:97-109: second-order equilibrium from given rho, ux, uy
+LBM_HD void mrt_init_thread(const MrtParams &P, const double *rho_i, const double *ux_i, const double *uy_i, double *f,
+                            long long i)
+{
+    const long long n = (long long)P.nx * P.ny;
+    const int CX[9] = LBM2_CX, CY[9] = LBM2_CY;
+    const double W[9] = LBM2_W;
+    const double rho = rho_i[i], ux = ux_i[i], uy = uy_i[i];
+    const double fluxx = 3.0 * ux, fluxy = 3.0 * uy;
+    const double qxx = 4.5 * ux * ux, qxy = 9.0 * ux * uy, qyy = 4.5 * uy * uy;
+    for (int k = 0; k < 9; k++) {
+        const int cx = CX[k], cy = CY[k];
+        f[k * n + i] = rho * W[k] * (1.0 + fluxx * cx + fluxy * cy + qxx * (cx * cx - 1.0 / 3.0) + qxy * cx * cy + qyy * (cy * cy - 1.0 / 3.0));
+    }
+}
+
+}  // namespace lbm2
+#endif

@@ -1,0 +1,456 @@
+// d3q19_binary.cu -- D3Q19 binary-liquid z-slab on one GPU.
+//
+// Reference: Microchannel3D/{FullChannel,QuarterChannel}: Lattice<D> (lattice.h,
+// lattice.hpp) and the per-step part of Solver<D> (solver.hpp:821-928).
+// Per-thread arithmetic: d3q19_threads.h / d3q19_node.h.
+#include <dlfcn.h>
+#include <cstring>
+#include <vector>
+
+#include "d3q19_threads.h"
+#include "lbm_internal.h"
+
+namespace lbm {
+namespace {
+
+using lbm3::FieldsOut;
+using lbm3::Geom;
+using lbm3::Params;
+
+constexpr int kThreads = 256;
+
+__global__ void __launch_bounds__(kThreads) k_phase(Geom g, Params P, const double *gpop, double *phi, int zs0)
+{
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (long long)g.nx * g.ny) return;
+    lbm3::phase_thread(g, P, gpop, phi, zs0 + blockIdx.y, (int)(idx % g.nx), (int)(idx / g.nx));
+}
+
+template <bool FXY, bool WRITE>
+__global__ void __launch_bounds__(kThreads) k_collide_push(Geom g, Params P, const double *fin, const double *gin,
+                                                            const double *phi, double *fout, double *gout, FieldsOut o,
+                                                            int zs0)
+{
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (long long)g.nx * g.ny) return;
+    lbm3::collide_push_thread<FXY, WRITE>(g, P, fin, gin, phi, fout, gout, o, zs0 + blockIdx.y, (int)(idx % g.nx),
+                                          (int)(idx / g.nx));
+}
+
+__global__ void k_init_fields(Geom g, Params P, double *phi, double *rho)
+{
+    const int z = blockIdx.x * blockDim.x + threadIdx.x;
+    if (z < g.nz) lbm3::init_fields_plane(g, P, phi, rho, z);
+}
+
+__global__ void __launch_bounds__(kThreads) k_init_pops(Geom g, Params P, const double *phi, const double *rho,
+                                                         const double *ux, const double *uy, const double *uz,
+                                                         double *fout, double *gout)
+{
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (long long)g.nx * g.ny) return;
+    lbm3::init_pops_thread(g, P, phi, rho, ux, uy, uz, fout, gout, blockIdx.y, (int)(idx % g.nx), (int)(idx / g.nx));
+}
+
+__global__ void __launch_bounds__(kThreads) k_after_init(Geom g, Params P, const double *fin, FieldsOut o)
+{
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (long long)g.nx * g.ny) return;
+    lbm3::after_init_thread(g, P, fin, o, blockIdx.y, (int)(idx % g.nx), (int)(idx / g.nx));
+}
+
+__global__ void __launch_bounds__(kThreads) k_gather_aos(Geom g, const double *pop, double *aos)
+{
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (long long)g.nx * g.ny) return;
+    lbm3::gather_aos_thread(g, pop, aos, blockIdx.y, (int)(idx % g.nx), (int)(idx / g.nx));
+}
+
+__global__ void __launch_bounds__(kThreads) k_scatter_aos(Geom g, const double *aos, double *pop)
+{
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (long long)g.nx * g.ny) return;
+    lbm3::scatter_aos_thread(g, aos, pop, blockIdx.y, (int)(idx % g.nx), (int)(idx / g.nx));
+}
+
+// ---- NCCL, loaded on demand so the library has no hard dependency on it ----
+struct Id128 { char b[128]; };   // ncclUniqueId
+static_assert(sizeof(Id128) == LBM_COMM_ID_BYTES, "ncclUniqueId is 128 bytes");
+struct NcclApi {
+    void *lib = nullptr;
+    int (*GetUniqueId)(void *) = nullptr;
+    int (*CommInitRank)(void **, int, Id128, int) = nullptr;
+    int (*CommDestroy)(void *) = nullptr;
+    int (*GroupStart)() = nullptr;
+    int (*GroupEnd)() = nullptr;
+    int (*Send)(const void *, size_t, int, int, void *, cudaStream_t) = nullptr;
+    int (*Recv)(void *, size_t, int, int, void *, cudaStream_t) = nullptr;
+    const char *(*GetErrorString)(int) = nullptr;
+};
+constexpr int kNcclFloat64 = 8;  // ncclDouble
+
+NcclApi *nccl_api(std::string *why)
+{
+    static NcclApi api;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        const char *names[] = {"libnccl.so.2", "libnccl.so"};
+        for (const char *nm : names) {
+            api.lib = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
+            if (api.lib) break;
+        }
+        if (api.lib) {
+            api.GetUniqueId = (int (*)(void *))dlsym(api.lib, "ncclGetUniqueId");
+            api.CommInitRank = (int (*)(void **, int, Id128, int))dlsym(api.lib, "ncclCommInitRank");
+            api.CommDestroy = (int (*)(void *))dlsym(api.lib, "ncclCommDestroy");
+            api.GroupStart = (int (*)())dlsym(api.lib, "ncclGroupStart");
+            api.GroupEnd = (int (*)())dlsym(api.lib, "ncclGroupEnd");
+            api.Send = (int (*)(const void *, size_t, int, int, void *, cudaStream_t))dlsym(api.lib, "ncclSend");
+            api.Recv = (int (*)(void *, size_t, int, int, void *, cudaStream_t))dlsym(api.lib, "ncclRecv");
+            api.GetErrorString = (const char *(*)(int))dlsym(api.lib, "ncclGetErrorString");
+        }
+    }
+    if (!api.lib || !api.GetUniqueId || !api.CommInitRank || !api.Send || !api.Recv || !api.GroupStart || !api.GroupEnd) {
+        if (why) *why = "NCCL (libnccl.so.2) could not be loaded";
+        return nullptr;
+    }
+    return &api;
+}
+
+class Slab3D : public Model {
+public:
+    Slab3D(Runtime &rt, const lbm_config &cfg) : rt_(rt), cfg_(cfg) {}
+
+    lbm_status setup()
+    {
+        if (cfg_.nx < 4 || cfg_.ny < 4) return rt_.fail(LBM_EINVAL, "D3Q19: nx and ny must be at least 4");
+        if (cfg_.slab_count < 1 || cfg_.slab_rank < 0 || cfg_.slab_rank >= cfg_.slab_count)
+            return rt_.fail(LBM_EINVAL, "bad slab_rank/slab_count");
+        // solver.hpp:25-30
+        const int zstep = cfg_.nz / cfg_.slab_count;
+        z_begin_ = cfg_.slab_rank * zstep;
+        int z_end = z_begin_ + zstep - 1;
+        if (cfg_.slab_rank == cfg_.slab_count - 1) z_end = cfg_.nz - 1;
+        g_.nx = cfg_.nx; g_.ny = cfg_.ny; g_.nz = z_end - z_begin_ + 1;
+        if (g_.nz < 2) return rt_.fail(LBM_EINVAL, "D3Q19: every slab needs at least 2 z planes");
+        g_.pl = ((long long)g_.nx * g_.ny + 15) / 16 * 16;
+        P_.aconst = cfg_.aconst; P_.kconst = cfg_.kconst; P_.gammaconst = cfg_.gammaconst;
+        P_.tau_gas = cfg_.tau_gas; P_.dtau = cfg_.tau_liq - cfg_.tau_gas;
+        P_.omega_phi = 1.0 / cfg_.tau_phi;
+        P_.fx = cfg_.force[0]; P_.fy = cfg_.force[1]; P_.fz = cfg_.force[2];
+        P_.phase_gradient = cfg_.wall_gradient; P_.rho_wall = cfg_.rho_wall;
+        fxy_ = P_.fx != 0.0 || P_.fy != 0.0;
+
+        const size_t pop_bytes = (size_t)(g_.nz + 4) * 19 * g_.pl * sizeof(double);
+        for (int b = 0; b < 2; b++) {
+            LBM_CUDA(rt_, cudaMalloc(&f_[b], pop_bytes));
+            LBM_CUDA(rt_, cudaMalloc(&gq_[b], pop_bytes));
+            LBM_CUDA(rt_, cudaMemsetAsync(f_[b], 0, pop_bytes, rt_.stream));
+            LBM_CUDA(rt_, cudaMemsetAsync(gq_[b], 0, pop_bytes, rt_.stream));
+        }
+        const size_t phi_bytes = (size_t)(g_.nz + 4) * g_.pl * sizeof(double);
+        LBM_CUDA(rt_, cudaMalloc(&phi_, phi_bytes));
+        LBM_CUDA(rt_, cudaMemsetAsync(phi_, 0, phi_bytes, rt_.stream));
+        const size_t fld_bytes = (size_t)g_.nz * g_.pl * sizeof(double);
+        double **fl[4] = {&rho_, &ux_, &uy_, &uz_};
+        for (auto p : fl) {
+            LBM_CUDA(rt_, cudaMalloc(p, fld_bytes));
+            LBM_CUDA(rt_, cudaMemsetAsync(*p, 0, fld_bytes, rt_.stream));
+        }
+        LBM_CUDA(rt_, cudaMalloc(&diag_, (size_t)(diagnostics_scratch_blocks() + 1) * 6 * sizeof(double)));
+        LBM_CUDA(rt_, cudaStreamSynchronize(rt_.stream));
+        return LBM_OK;
+    }
+
+    ~Slab3D() override
+    {
+        cudaSetDevice(rt_.device);
+        if (comm_) {
+            NcclApi *api = nccl_api(nullptr);
+            if (api && api->CommDestroy) api->CommDestroy(comm_);
+        }
+        for (int b = 0; b < 2; b++) { cudaFree(f_[b]); cudaFree(gq_[b]); }
+        cudaFree(phi_); cudaFree(rho_); cudaFree(ux_); cudaFree(uy_); cudaFree(uz_); cudaFree(diag_);
+    }
+
+    size_t local_nodes() const override { return (size_t)g_.nx * g_.ny * g_.nz; }
+    int q() const override { return 19; }
+    int nsets() const override { return 2; }
+    lbm_status slab_extent(int *zb, int *nzl) const override { *zb = z_begin_; *nzl = g_.nz; return LBM_OK; }
+
+    double *field_ptr(int field)
+    {
+        switch (field) {
+        case LBM_RHO: return rho_;
+        case LBM_PHASE: return phi_ + 2 * g_.pl;
+        case LBM_UX: return ux_;
+        case LBM_UY: return uy_;
+        case LBM_UZ: return uz_;
+        }
+        return nullptr;
+    }
+    lbm_status set_field(int field, const double *host) override
+    {
+        double *d = field_ptr(field);
+        if (!d) return rt_.fail(LBM_EINVAL, "unknown field");
+        const size_t row = (size_t)g_.nx * g_.ny * sizeof(double);
+        LBM_CUDA(rt_, cudaMemcpy2DAsync(d, g_.pl * sizeof(double), host, row, row, g_.nz, cudaMemcpyHostToDevice, rt_.stream));
+        LBM_CUDA(rt_, cudaStreamSynchronize(rt_.stream));
+        return LBM_OK;
+    }
+    lbm_status get_field(int field, double *host) override
+    {
+        double *d = field_ptr(field);
+        if (!d) return rt_.fail(LBM_EINVAL, "unknown field");
+        const size_t row = (size_t)g_.nx * g_.ny * sizeof(double);
+        LBM_CUDA(rt_, cudaMemcpy2DAsync(host, row, d, g_.pl * sizeof(double), row, g_.nz, cudaMemcpyDeviceToHost, rt_.stream));
+        LBM_CUDA(rt_, cudaStreamSynchronize(rt_.stream));
+        return LBM_OK;
+    }
+
+    dim3 plane_grid(int planes) const { return dim3((unsigned)(((long long)g_.nx * g_.ny + kThreads - 1) / kThreads), planes); }
+    FieldsOut fields_out() const { return FieldsOut{rho_, ux_, uy_, uz_}; }
+
+    // ---- slab phases ----
+    lbm_status slab_init_fields() override
+    {
+        k_init_fields<<<(g_.nz + 63) / 64, 64, 0, rt_.stream>>>(g_, P_, phi_, rho_);
+        return rt_.launched("k_init_fields");
+    }
+    lbm_status slab_init_pops() override
+    {
+        const int b = 1 - cur_;
+        k_init_pops<<<plane_grid(g_.nz), kThreads, 0, rt_.stream>>>(g_, P_, phi_, rho_, ux_, uy_, uz_, f_[b], gq_[b]);
+        return rt_.launched("k_init_pops");
+    }
+    lbm_status slab_after_init() override
+    {
+        k_phase<<<plane_grid(g_.nz + 4), kThreads, 0, rt_.stream>>>(g_, P_, gq_[cur_], phi_, 0);
+        LBM_TRY(rt_.launched("k_phase"));
+        k_after_init<<<plane_grid(g_.nz), kThreads, 0, rt_.stream>>>(g_, P_, f_[cur_], fields_out());
+        return rt_.launched("k_after_init");
+    }
+    lbm_status slab_collide(int write_fields) override
+    {
+        const int a = cur_, b = 1 - cur_;
+        rt_.about_to_launch();
+        k_phase<<<plane_grid(g_.nz + 4), kThreads, 0, rt_.stream>>>(g_, P_, gq_[a], phi_, 0);
+        LBM_TRY(rt_.launched("k_phase"));
+        const dim3 grid = plane_grid(g_.nz + 2);
+        const FieldsOut o = fields_out();
+        rt_.about_to_launch();
+#define LBM_LAUNCH_COLLIDE(FXY, WR) \
+    k_collide_push<FXY, WR><<<grid, kThreads, 0, rt_.stream>>>(g_, P_, f_[a], gq_[a], phi_, f_[b], gq_[b], o, 1)
+        if (fxy_) {
+            if (write_fields) LBM_LAUNCH_COLLIDE(true, true); else LBM_LAUNCH_COLLIDE(true, false);
+        } else {
+            if (write_fields) LBM_LAUNCH_COLLIDE(false, true); else LBM_LAUNCH_COLLIDE(false, false);
+        }
+#undef LBM_LAUNCH_COLLIDE
+        return rt_.launched("k_collide_push");
+    }
+    lbm_status slab_finish() override
+    {
+        cur_ = 1 - cur_;
+        return LBM_OK;
+    }
+    // halo messages always refer to the back buffers (what collide / init_pops just wrote)
+    lbm_status slab_halo(int id, void **ptr, size_t *count) override
+    {
+        const int b = 1 - cur_;
+        const size_t pp = 19 * (size_t)g_.pl;
+        auto at = [&](double *arr, int z) { return arr + (size_t)(z + 2) * pp; };
+        const int nz = g_.nz;
+        double *p = nullptr;
+        size_t n = 0;
+        switch (id) {
+        case LBM_HALO_S_F_UP: p = at(f_[b], nz - 1); n = pp; break;
+        case LBM_HALO_S_G_UP: p = at(gq_[b], nz - 2); n = 2 * pp; break;
+        case LBM_HALO_S_F_DOWN: p = at(f_[b], 0); n = pp; break;
+        case LBM_HALO_S_G_DOWN: p = at(gq_[b], 0); n = 2 * pp; break;
+        case LBM_HALO_R_F_FROM_BELOW: p = at(f_[b], -1); n = pp; break;
+        case LBM_HALO_R_G_FROM_BELOW: p = at(gq_[b], -2); n = 2 * pp; break;
+        case LBM_HALO_R_F_FROM_ABOVE: p = at(f_[b], nz); n = pp; break;
+        case LBM_HALO_R_G_FROM_ABOVE: p = at(gq_[b], nz); n = 2 * pp; break;
+        case LBM_HALO_S_PHI_UP: p = phi_ + (size_t)(nz - 1 + 2) * g_.pl; n = g_.pl; break;
+        case LBM_HALO_S_PHI_DOWN: p = phi_ + (size_t)2 * g_.pl; n = g_.pl; break;
+        case LBM_HALO_R_PHI_FROM_BELOW: p = phi_ + (size_t)1 * g_.pl; n = g_.pl; break;
+        case LBM_HALO_R_PHI_FROM_ABOVE: p = phi_ + (size_t)(nz + 2) * g_.pl; n = g_.pl; break;
+        default: return rt_.fail(LBM_EINVAL, "unknown halo id");
+        }
+        *ptr = p;
+        *count = n;
+        return LBM_OK;
+    }
+
+    // ---- exchange: with itself (one slab, z periodic) or with the ring neighbours over NCCL ----
+    lbm_status exchange(bool phi_only)
+    {
+        static const int kState[4][2] = {{LBM_HALO_S_F_UP, LBM_HALO_R_F_FROM_BELOW}, {LBM_HALO_S_G_UP, LBM_HALO_R_G_FROM_BELOW},
+                                         {LBM_HALO_S_F_DOWN, LBM_HALO_R_F_FROM_ABOVE}, {LBM_HALO_S_G_DOWN, LBM_HALO_R_G_FROM_ABOVE}};
+        static const int kPhi[2][2] = {{LBM_HALO_S_PHI_UP, LBM_HALO_R_PHI_FROM_BELOW}, {LBM_HALO_S_PHI_DOWN, LBM_HALO_R_PHI_FROM_ABOVE}};
+        const int(*pairs)[2] = phi_only ? kPhi : kState;
+        const int npairs = phi_only ? 2 : 4;
+        if (cfg_.slab_count == 1) {
+            for (int i = 0; i < npairs; i++) {
+                void *s, *r;
+                size_t ns, nr;
+                LBM_TRY(slab_halo(pairs[i][0], &s, &ns));
+                LBM_TRY(slab_halo(pairs[i][1], &r, &nr));
+                LBM_CUDA(rt_, cudaMemcpyAsync(r, s, ns * sizeof(double), cudaMemcpyDeviceToDevice, rt_.stream));
+            }
+            return LBM_OK;
+        }
+        if (!comm_) return rt_.fail(LBM_ESTATE, "slab_count > 1: call lbm_comm_attach first, or drive lbm_slab_* yourself");
+        NcclApi *api = nccl_api(&rt_.err);
+        if (!api) return LBM_ENCCL;
+        const int up = (cfg_.slab_rank + 1) % cfg_.slab_count, down = (cfg_.slab_rank - 1 + cfg_.slab_count) % cfg_.slab_count;
+        int rc = api->GroupStart();
+        // sends in the order [up..., down...], receives [from below..., from above...]: with two
+        // slabs both neighbours are the same peer and NCCL matches a pair's messages in order
+        for (int i = 0; i < npairs && rc == 0; i++) {
+            void *s;
+            size_t ns;
+            LBM_TRY(slab_halo(pairs[i][0], &s, &ns));
+            const bool to_up = i < npairs / 2;
+            rc = api->Send(s, ns, kNcclFloat64, to_up ? up : down, comm_, rt_.stream);
+        }
+        for (int i = 0; i < npairs && rc == 0; i++) {
+            void *r;
+            size_t nr;
+            LBM_TRY(slab_halo(pairs[i][1], &r, &nr));
+            const bool from_below = i < npairs / 2;
+            rc = api->Recv(r, nr, kNcclFloat64, from_below ? down : up, comm_, rt_.stream);
+        }
+        const int rc2 = api->GroupEnd();
+        if (rc == 0) rc = rc2;
+        if (rc != 0) return rt_.fail(LBM_ENCCL, std::string("NCCL halo exchange: ") + (api->GetErrorString ? api->GetErrorString(rc) : "error"));
+        return LBM_OK;
+    }
+
+    lbm_status comm_attach(const void *id) override
+    {
+        if (cfg_.slab_count == 1) return LBM_OK;
+        NcclApi *api = nccl_api(&rt_.err);
+        if (!api) return LBM_ENCCL;
+        Id128 uid;
+        memcpy(&uid, id, sizeof uid);
+        const int rc = api->CommInitRank(&comm_, cfg_.slab_count, uid, cfg_.slab_rank);
+        if (rc != 0) {
+            comm_ = nullptr;
+            return rt_.fail(LBM_ENCCL, std::string("ncclCommInitRank: ") + (api->GetErrorString ? api->GetErrorString(rc) : "error"));
+        }
+        return LBM_OK;
+    }
+
+    lbm_status init() override
+    {
+        LBM_TRY(slab_init_fields());
+        LBM_TRY(exchange(true));
+        LBM_TRY(slab_init_pops());
+        LBM_TRY(exchange(false));
+        LBM_TRY(slab_finish());
+        return slab_after_init();
+    }
+    lbm_status step(int nsteps) override
+    {
+        for (int t = 0; t < nsteps; t++) {
+            LBM_TRY(slab_collide(t == nsteps - 1));
+            LBM_TRY(exchange(false));
+            LBM_TRY(slab_finish());
+        }
+        return LBM_OK;
+    }
+
+    lbm_status set_populations(int set, const double *host) override
+    {
+        const size_t n = local_nodes() * 19;
+        double *stage = nullptr;
+        LBM_CUDA(rt_, cudaMalloc(&stage, n * sizeof(double)));
+        lbm_status st = rt_.cuda(cudaMemcpyAsync(stage, host, n * sizeof(double), cudaMemcpyHostToDevice, rt_.stream), "H2D populations");
+        if (st == LBM_OK) {
+            double *dst = set == 0 ? f_[cur_] : gq_[cur_];
+            k_scatter_aos<<<plane_grid(g_.nz), kThreads, 0, rt_.stream>>>(g_, stage, dst);
+            st = rt_.launched("k_scatter_aos");
+        }
+        if (st == LBM_OK) st = rt_.cuda(cudaStreamSynchronize(rt_.stream), "sync");
+        cudaFree(stage);
+        LBM_TRY(st);
+        // refresh the ghost planes of the front buffers: slab_halo() addresses the back buffers, so
+        // flip, exchange, flip back
+        cur_ = 1 - cur_;
+        st = exchange(false);
+        cur_ = 1 - cur_;
+        return st;
+    }
+    lbm_status get_populations(int set, double *host) override
+    {
+        const size_t n = local_nodes() * 19;
+        double *stage = nullptr;
+        LBM_CUDA(rt_, cudaMalloc(&stage, n * sizeof(double)));
+        k_gather_aos<<<plane_grid(g_.nz), kThreads, 0, rt_.stream>>>(g_, set == 0 ? f_[cur_] : gq_[cur_], stage);
+        lbm_status st = rt_.launched("k_gather_aos");
+        if (st == LBM_OK) st = rt_.cuda(cudaMemcpyAsync(host, stage, n * sizeof(double), cudaMemcpyDeviceToHost, rt_.stream), "D2H populations");
+        if (st == LBM_OK) st = rt_.cuda(cudaStreamSynchronize(rt_.stream), "sync");
+        cudaFree(stage);
+        return st;
+    }
+
+    lbm_status diagnostics(double *mass, double *mom, double *phase_mass, int *has_nan) override
+    {
+        DiagLayout L;
+        const size_t pp = 19 * (size_t)g_.pl;
+        L.f = f_[cur_] + 2 * pp;
+        L.g = gq_[cur_] + 2 * pp;
+        L.stride_k = g_.pl;
+        L.plane_stride = (long long)pp;
+        L.planes = g_.nz; L.nx = g_.nx; L.ny = g_.ny; L.q = 19; L.skip_border = 1; L.node_major_x = 1;
+        double out[6];
+        LBM_TRY(run_diagnostics(rt_, L, diag_, diagnostics_scratch_blocks(), out));
+        if (mass) *mass = out[0];
+        if (mom) { mom[0] = out[1]; mom[1] = out[2]; mom[2] = out[3]; }
+        if (phase_mass) *phase_mass = out[4];
+        if (has_nan) *has_nan = out[5] != 0.0;
+        return LBM_OK;
+    }
+
+private:
+    Runtime &rt_;
+    lbm_config cfg_;
+    Geom g_{};
+    Params P_{};
+    bool fxy_ = false;
+    int z_begin_ = 0, cur_ = 0;
+    double *f_[2] = {nullptr, nullptr}, *gq_[2] = {nullptr, nullptr};
+    double *phi_ = nullptr, *rho_ = nullptr, *ux_ = nullptr, *uy_ = nullptr, *uz_ = nullptr, *diag_ = nullptr;
+    void *comm_ = nullptr;
+};
+
+}  // namespace
+
+Model *make_d3q19_binary(Runtime &rt, const lbm_config &cfg, lbm_status *st)
+{
+    Slab3D *m = new Slab3D(rt, cfg);
+    *st = m->setup();
+    if (*st != LBM_OK) {
+        delete m;
+        return nullptr;
+    }
+    return m;
+}
+
+// used by lbm_comm_unique_id (lbm_api.cu)
+lbm_status nccl_unique_id(void *out, std::string *why)
+{
+    NcclApi *api = nccl_api(why);
+    if (!api) return LBM_ENCCL;
+    const int rc = api->GetUniqueId(out);
+    if (rc != 0) {
+        if (why) *why = "ncclGetUniqueId failed";
+        return LBM_ENCCL;
+    }
+    return LBM_OK;
+}
+
+}  // namespace lbm

@@ -1,0 +1,279 @@
+// d3q19_threads.h -- what ONE thread of each plain D3Q19 kernel does.
+//
+// The __global__ wrappers in d3q19_binary.cu only turn (blockIdx, threadIdx)
+// into (storage plane, in-plane index) and call these functions; the CPU unit
+// test (tests/emu/) calls the same functions from loops.  Everything here is
+// plain C++ for that reason.
+//
+// Storage (this repo's layout, not the reference's AoS):
+//   populations  [plane zs][direction k][in-plane index], plane pitch PL doubles,
+//                in-plane index = iY*NX+iX, zs = z+2 for z in [-2, nz+1]
+//   phase field  [plane zs][in-plane index]   (extended: bulk, mirror, wall nodes)
+//   out fields   [z][in-plane index], z in [0, nz)
+// A population array holds the STREAMED populations, i.e. exactly what the
+// reference's f/g hold at the start of a step (lattice.h:35-38), for bulk nodes
+// 1<=iX<=NX-2, 1<=iY<=NY-2.  Mirror nodes (iX=0 or iY=0) and wall nodes
+// (iX=NX-1 or iY=NY-1) are not stored: the reference's mirror nodes are permuted
+// copies of their inner neighbour (lattice.hpp:645-686) and its wall-node
+// populations are never read.
+#ifndef LBM_D3Q19_THREADS_H
+#define LBM_D3Q19_THREADS_H
+
+#include "d3q19_node.h"
+
+namespace lbm3 {
+
+struct Geom {
+    int nx, ny, nz;        // local slab: nz owned planes
+    long long pl;          // plane pitch in doubles (>= nx*ny, multiple of 16)
+};
+
+LBM_HD long long pop_index(const Geom &g, int zs, int k, long long idx) { return ((long long)zs * 19 + k) * g.pl + idx; }
+
+// ---- phase field of one storage plane from its g populations -------------
+// Reference: lattice.hpp:19-22 (bulk sum), :645-686 + :19-22 (mirror nodes sum
+// the permuted copy), :75-106 (wall nodes: inner neighbour - phase_gradient).
+// The thread of bulk node (ix,iy) also writes the mirror/wall nodes whose inner
+// neighbour it is, so no second pass is needed.
+LBM_HD void phase_thread(const Geom &g, const Params &P, const double *gpop, double *phi, int zs, int ix, int iy)
+{
+    const int NX = g.nx, NY = g.ny;
+    if (ix < 1 || ix > NX - 2 || iy < 1 || iy > NY - 2) return;
+    const long long idx = (long long)iy * NX + ix;
+    double G[19];
+#pragma unroll
+    for (int k = 0; k < 19; k++) G[k] = gpop[pop_index(g, zs, k, idx)];
+    double *ph = phi + (long long)zs * g.pl;
+    const double own = sum19(G);
+    ph[idx] = own;
+    const bool xlo = ix == 1, ylo = iy == 1, xhi = ix == NX - 2, yhi = iy == NY - 2;
+    if (yhi) ph[idx + NX] = own - P.phase_gradient;
+    if (xhi) ph[idx + 1] = own - P.phase_gradient;
+    if (xhi && yhi) ph[idx + NX + 1] = own - P.phase_gradient;
+    if (ylo) {
+        const double m = sum19_mirror<2>(G);
+        ph[idx - NX] = m;
+        if (xhi) ph[idx - NX + 1] = m - P.phase_gradient;
+    }
+    if (xlo) {
+        const double m = sum19_mirror<1>(G);
+        ph[idx - 1] = m;
+        if (yhi) ph[idx + NX - 1] = m - P.phase_gradient;
+    }
+    if (xlo && ylo) ph[idx - NX - 1] = sum19_mirror<3>(G);
+}
+
+// ---- push of one post-collision population -------------------------------
+// Reference: lattice.hpp:491-499 (push), :503-585 (mirror nodes copy the inner
+// node's post-collision populations permuted and push them), :588-643 (half-way
+// bounce-back).  Folded: a population heading into a wall returns to its own
+// node reversed; one heading into a mirror line is reflected (the mirrored
+// velocity component flips, the node coordinate stays on the inner line).
+LBM_HD void push_border(const Geom &g, double *fout, double *gout, int zs, int ix, int iy, int k, double fv, double gv)
+{
+    const int CX[19] = LBM3_CX, CY[19] = LBM3_CY, CZ[19] = LBM3_CZ;
+    const int OPP[19] = {0, 2, 1, 4, 3, 6, 5, 10, 9, 8, 7, 14, 13, 12, 11, 18, 17, 16, 15};
+    const int SYMX[19] = {0, 2, 1, 3, 4, 5, 6, 8, 7, 10, 9, 11, 12, 13, 14, 16, 15, 18, 17};
+    const int SYMY[19] = {0, 1, 2, 4, 3, 5, 6, 9, 10, 7, 8, 12, 11, 14, 13, 15, 16, 17, 18};
+    int px = ix + CX[k], py = iy + CY[k], pz = zs + CZ[k], kk = k;
+    if (px == g.nx - 1 || py == g.ny - 1) {
+        px = ix; py = iy; pz = zs; kk = OPP[k];
+    } else {
+        if (px == 0) { px = 1; kk = SYMX[kk]; }
+        if (py == 0) { py = 1; kk = SYMY[kk]; }
+    }
+    const long long t = pop_index(g, pz, kk, (long long)py * g.nx + px);
+    fout[t] = fv;
+    gout[t] = gv;
+}
+
+struct FieldsOut {
+    double *rho, *ux, *uy, *uz;   // [z][in-plane], may be null when WRITE is false
+};
+
+// mirror-node moments for the output fields: updateMacro (lattice.hpp:15-38) on
+// the permuted populations, then the force shift of lattice.hpp:512-514 etc.
+template <int MODE>
+LBM_HD void mirror_fields(const double *F, const Params &P, const FieldsOut &o, long long at)
+{
+    const int SYM[3][19] = {{0, 2, 1, 3, 4, 5, 6, 8, 7, 10, 9, 11, 12, 13, 14, 16, 15, 18, 17},
+                            {0, 1, 2, 4, 3, 5, 6, 9, 10, 7, 8, 12, 11, 14, 13, 15, 16, 17, 18},
+                            {0, 2, 1, 4, 3, 5, 6, 10, 9, 8, 7, 12, 11, 14, 13, 16, 15, 18, 17}};
+    double Pm[19];
+#pragma unroll
+    for (int k = 0; k < 19; k++) Pm[k] = F[SYM[MODE - 1][k]];
+    double d, ux, uy, uz;
+    moments(Pm, d, ux, uy, uz);
+    o.rho[at] = d;
+    o.ux[at] = ux + P.fx / (2 * d);
+    o.uy[at] = uy + P.fy / (2 * d);
+    o.uz[at] = uz + P.fz / (2 * d);
+}
+
+// ---- one bulk node: moments, stencils, collision, push -------------------
+// Reference: Lattice::updateMacro + Lattice::collide_stream (lattice.hpp:4-108,
+// 377-688) for this node.  `phi` must already hold the extended phase field of
+// planes zs-1..zs+1.
+template <bool FXY, bool WRITE>
+LBM_HD void collide_push_thread(const Geom &g, const Params &P, const double *fin, const double *gin,
+                                const double *phi, double *fout, double *gout, const FieldsOut &o, int zs, int ix, int iy)
+{
+    const int NX = g.nx, NY = g.ny;
+    if (ix < 1 || ix > NX - 2 || iy < 1 || iy > NY - 2) {
+        if (WRITE && zs >= 2 && zs < g.nz + 2 && ix < NX && iy < NY && (ix == NX - 1 || iy == NY - 1)) {
+            // wall node fields, lattice.hpp:75-106 (phase is taken from the extended field by the caller)
+            const long long at = (long long)(zs - 2) * g.pl + (long long)iy * NX + ix;
+            o.rho[at] = P.rho_wall; o.ux[at] = 0.0; o.uy[at] = 0.0; o.uz[at] = 0.0;
+        }
+        return;
+    }
+    const long long idx = (long long)iy * NX + ix;
+    double F[19], G[19], PH[19];
+#pragma unroll
+    for (int k = 0; k < 19; k++) {
+        F[k] = fin[pop_index(g, zs, k, idx)];
+        G[k] = gin[pop_index(g, zs, k, idx)];
+    }
+    {
+        const int CX[19] = LBM3_CX, CY[19] = LBM3_CY, CZ[19] = LBM3_CZ;
+#pragma unroll
+        for (int k = 0; k < 19; k++) PH[k] = phi[(long long)(zs + CZ[k]) * g.pl + idx + CY[k] * NX + CX[k]];
+    }
+    double gx, gy, gz, lap;
+    stencils(PH, gx, gy, gz, lap);
+
+    const bool own = zs >= 2 && zs < g.nz + 2;
+    if (WRITE && own) {
+        if (iy == 1) mirror_fields<2>(F, P, o, (long long)(zs - 2) * g.pl + ix);
+        if (ix == 1) mirror_fields<1>(F, P, o, (long long)(zs - 2) * g.pl + (long long)iy * NX);
+        if (ix == 1 && iy == 1) mirror_fields<3>(F, P, o, (long long)(zs - 2) * g.pl);
+    }
+
+    double rho, ux, uy, uz;
+    collide<FXY>(F, G, PH[0], gx, gy, gz, lap, P, rho, ux, uy, uz);
+
+    if (WRITE && own) {
+        const long long at = (long long)(zs - 2) * g.pl + idx;
+        o.rho[at] = rho; o.ux[at] = ux; o.uy[at] = uy; o.uz[at] = uz;
+    }
+
+    const bool border = ix == 1 || iy == 1 || ix == NX - 2 || iy == NY - 2;
+    if (!border) {
+        const int CX[19] = LBM3_CX, CY[19] = LBM3_CY, CZ[19] = LBM3_CZ;
+#pragma unroll
+        for (int k = 0; k < 19; k++) {
+            const long long t = pop_index(g, zs + CZ[k], k, idx + CY[k] * NX + CX[k]);
+            fout[t] = F[k];
+            gout[t] = G[k];
+        }
+    } else {
+        for (int k = 0; k < 19; k++) push_border(g, fout, gout, zs, ix, iy, k, F[k], G[k]);
+    }
+}
+
+// ---- initialisation -------------------------------------------------------
+// updateSymmetric + updateWall on the user's fields, one plane per call site
+// thread-row; reference lattice.hpp:705-760 including the loops that stop one
+// node short.  Sequential dependencies (a wall node reads
+// a mirror node) are resolved by doing the work of one z plane in one thread.
+LBM_HD void init_fields_plane(const Geom &g, const Params &P, double *phi, double *rho, int z)
+{
+    const int NX = g.nx, NY = g.ny;
+    double *ph = phi + (long long)(z + 2) * g.pl;
+    double *rh = rho + (long long)z * g.pl;
+    for (int ix = 1; ix < NX - 2; ix++) { ph[ix] = ph[NX + ix]; rh[ix] = rh[NX + ix]; }
+    for (int iy = 1; iy < NY - 2; iy++) { ph[(long long)iy * NX] = ph[(long long)iy * NX + 1]; rh[(long long)iy * NX] = rh[(long long)iy * NX + 1]; }
+    ph[0] = ph[NX + 1];
+    rh[0] = rh[NX + 1];
+    for (int ix = 0; ix < NX; ix++) rh[(long long)(NY - 1) * NX + ix] = P.rho_wall;
+    for (int iy = 0; iy < NY; iy++) rh[(long long)iy * NX + NX - 1] = P.rho_wall;
+    for (int ix = 0; ix < NX - 2; ix++) ph[(long long)(NY - 1) * NX + ix] = ph[(long long)(NY - 2) * NX + ix] - P.phase_gradient;
+    for (int iy = 0; iy < NY - 2; iy++) ph[(long long)iy * NX + NX - 1] = ph[(long long)iy * NX + NX - 2] - P.phase_gradient;
+    ph[(long long)(NY - 1) * NX + NX - 1] = ph[(long long)(NY - 2) * NX + NX - 2] - P.phase_gradient;
+}
+
+// Lattice::init for one bulk node (lattice.hpp:216-276); fields [z][in-plane]
+LBM_HD void init_pops_thread(const Geom &g, const Params &P, const double *phi, const double *rho, const double *ux,
+                             const double *uy, const double *uz, double *fout, double *gout, int z, int ix, int iy)
+{
+    const int NX = g.nx, NY = g.ny;
+    if (ix < 1 || ix > NX - 2 || iy < 1 || iy > NY - 2) return;
+    const int zs = z + 2;
+    const long long idx = (long long)iy * NX + ix, at = (long long)z * g.pl + idx;
+    const int CX[19] = LBM3_CX, CY[19] = LBM3_CY, CZ[19] = LBM3_CZ;
+    double PH[19], F[19], G[19];
+    for (int k = 0; k < 19; k++) PH[k] = phi[(long long)(zs + CZ[k]) * g.pl + idx + CY[k] * NX + CX[k]];
+    double gx, gy, gz, lap;
+    stencils(PH, gx, gy, gz, lap);
+    init_equilibrium(rho[at], PH[0], ux[at], uy[at], uz[at], gx, gy, gz, lap, P, F, G);
+    for (int k = 0; k < 19; k++) {
+        fout[pop_index(g, zs, k, idx)] = F[k];
+        gout[pop_index(g, zs, k, idx)] = G[k];
+    }
+}
+
+// updateMacro right after init (solver.hpp:877): moments without the force shift
+LBM_HD void after_init_thread(const Geom &g, const Params &P, const double *fin, const FieldsOut &o, int z, int ix, int iy)
+{
+    const int NX = g.nx, NY = g.ny;
+    if (ix >= NX || iy >= NY) return;
+    const long long base = (long long)z * g.pl;
+    if (ix == NX - 1 || iy == NY - 1) {
+        const long long at = base + (long long)iy * NX + ix;
+        o.rho[at] = P.rho_wall; o.ux[at] = 0.0; o.uy[at] = 0.0; o.uz[at] = 0.0;
+        return;
+    }
+    if (ix < 1 || iy < 1) return;
+    const long long idx = (long long)iy * NX + ix;
+    double F[19];
+    for (int k = 0; k < 19; k++) F[k] = fin[pop_index(g, z + 2, k, idx)];
+    double d, ux, uy, uz;
+    moments(F, d, ux, uy, uz);
+    o.rho[base + idx] = d; o.ux[base + idx] = ux; o.uy[base + idx] = uy; o.uz[base + idx] = uz;
+    const int SYM[3][19] = {{0, 2, 1, 3, 4, 5, 6, 8, 7, 10, 9, 11, 12, 13, 14, 16, 15, 18, 17},
+                            {0, 1, 2, 4, 3, 5, 6, 9, 10, 7, 8, 12, 11, 14, 13, 15, 16, 17, 18},
+                            {0, 2, 1, 4, 3, 5, 6, 10, 9, 8, 7, 12, 11, 14, 13, 16, 15, 18, 17}};
+    for (int m = 0; m < 3; m++) {
+        long long at;
+        if (m == 0) { if (ix != 1) continue; at = base + (long long)iy * NX; }
+        else if (m == 1) { if (iy != 1) continue; at = base + ix; }
+        else { if (ix != 1 || iy != 1) continue; at = base; }
+        double Pm[19];
+        for (int k = 0; k < 19; k++) Pm[k] = F[SYM[m][k]];
+        moments(Pm, d, ux, uy, uz);
+        o.rho[at] = d; o.ux[at] = ux; o.uy[at] = uy; o.uz[at] = uz;
+    }
+}
+
+// populations in the reference's AoS order for one node of plane z (any node):
+// mirror nodes get the permuted copy, wall nodes zero
+LBM_HD void gather_aos_thread(const Geom &g, const double *pop, double *aos, int z, int ix, int iy)
+{
+    const int NX = g.nx, NY = g.ny;
+    if (ix >= NX || iy >= NY) return;
+    double *out = aos + (((long long)z * NY + iy) * NX + ix) * 19;
+    if (ix == NX - 1 || iy == NY - 1) {
+        for (int k = 0; k < 19; k++) out[k] = 0.0;
+        return;
+    }
+    const int SYM[4][19] = {{0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15, 16, 17, 18},
+                            {0, 2, 1, 3, 4, 5, 6, 8, 7, 10, 9, 11, 12, 13, 14, 16, 15, 18, 17},
+                            {0, 1, 2, 4, 3, 5, 6, 9, 10, 7, 8, 12, 11, 14, 13, 15, 16, 17, 18},
+                            {0, 2, 1, 4, 3, 5, 6, 10, 9, 8, 7, 12, 11, 14, 13, 16, 15, 18, 17}};
+    const int m = (ix == 0 ? 1 : 0) + (iy == 0 ? 2 : 0);
+    const int sx = ix == 0 ? 1 : ix, sy = iy == 0 ? 1 : iy;
+    const long long idx = (long long)sy * NX + sx;
+    for (int k = 0; k < 19; k++) out[k] = pop[pop_index(g, z + 2, SYM[m][k], idx)];
+}
+
+LBM_HD void scatter_aos_thread(const Geom &g, const double *aos, double *pop, int z, int ix, int iy)
+{
+    const int NX = g.nx, NY = g.ny;
+    if (ix < 1 || ix > NX - 2 || iy < 1 || iy > NY - 2) return;
+    const double *in = aos + (((long long)z * NY + iy) * NX + ix) * 19;
+    const long long idx = (long long)iy * NX + ix;
+    for (int k = 0; k < 19; k++) pop[pop_index(g, z + 2, k, idx)] = in[k];
+}
+
+}  // namespace lbm3
+#endif

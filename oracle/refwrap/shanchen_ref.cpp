@@ -88,7 +88,9 @@ int ref_shanchen_run(int last_step, const char *outdir, double *rho_out, double 
     if (!getcwd(cwd, sizeof cwd)) return -1;
     if (outdir && chdir(outdir) != 0) return -2;
     lbmref::step = 0;
-    lbmref::stop_after = last_step;
+    // the hook fires before the step's file output (shanchen.cpp:190-207); let the final step run to the
+    // program's own end so that its .dat files are written too
+    lbmref::stop_after = last_step >= nsteps ? -1 : last_step;
     lbmref::snap_step = last_step;
     lbmref::snap_rho = rho_out; lbmref::snap_u1 = u1_out; lbmref::snap_u2 = u2_out; lbmref::snap_f = f_out;
     std::streambuf *old = std::cout.rdbuf();

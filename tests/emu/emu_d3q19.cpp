@@ -1,0 +1,136 @@
+// CPU emulation of the plain D3Q19 CUDA kernels: runs the per-thread functions of
+// latticeboltzmannmethod_b200/csrc/d3q19_threads.h from host loops, with the same
+// storage layout and the same call order as the CUDA library.  TEST INFRASTRUCTURE
+// (lets the kernel logic be checked against the oracle without a GPU); never part
+// of the product library.  Build: g++ -O2 -ffp-contract=off (tests/emu/build.sh).
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+#include "d3q19_threads.h"
+
+using namespace lbm3;
+
+struct Emu {
+    Geom g;
+    Params P;
+    bool fxy;
+    std::vector<double> f[2], gq[2], phi, rho, ux, uy, uz;
+    int cur = 0;
+};
+
+extern "C" {
+Emu *emu3_create(int nx, int ny, int nz, const double *p)
+{
+    Emu *e = new Emu;
+    e->g.nx = nx; e->g.ny = ny; e->g.nz = nz;
+    e->g.pl = ((long long)nx * ny + 15) / 16 * 16;
+    e->P.aconst = p[0]; e->P.kconst = p[1]; e->P.gammaconst = p[2]; e->P.phase_gradient = p[3];
+    e->P.rho_wall = p[5]; e->P.omega_phi = 1.0 / p[6]; e->P.tau_gas = p[8]; e->P.dtau = p[7] - p[8];
+    e->P.fx = p[9]; e->P.fy = p[10]; e->P.fz = p[11];
+    e->fxy = p[9] != 0.0 || p[10] != 0.0;
+    size_t npop = (size_t)(nz + 4) * 19 * e->g.pl;
+    for (int i = 0; i < 2; i++) { e->f[i].assign(npop, 0.0); e->gq[i].assign(npop, 0.0); }
+    e->phi.assign((size_t)(nz + 4) * e->g.pl, 0.0);
+    size_t nf = (size_t)nz * e->g.pl;
+    e->rho.assign(nf, 0.0); e->ux.assign(nf, 0.0); e->uy.assign(nf, 0.0); e->uz.assign(nf, 0.0);
+    return e;
+}
+void emu3_destroy(Emu *e) { delete e; }
+
+static void put(Emu *e, double *dst, const double *src)
+{
+    size_t n = (size_t)e->g.nx * e->g.ny;
+    for (int z = 0; z < e->g.nz; z++) memcpy(dst + (size_t)z * e->g.pl, src + (size_t)z * n, n * sizeof(double));
+}
+static void get(Emu *e, double *dst, const double *src)
+{
+    size_t n = (size_t)e->g.nx * e->g.ny;
+    for (int z = 0; z < e->g.nz; z++) memcpy(dst + (size_t)z * n, src + (size_t)z * e->g.pl, n * sizeof(double));
+}
+void emu3_set_fields(Emu *e, const double *rho, const double *phase, const double *ux, const double *uy, const double *uz)
+{
+    put(e, e->rho.data(), rho); put(e, e->phi.data() + 2 * e->g.pl, phase);
+    put(e, e->ux.data(), ux); put(e, e->uy.data(), uy); put(e, e->uz.data(), uz);
+}
+void emu3_get_fields(Emu *e, double *rho, double *phase, double *ux, double *uy, double *uz)
+{
+    get(e, rho, e->rho.data()); get(e, phase, e->phi.data() + 2 * e->g.pl);
+    get(e, ux, e->ux.data()); get(e, uy, e->uy.data()); get(e, uz, e->uz.data());
+}
+static void self_exchange(Emu *e, int b)
+{
+    const size_t pp = 19 * (size_t)e->g.pl;
+    const int nz = e->g.nz;
+    double *f = e->f[b].data(), *g = e->gq[b].data();
+    memcpy(f + (size_t)(-1 + 2) * pp, f + (size_t)(nz - 1 + 2) * pp, pp * sizeof(double));
+    memcpy(g + (size_t)(-2 + 2) * pp, g + (size_t)(nz - 2 + 2) * pp, 2 * pp * sizeof(double));
+    memcpy(f + (size_t)(nz + 2) * pp, f + (size_t)(0 + 2) * pp, pp * sizeof(double));
+    memcpy(g + (size_t)(nz + 2) * pp, g + (size_t)(0 + 2) * pp, 2 * pp * sizeof(double));
+}
+void emu3_init(Emu *e)
+{
+    const Geom &g = e->g;
+    for (int z = 0; z < g.nz; z++) init_fields_plane(g, e->P, e->phi.data(), e->rho.data(), z);
+    memcpy(e->phi.data() + 1 * g.pl, e->phi.data() + (size_t)(g.nz - 1 + 2) * g.pl, g.pl * sizeof(double));
+    memcpy(e->phi.data() + (size_t)(g.nz + 2) * g.pl, e->phi.data() + 2 * g.pl, g.pl * sizeof(double));
+    int b = 1 - e->cur;
+    for (int z = 0; z < g.nz; z++)
+        for (int iy = 0; iy < g.ny; iy++)
+            for (int ix = 0; ix < g.nx; ix++)
+                init_pops_thread(g, e->P, e->phi.data(), e->rho.data(), e->ux.data(), e->uy.data(), e->uz.data(),
+                                 e->f[b].data(), e->gq[b].data(), z, ix, iy);
+    self_exchange(e, b);
+    e->cur = b;
+    FieldsOut o{e->rho.data(), e->ux.data(), e->uy.data(), e->uz.data()};
+    for (int zs = 0; zs < g.nz + 4; zs++)
+        for (int iy = 0; iy < g.ny; iy++)
+            for (int ix = 0; ix < g.nx; ix++) phase_thread(g, e->P, e->gq[e->cur].data(), e->phi.data(), zs, ix, iy);
+    for (int z = 0; z < g.nz; z++)
+        for (int iy = 0; iy < g.ny; iy++)
+            for (int ix = 0; ix < g.nx; ix++) after_init_thread(g, e->P, e->f[e->cur].data(), o, z, ix, iy);
+}
+void emu3_step(Emu *e, int n)
+{
+    const Geom &g = e->g;
+    FieldsOut o{e->rho.data(), e->ux.data(), e->uy.data(), e->uz.data()};
+    for (int t = 0; t < n; t++) {
+        const int a = e->cur, b = 1 - a;
+        const bool w = t == n - 1;
+        for (int zs = 0; zs < g.nz + 4; zs++)
+            for (int iy = 0; iy < g.ny; iy++)
+                for (int ix = 0; ix < g.nx; ix++) phase_thread(g, e->P, e->gq[a].data(), e->phi.data(), zs, ix, iy);
+        for (int zs = 1; zs <= g.nz + 2; zs++)
+            for (int iy = 0; iy < g.ny; iy++)
+                for (int ix = 0; ix < g.nx; ix++) {
+                    if (e->fxy) {
+                        if (w) collide_push_thread<true, true>(g, e->P, e->f[a].data(), e->gq[a].data(), e->phi.data(), e->f[b].data(), e->gq[b].data(), o, zs, ix, iy);
+                        else collide_push_thread<true, false>(g, e->P, e->f[a].data(), e->gq[a].data(), e->phi.data(), e->f[b].data(), e->gq[b].data(), o, zs, ix, iy);
+                    } else {
+                        if (w) collide_push_thread<false, true>(g, e->P, e->f[a].data(), e->gq[a].data(), e->phi.data(), e->f[b].data(), e->gq[b].data(), o, zs, ix, iy);
+                        else collide_push_thread<false, false>(g, e->P, e->f[a].data(), e->gq[a].data(), e->phi.data(), e->f[b].data(), e->gq[b].data(), o, zs, ix, iy);
+                    }
+                }
+        self_exchange(e, b);
+        e->cur = b;
+    }
+}
+void emu3_get_pops(Emu *e, double *f, double *g)
+{
+    for (int z = 0; z < e->g.nz; z++)
+        for (int iy = 0; iy < e->g.ny; iy++)
+            for (int ix = 0; ix < e->g.nx; ix++) {
+                gather_aos_thread(e->g, e->f[e->cur].data(), f, z, ix, iy);
+                gather_aos_thread(e->g, e->gq[e->cur].data(), g, z, ix, iy);
+            }
+}
+void emu3_set_pops(Emu *e, const double *f, const double *g)
+{
+    for (int z = 0; z < e->g.nz; z++)
+        for (int iy = 0; iy < e->g.ny; iy++)
+            for (int ix = 0; ix < e->g.nx; ix++) {
+                scatter_aos_thread(e->g, f, e->f[e->cur].data(), z, ix, iy);
+                scatter_aos_thread(e->g, g, e->gq[e->cur].data(), z, ix, iy);
+            }
+    self_exchange(e, e->cur);
+}
+}
