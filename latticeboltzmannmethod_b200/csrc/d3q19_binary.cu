@@ -4,9 +4,11 @@
 // lattice.hpp) and the per-step part of Solver<D> (solver.hpp:821-928).
 // Per-thread arithmetic: d3q19_threads.h / d3q19_node.h.
 #include <dlfcn.h>
+#include <algorithm>
 #include <cstring>
 #include <vector>
 
+#include "d3q19_fused.cuh"
 #include "d3q19_threads.h"
 #include "lbm_internal.h"
 
@@ -35,6 +37,83 @@ __global__ void __launch_bounds__(kThreads) k_collide_push(Geom g, Params P, con
     if (idx >= (long long)g.nx * g.ny) return;
     lbm3::collide_push_thread<FXY, WRITE>(g, P, fin, gin, phi, fout, gout, o, zs0 + blockIdx.y, (int)(idx % g.nx),
                                           (int)(idx / g.nx));
+}
+
+template <bool FXY, bool WRITE, int MINB>
+__global__ void __launch_bounds__(128, MINB) k_collide_push_occ(Geom g, Params P, const double *fin, const double *gin,
+                                                                const double *phi, double *fout, double *gout, FieldsOut o,
+                                                                int zs0)
+{
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (long long)g.nx * g.ny) return;
+    lbm3::collide_push_thread<FXY, WRITE>(g, P, fin, gin, phi, fout, gout, o, zs0 + blockIdx.y, (int)(idx % g.nx),
+                                          (int)(idx / g.nx));
+}
+
+// Plain collide-push through collide_streamed(): fewer live registers, more resident warps.
+template <bool FXY, bool WRITE, int MINB>
+__global__ void __launch_bounds__(128, MINB) k_collide_streamed(Geom g, Params P, const double *__restrict__ fin,
+                                                                const double *__restrict__ gin, const double *__restrict__ phi,
+                                                                double *__restrict__ fout, double *__restrict__ gout, FieldsOut o,
+                                                                int zs0)
+{
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (long long)g.nx * g.ny) return;
+    lbm3::collide_push_thread_streamed<FXY, WRITE>(g, P, fin, gin, phi, fout, gout, o, zs0 + blockIdx.y, (int)(idx % g.nx),
+                                                   (int)(idx / g.nx));
+}
+
+// Plain collide-push with the f and the g populations of a node on two different threads: a block
+// of 256 threads updates 128 nodes, warps 0-3 hold f, warps 4-7 hold g (d3q19_threads.h, "split").
+template <bool FXY, bool WRITE, int MINB>
+__global__ void __launch_bounds__(256, MINB) k_collide_split(Geom g, Params P, const double *__restrict__ fin,
+                                                             const double *__restrict__ gin, const double *__restrict__ phi,
+                                                             double *__restrict__ fout, double *__restrict__ gout, FieldsOut o,
+                                                             int zs0)
+{
+    __shared__ double xch[8][128];
+    const int ln = threadIdx.x & 127;
+    const bool is_g = threadIdx.x >= 128;
+    const long long idx = (long long)blockIdx.x * 128 + ln;
+    const int zs = zs0 + blockIdx.y;
+    const int NX = g.nx, NY = g.ny;
+    const bool in_dom = idx < (long long)NX * NY;
+    const int ix = (int)(idx % NX), iy = (int)(idx / NX);
+    const bool bulk = in_dom && ix >= 1 && ix <= NX - 2 && iy >= 1 && iy <= NY - 2;
+    double V[19];
+    double rho = 0, ux = 0, uy = 0, uz = 0;
+    if (bulk) {
+        if (!is_g) {
+            const double *src = fin + lbm3::pop_index(g, zs, 0, idx);
+#pragma unroll
+            for (int k = 0; k < 19; k++) V[k] = __ldg(src + (long long)k * g.pl);
+            lbm3::moments_shifted<FXY>(V, P, rho, ux, uy, uz);
+            xch[0][ln] = ux; xch[1][ln] = uy; xch[2][ln] = uz;
+        } else {
+            const double *src = gin + lbm3::pop_index(g, zs, 0, idx);
+            double PH[19];
+            constexpr int CX[19] = LBM3_CX, CY[19] = LBM3_CY, CZ[19] = LBM3_CZ;
+#pragma unroll
+            for (int k = 0; k < 19; k++) {
+                V[k] = __ldg(src + (long long)k * g.pl);
+                PH[k] = __ldg(phi + (long long)(zs + CZ[k]) * g.pl + idx + CY[k] * NX + CX[k]);
+            }
+            double gx, gy, gz, lap;
+            lbm3::stencils(PH, gx, gy, gz, lap);
+            xch[3][ln] = PH[0]; xch[4][ln] = gx; xch[5][ln] = gy; xch[6][ln] = gz; xch[7][ln] = lap;
+        }
+    }
+    __syncthreads();
+    if (bulk) {
+        if (!is_g)
+            lbm3::f_thread_finish<FXY, WRITE>(g, P, V, xch[3][ln], xch[4][ln], xch[5][ln], xch[6][ln], xch[7][ln], rho, ux, uy, uz,
+                                              fout, o, zs, ix, iy);
+        else
+            lbm3::g_thread_finish(g, P, V, xch[3][ln], xch[7][ln], xch[0][ln], xch[1][ln], xch[2][ln], gout, zs, ix, iy);
+    } else if (WRITE && !is_g && in_dom && zs >= 2 && zs < g.nz + 2 && (ix == NX - 1 || iy == NY - 1)) {
+        const long long at = (long long)(zs - 2) * g.pl + idx;
+        o.rho[at] = P.rho_wall; o.ux[at] = 0.0; o.uy[at] = 0.0; o.uz[at] = 0.0;
+    }
 }
 
 __global__ void k_init_fields(Geom g, Params P, double *phi, double *rho)
@@ -231,8 +310,81 @@ public:
         k_after_init<<<plane_grid(g_.nz), kThreads, 0, rt_.stream>>>(g_, P_, f_[cur_], fields_out());
         return rt_.launched("k_after_init");
     }
+    // kernel_variant 0: the whole step as one kernel (d3q19_fused.cuh)
+    template <int TY>
+    lbm_status launch_fused(int write_fields)
+    {
+        using S = lbm3::FusedSmem<TY>;
+        const int a = cur_, b = 1 - cur_;
+        const int planes = g_.nz + 2;
+        const int gx = (g_.nx + lbm3::FT_TX - 1) / lbm3::FT_TX, gy = (g_.ny + TY - 1) / TY;
+        int nch = std::max((planes + 63) / 64, (148 * 8 + gx * gy - 1) / (gx * gy));
+        nch = std::max(1, std::min(nch, planes / 4));
+        const int chunk = (planes + nch - 1) / nch;
+        nch = (planes + chunk - 1) / chunk;
+        const dim3 grid(gx, gy, nch);
+        const FieldsOut o = fields_out();
+#define LBM_LAUNCH_FUSED(FXY, WR)                                                                                        \
+    do {                                                                                                                 \
+        auto kern = lbm3::k_fused_step<TY, FXY, WR>;                                                                     \
+        LBM_CUDA(rt_, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::bytes));          \
+        rt_.about_to_launch();                                                                                           \
+        kern<<<grid, S::NT, S::bytes, rt_.stream>>>(g_, P_, f_[a], gq_[a], f_[b], gq_[b], o, phi_, 1, g_.nz + 3, chunk); \
+    } while (0)
+        if (fxy_) {
+            if (write_fields) LBM_LAUNCH_FUSED(true, true); else LBM_LAUNCH_FUSED(true, false);
+        } else {
+            if (write_fields) LBM_LAUNCH_FUSED(false, true); else LBM_LAUNCH_FUSED(false, false);
+        }
+#undef LBM_LAUNCH_FUSED
+        return rt_.launched("k_fused_step");
+    }
+
+    // kernel_variant 0/2: fused, occupancy-oriented (k_fused2_step, TY = 8 / 4)
+    template <int TY, int MINB, bool FEARLY>
+    lbm_status launch_fused2(int write_fields)
+    {
+        using S = lbm3::Fused2Smem<TY>;
+        const int a = cur_, b = 1 - cur_;
+        const int planes = g_.nz + 2;
+        const int gx = (g_.nx + lbm3::FT_TX - 1) / lbm3::FT_TX, gy = (g_.ny + TY - 1) / TY;
+        int nch = std::max((planes + 63) / 64, (148 * 16 + gx * gy - 1) / (gx * gy));
+        nch = std::max(1, std::min(nch, planes / 4));
+        const int chunk = (planes + nch - 1) / nch;
+        nch = (planes + chunk - 1) / chunk;
+        const dim3 grid(gx, gy, nch);
+        const FieldsOut o = fields_out();
+#define LBM_LAUNCH_FUSED2(FXY, WR)                                                                                       \
+    do {                                                                                                                 \
+        auto kern = lbm3::k_fused2_step<TY, FXY, WR, MINB, FEARLY>;                                                                   \
+        LBM_CUDA(rt_, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::bytes));          \
+        rt_.about_to_launch();                                                                                           \
+        kern<<<grid, S::NT, S::bytes, rt_.stream>>>(g_, P_, f_[a], gq_[a], f_[b], gq_[b], o, phi_, 1, g_.nz + 3, chunk); \
+    } while (0)
+        if (fxy_) {
+            if (write_fields) LBM_LAUNCH_FUSED2(true, true); else LBM_LAUNCH_FUSED2(true, false);
+        } else {
+            if (write_fields) LBM_LAUNCH_FUSED2(false, true); else LBM_LAUNCH_FUSED2(false, false);
+        }
+#undef LBM_LAUNCH_FUSED2
+        return rt_.launched("k_fused2_step");
+    }
+
     lbm_status slab_collide(int write_fields) override
     {
+        switch (cfg_.kernel_variant) {
+        case 0: return launch_fused2<4, 3, true>(write_fields);
+        case 2: return launch_fused2<8, 1, true>(write_fields);
+        case 20: return launch_fused2<4, 3, false>(write_fields);
+        case 21: return launch_fused2<4, 4, true>(write_fields);
+        case 22: return launch_fused2<4, 4, false>(write_fields);
+        case 23: return launch_fused2<4, 2, true>(write_fields);
+        case 24: return launch_fused2<8, 2, true>(write_fields);
+        case 25: return launch_fused2<8, 2, false>(write_fields);
+        default: break;
+        }
+        if (cfg_.kernel_variant == 10) return launch_fused<8>(write_fields);
+        if (cfg_.kernel_variant == 12) return launch_fused<4>(write_fields);
         const int a = cur_, b = 1 - cur_;
         rt_.about_to_launch();
         k_phase<<<plane_grid(g_.nz + 4), kThreads, 0, rt_.stream>>>(g_, P_, gq_[a], phi_, 0);
@@ -240,6 +392,52 @@ public:
         const dim3 grid = plane_grid(g_.nz + 2);
         const FieldsOut o = fields_out();
         rt_.about_to_launch();
+        if (cfg_.kernel_variant >= 40 && cfg_.kernel_variant <= 42) {
+            const dim3 grid2((unsigned)(((long long)g_.nx * g_.ny + 127) / 128), g_.nz + 2);
+#define LBM_LAUNCH_STREAMED(FXY, WR)                                                                                         \
+    do {                                                                                                                     \
+        if (cfg_.kernel_variant == 40)                                                                                       \
+            k_collide_streamed<FXY, WR, 3><<<grid2, 128, 0, rt_.stream>>>(g_, P_, f_[a], gq_[a], phi_, f_[b], gq_[b], o, 1);  \
+        else if (cfg_.kernel_variant == 41)                                                                                  \
+            k_collide_streamed<FXY, WR, 4><<<grid2, 128, 0, rt_.stream>>>(g_, P_, f_[a], gq_[a], phi_, f_[b], gq_[b], o, 1);  \
+        else                                                                                                                 \
+            k_collide_streamed<FXY, WR, 2><<<grid2, 128, 0, rt_.stream>>>(g_, P_, f_[a], gq_[a], phi_, f_[b], gq_[b], o, 1);  \
+    } while (0)
+            if (fxy_) {
+                if (write_fields) LBM_LAUNCH_STREAMED(true, true); else LBM_LAUNCH_STREAMED(true, false);
+            } else {
+                if (write_fields) LBM_LAUNCH_STREAMED(false, true); else LBM_LAUNCH_STREAMED(false, false);
+            }
+#undef LBM_LAUNCH_STREAMED
+            return rt_.launched("k_collide_streamed");
+        }
+        if (cfg_.kernel_variant >= 30 && cfg_.kernel_variant <= 32) {
+            const dim3 grid2((unsigned)(((long long)g_.nx * g_.ny + 127) / 128), g_.nz + 2);
+#define LBM_LAUNCH_SPLIT(FXY, WR)                                                                                          \
+    do {                                                                                                                   \
+        if (cfg_.kernel_variant == 30)                                                                                     \
+            k_collide_split<FXY, WR, 1><<<grid2, 256, 0, rt_.stream>>>(g_, P_, f_[a], gq_[a], phi_, f_[b], gq_[b], o, 1);   \
+        else if (cfg_.kernel_variant == 31)                                                                                \
+            k_collide_split<FXY, WR, 2><<<grid2, 256, 0, rt_.stream>>>(g_, P_, f_[a], gq_[a], phi_, f_[b], gq_[b], o, 1);   \
+        else                                                                                                               \
+            k_collide_split<FXY, WR, 3><<<grid2, 256, 0, rt_.stream>>>(g_, P_, f_[a], gq_[a], phi_, f_[b], gq_[b], o, 1);   \
+    } while (0)
+            if (fxy_) {
+                if (write_fields) LBM_LAUNCH_SPLIT(true, true); else LBM_LAUNCH_SPLIT(true, false);
+            } else {
+                if (write_fields) LBM_LAUNCH_SPLIT(false, true); else LBM_LAUNCH_SPLIT(false, false);
+            }
+#undef LBM_LAUNCH_SPLIT
+            return rt_.launched("k_collide_split");
+        }
+        if ((cfg_.kernel_variant == 13 || cfg_.kernel_variant == 14) && !fxy_ && !write_fields) {
+            const dim3 grid2((unsigned)(((long long)g_.nx * g_.ny + 127) / 128), g_.nz + 2);
+            if (cfg_.kernel_variant == 13)
+                k_collide_push_occ<false, false, 3><<<grid2, 128, 0, rt_.stream>>>(g_, P_, f_[a], gq_[a], phi_, f_[b], gq_[b], o, 1);
+            else
+                k_collide_push_occ<false, false, 4><<<grid2, 128, 0, rt_.stream>>>(g_, P_, f_[a], gq_[a], phi_, f_[b], gq_[b], o, 1);
+            return rt_.launched("k_collide_push_occ");
+        }
 #define LBM_LAUNCH_COLLIDE(FXY, WR) \
     k_collide_push<FXY, WR><<<grid, kThreads, 0, rt_.stream>>>(g_, P_, f_[a], gq_[a], phi_, f_[b], gq_[b], o, 1)
         if (fxy_) {

@@ -16,6 +16,7 @@ struct Emu {
     bool fxy;
     std::vector<double> f[2], gq[2], phi, rho, ux, uy, uz;
     int cur = 0;
+    int streamed = 0;        // 0: collide(), 1: collide_streamed(), 2: collide_f_part()+collide_g_part()
 };
 
 extern "C" {
@@ -36,6 +37,7 @@ Emu *emu3_create(int nx, int ny, int nz, const double *p)
     return e;
 }
 void emu3_destroy(Emu *e) { delete e; }
+void emu3_use_streamed(Emu *e, int on) { e->streamed = on; }
 
 static void put(Emu *e, double *dst, const double *src)
 {
@@ -102,6 +104,26 @@ void emu3_step(Emu *e, int n)
         for (int zs = 1; zs <= g.nz + 2; zs++)
             for (int iy = 0; iy < g.ny; iy++)
                 for (int ix = 0; ix < g.nx; ix++) {
+                    if (e->streamed == 2) {
+                        if (e->fxy) {
+                            if (w) collide_push_thread_split<true, true>(g, e->P, e->f[a].data(), e->gq[a].data(), e->phi.data(), e->f[b].data(), e->gq[b].data(), o, zs, ix, iy);
+                            else collide_push_thread_split<true, false>(g, e->P, e->f[a].data(), e->gq[a].data(), e->phi.data(), e->f[b].data(), e->gq[b].data(), o, zs, ix, iy);
+                        } else {
+                            if (w) collide_push_thread_split<false, true>(g, e->P, e->f[a].data(), e->gq[a].data(), e->phi.data(), e->f[b].data(), e->gq[b].data(), o, zs, ix, iy);
+                            else collide_push_thread_split<false, false>(g, e->P, e->f[a].data(), e->gq[a].data(), e->phi.data(), e->f[b].data(), e->gq[b].data(), o, zs, ix, iy);
+                        }
+                        continue;
+                    }
+                    if (e->streamed) {
+                        if (e->fxy) {
+                            if (w) collide_push_thread_streamed<true, true>(g, e->P, e->f[a].data(), e->gq[a].data(), e->phi.data(), e->f[b].data(), e->gq[b].data(), o, zs, ix, iy);
+                            else collide_push_thread_streamed<true, false>(g, e->P, e->f[a].data(), e->gq[a].data(), e->phi.data(), e->f[b].data(), e->gq[b].data(), o, zs, ix, iy);
+                        } else {
+                            if (w) collide_push_thread_streamed<false, true>(g, e->P, e->f[a].data(), e->gq[a].data(), e->phi.data(), e->f[b].data(), e->gq[b].data(), o, zs, ix, iy);
+                            else collide_push_thread_streamed<false, false>(g, e->P, e->f[a].data(), e->gq[a].data(), e->phi.data(), e->f[b].data(), e->gq[b].data(), o, zs, ix, iy);
+                        }
+                        continue;
+                    }
                     if (e->fxy) {
                         if (w) collide_push_thread<true, true>(g, e->P, e->f[a].data(), e->gq[a].data(), e->phi.data(), e->f[b].data(), e->gq[b].data(), o, zs, ix, iy);
                         else collide_push_thread<true, false>(g, e->P, e->f[a].data(), e->gq[a].data(), e->phi.data(), e->f[b].data(), e->gq[b].data(), o, zs, ix, iy);
