@@ -50,6 +50,136 @@ __global__ void __launch_bounds__(128, MINB) k_collide_push_occ(Geom g, Params P
                                           (int)(idx / g.nx));
 }
 
+// Interior / rim split of the plain collide-push.  The interior kernel contains no boundary code at all
+// (nodes 2..NX-3 x 2..NY-3: every push is a plain shifted store), which removes the control-flow merges
+// and register moves the folded boundary path costs every thread; the rim kernel runs the one-node rim
+// (and, on output steps, the wall-node fields) -- 2(NX+NY) nodes per plane.
+template <bool FXY, bool WRITE, int MINB>
+__global__ void __launch_bounds__(128, MINB) k_collide_interior(Geom g, Params P, const double *__restrict__ fin,
+                                                                const double *__restrict__ gin, const double *__restrict__ phi,
+                                                                double *__restrict__ fout, double *__restrict__ gout, FieldsOut o,
+                                                                int zs0)
+{
+    const long long idx = (long long)blockIdx.x * 128 + threadIdx.x;
+    const int NX = g.nx, NY = g.ny;
+    if (idx >= (long long)NX * NY) return;
+    const int ix = (int)(idx % NX), iy = (int)(idx / NX), zs = zs0 + blockIdx.y;
+    if (ix < 2 || ix > NX - 3 || iy < 2 || iy > NY - 3) return;
+    const long long pl = g.pl;
+    double F[19], G[19], PH[19];
+    const double *pf = fin + lbm3::pop_index(g, zs, 0, idx), *pg = gin + lbm3::pop_index(g, zs, 0, idx);
+    constexpr int CX[19] = LBM3_CX, CY[19] = LBM3_CY, CZ[19] = LBM3_CZ;
+#pragma unroll
+    for (int k = 0; k < 19; k++) {
+        F[k] = __ldg(pf + k * pl);
+        G[k] = __ldg(pg + k * pl);
+        PH[k] = __ldg(phi + (long long)(zs + CZ[k]) * pl + idx + CY[k] * NX + CX[k]);
+    }
+    lbm3::collide_push_node<FXY, WRITE, 1>(g, P, F, G, PH, fout, gout, o, zs, ix, iy);
+}
+
+template <bool FXY, bool WRITE>
+__global__ void __launch_bounds__(128) k_collide_rim(Geom g, Params P, const double *__restrict__ fin,
+                                                     const double *__restrict__ gin, const double *__restrict__ phi,
+                                                     double *__restrict__ fout, double *__restrict__ gout, FieldsOut o, int zs0)
+{
+    const int NX = g.nx, NY = g.ny, zs = zs0 + blockIdx.y;
+    const int rows = 2 * (NX - 2), cols = 2 * (NY - 4 > 0 ? NY - 4 : 0);
+    int t = blockIdx.x * 128 + threadIdx.x;
+    int ix, iy;
+    if (t < rows) {
+        iy = t < NX - 2 ? 1 : NY - 2;
+        ix = 1 + (t < NX - 2 ? t : t - (NX - 2));
+        if (NY - 2 == 1 && t >= NX - 2) return;
+    } else if (t < rows + cols) {
+        t -= rows;
+        const int h = NY - 4;
+        ix = t < h ? 1 : NX - 2;
+        iy = 2 + (t < h ? t : t - h);
+        if (NX - 2 == 1 && t >= h) return;
+    } else {
+        if (!WRITE) return;
+        t -= rows + cols;   // wall nodes, lattice.hpp:75-106: row NY-1 then column NX-1
+        if (t < NX) { ix = t; iy = NY - 1; }
+        else if (t < NX + NY - 1) { ix = NX - 1; iy = t - NX; }
+        else return;
+        if (zs >= 2 && zs < g.nz + 2) {
+            const long long at = (long long)(zs - 2) * g.pl + (long long)iy * NX + ix;
+            o.rho[at] = P.rho_wall; o.ux[at] = 0.0; o.uy[at] = 0.0; o.uz[at] = 0.0;
+        }
+        return;
+    }
+    const long long idx = (long long)iy * NX + ix, pl = g.pl;
+    double F[19], G[19], PH[19];
+    const int CX[19] = LBM3_CX, CY[19] = LBM3_CY, CZ[19] = LBM3_CZ;
+    for (int k = 0; k < 19; k++) {
+        F[k] = fin[lbm3::pop_index(g, zs, k, idx)];
+        G[k] = gin[lbm3::pop_index(g, zs, k, idx)];
+        PH[k] = phi[(long long)(zs + CZ[k]) * pl + idx + CY[k] * NX + CX[k]];
+    }
+    lbm3::collide_push_node<FXY, WRITE, 2>(g, P, F, G, PH, fout, gout, o, zs, ix, iy);
+}
+
+// Collide-push with every global load asynchronous and no block-wide barrier.
+//
+// ncu on k_collide_push (profiles/r01_collide_plain.*): 8 resident warps per SM (238 registers), top stall
+// long-scoreboard, 33 % of the issue slots used, 4.7 TB/s.  The loads of a node are only in flight while its
+// thread waits for them; during the ~1500 instructions of arithmetic nothing is.  Here a thread keeps one
+// (x,y) and marches along z: as soon as the 57 values of plane z (19 f, 19 g, 19 neighbour phi) have been
+// moved from its private shared-memory slots into registers, it issues the 57 cp.async (LDGSTS, 8 B) for
+// plane z+1 into the same slots and then does the arithmetic of plane z.  Loads of the next node overlap the
+// whole collision of the current one without holding registers; every thread only ever touches its own
+// slots, so there is no __syncthreads and warps drift freely.
+template <bool FXY, bool WRITE, int MINB>
+__global__ void __launch_bounds__(128, MINB) k_collide_async(Geom g, Params P, const double *__restrict__ fin,
+                                                             const double *__restrict__ gin, const double *__restrict__ phi,
+                                                             double *__restrict__ fout, double *__restrict__ gout, FieldsOut o,
+                                                             int zs_begin, int zs_end, int chunk)
+{
+    extern __shared__ __align__(16) double slots[];   // [57][128]
+    const int tid = threadIdx.x;
+    const long long idx = (long long)blockIdx.x * 128 + tid;
+    const int NX = g.nx, NY = g.ny;
+    if (idx >= (long long)NX * NY) return;
+    const int ix = (int)(idx % NX), iy = (int)(idx / NX);
+    const int zs0 = zs_begin + blockIdx.y * chunk, zs1 = min(zs0 + chunk, zs_end);
+    if (ix < 1 || ix > NX - 2 || iy < 1 || iy > NY - 2) {
+        if (WRITE && (ix == NX - 1 || iy == NY - 1))   // wall node fields, lattice.hpp:75-106
+            for (int zs = max(zs0, 2); zs < min(zs1, g.nz + 2); zs++) {
+                const long long at = (long long)(zs - 2) * g.pl + idx;
+                o.rho[at] = P.rho_wall; o.ux[at] = 0.0; o.uy[at] = 0.0; o.uz[at] = 0.0;
+            }
+        return;
+    }
+    double *slot = slots + tid;
+    const long long pl = g.pl;
+    auto issue = [&](int zs) {
+        constexpr int CX[19] = LBM3_CX, CY[19] = LBM3_CY, CZ[19] = LBM3_CZ;
+        const double *pf = fin + lbm3::pop_index(g, zs, 0, idx);
+        const double *pg = gin + lbm3::pop_index(g, zs, 0, idx);
+#pragma unroll
+        for (int k = 0; k < 19; k++) {
+            lbm3::cp_async8(slot + k * 128, pf + k * pl);
+            lbm3::cp_async8(slot + (19 + k) * 128, pg + k * pl);
+            lbm3::cp_async8(slot + (38 + k) * 128, phi + (long long)(zs + CZ[k]) * pl + idx + CY[k] * NX + CX[k]);
+        }
+        lbm3::cp_async_commit();
+    };
+    issue(zs0);
+    for (int zs = zs0; zs < zs1; zs++) {
+        double F[19], G[19], PH[19];
+        lbm3::cp_async_wait<0>();
+#pragma unroll
+        for (int k = 0; k < 19; k++) {
+            F[k] = slot[k * 128];
+            G[k] = slot[(19 + k) * 128];
+            PH[k] = slot[(38 + k) * 128];
+        }
+        if (zs + 1 < zs1) issue(zs + 1);
+        lbm3::collide_push_node<FXY, WRITE>(g, P, F, G, PH, fout, gout, o, zs, ix, iy);
+    }
+}
+
 // Plain collide-push through collide_streamed(): fewer live registers, more resident warps.
 template <bool FXY, bool WRITE, int MINB>
 __global__ void __launch_bounds__(128, MINB) k_collide_streamed(Geom g, Params P, const double *__restrict__ fin,
@@ -392,6 +522,60 @@ public:
         const dim3 grid = plane_grid(g_.nz + 2);
         const FieldsOut o = fields_out();
         rt_.about_to_launch();
+        if (cfg_.kernel_variant >= 60 && cfg_.kernel_variant <= 62) {
+            const dim3 gi((unsigned)(((long long)g_.nx * g_.ny + 127) / 128), g_.nz + 2);
+            const int rim = 2 * (g_.nx - 2) + 2 * std::max(0, g_.ny - 4) + g_.nx + g_.ny - 1;
+            const dim3 gr((rim + 127) / 128, g_.nz + 2);
+#define LBM_LAUNCH_SPLIT2(FXY, WR)                                                                                           \
+    do {                                                                                                                     \
+        if (cfg_.kernel_variant == 60)                                                                                       \
+            k_collide_interior<FXY, WR, 2><<<gi, 128, 0, rt_.stream>>>(g_, P_, f_[a], gq_[a], phi_, f_[b], gq_[b], o, 1);     \
+        else if (cfg_.kernel_variant == 61)                                                                                  \
+            k_collide_interior<FXY, WR, 3><<<gi, 128, 0, rt_.stream>>>(g_, P_, f_[a], gq_[a], phi_, f_[b], gq_[b], o, 1);     \
+        else                                                                                                                 \
+            k_collide_interior<FXY, WR, 4><<<gi, 128, 0, rt_.stream>>>(g_, P_, f_[a], gq_[a], phi_, f_[b], gq_[b], o, 1);     \
+        LBM_TRY(rt_.launched("k_collide_interior"));                                                                         \
+        rt_.about_to_launch();                                                                                               \
+        k_collide_rim<FXY, WR><<<gr, 128, 0, rt_.stream>>>(g_, P_, f_[a], gq_[a], phi_, f_[b], gq_[b], o, 1);                 \
+    } while (0)
+            if (fxy_) {
+                if (write_fields) LBM_LAUNCH_SPLIT2(true, true); else LBM_LAUNCH_SPLIT2(true, false);
+            } else {
+                if (write_fields) LBM_LAUNCH_SPLIT2(false, true); else LBM_LAUNCH_SPLIT2(false, false);
+            }
+#undef LBM_LAUNCH_SPLIT2
+            return rt_.launched("k_collide_rim");
+        }
+        if (cfg_.kernel_variant >= 50 && cfg_.kernel_variant <= 52) {
+            const int planes = g_.nz + 2;
+            const int gxb = (int)(((long long)g_.nx * g_.ny + 127) / 128);
+            int nch = std::max((planes + 31) / 32, (148 * 16 + gxb - 1) / gxb);
+            nch = std::max(1, std::min(nch, planes / 4));
+            const int chunk = (planes + nch - 1) / nch;
+            nch = (planes + chunk - 1) / chunk;
+            const dim3 grid2(gxb, nch);
+            const size_t smem = 57 * 128 * sizeof(double);
+#define LBM_LAUNCH_ASYNC1(FXY, WR, MB)                                                                                \
+    do {                                                                                                              \
+        auto kern = k_collide_async<FXY, WR, MB>;                                                                     \
+        LBM_CUDA(rt_, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));           \
+        kern<<<grid2, 128, smem, rt_.stream>>>(g_, P_, f_[a], gq_[a], phi_, f_[b], gq_[b], o, 1, g_.nz + 3, chunk);   \
+    } while (0)
+#define LBM_LAUNCH_ASYNC(FXY, WR)                                                                                     \
+    do {                                                                                                              \
+        if (cfg_.kernel_variant == 50) LBM_LAUNCH_ASYNC1(FXY, WR, 2);                                                 \
+        else if (cfg_.kernel_variant == 51) LBM_LAUNCH_ASYNC1(FXY, WR, 3);                                            \
+        else LBM_LAUNCH_ASYNC1(FXY, WR, 4);                                                                           \
+    } while (0)
+            if (fxy_) {
+                if (write_fields) LBM_LAUNCH_ASYNC(true, true); else LBM_LAUNCH_ASYNC(true, false);
+            } else {
+                if (write_fields) LBM_LAUNCH_ASYNC(false, true); else LBM_LAUNCH_ASYNC(false, false);
+            }
+#undef LBM_LAUNCH_ASYNC
+#undef LBM_LAUNCH_ASYNC1
+            return rt_.launched("k_collide_async");
+        }
         if (cfg_.kernel_variant >= 40 && cfg_.kernel_variant <= 42) {
             const dim3 grid2((unsigned)(((long long)g_.nx * g_.ny + 127) / 128), g_.nz + 2);
 #define LBM_LAUNCH_STREAMED(FXY, WR)                                                                                         \

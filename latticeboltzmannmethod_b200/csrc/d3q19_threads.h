@@ -112,6 +112,44 @@ LBM_HD void mirror_fields(const double *F, const Params &P, const FieldsOut &o, 
     o.uz[at] = uz + P.fz / (2 * d);
 }
 
+// ---- one bulk node whose 19+19 populations and 19 neighbour phase values are already in registers ----
+// PART 0: any bulk node; 1: a node at least two away from every mirror line / wall (no boundary code is
+// even compiled in: straight-line kernel for the interior); 2: a node of the one-node rim (always the
+// folded boundary push).
+template <bool FXY, bool WRITE, int PART = 0>
+LBM_HD void collide_push_node(const Geom &g, const Params &P, double *F, double *G, const double *PH, double *fout,
+                              double *gout, const FieldsOut &o, int zs, int ix, int iy)
+{
+    const int NX = g.nx, NY = g.ny;
+    const long long idx = (long long)iy * NX + ix;
+    double gx, gy, gz, lap;
+    stencils(PH, gx, gy, gz, lap);
+    const bool own = zs >= 2 && zs < g.nz + 2;
+    if (WRITE && own && PART != 1) {
+        if (iy == 1) mirror_fields<2>(F, P, o, (long long)(zs - 2) * g.pl + ix);
+        if (ix == 1) mirror_fields<1>(F, P, o, (long long)(zs - 2) * g.pl + (long long)iy * NX);
+        if (ix == 1 && iy == 1) mirror_fields<3>(F, P, o, (long long)(zs - 2) * g.pl);
+    }
+    double rho, ux, uy, uz;
+    collide<FXY>(F, G, PH[0], gx, gy, gz, lap, P, rho, ux, uy, uz);
+    if (WRITE && own) {
+        const long long at = (long long)(zs - 2) * g.pl + idx;
+        o.rho[at] = rho; o.ux[at] = ux; o.uy[at] = uy; o.uz[at] = uz;
+    }
+    const bool border = PART == 2 || (PART == 0 && (ix == 1 || iy == 1 || ix == NX - 2 || iy == NY - 2));
+    if (!border) {
+        const int CX[19] = LBM3_CX, CY[19] = LBM3_CY, CZ[19] = LBM3_CZ;
+#pragma unroll
+        for (int k = 0; k < 19; k++) {
+            const long long t = pop_index(g, zs + CZ[k], k, idx + CY[k] * NX + CX[k]);
+            fout[t] = F[k];
+            gout[t] = G[k];
+        }
+    } else {
+        for (int k = 0; k < 19; k++) push_border(g, fout, gout, zs, ix, iy, k, F[k], G[k]);
+    }
+}
+
 // ---- one bulk node: moments, stencils, collision, push -------------------
 // Reference: Lattice::updateMacro + Lattice::collide_stream (lattice.hpp:4-108,
 // 377-688) for this node.  `phi` must already hold the extended phase field of
@@ -141,36 +179,7 @@ LBM_HD void collide_push_thread(const Geom &g, const Params &P, const double *fi
 #pragma unroll
         for (int k = 0; k < 19; k++) PH[k] = phi[(long long)(zs + CZ[k]) * g.pl + idx + CY[k] * NX + CX[k]];
     }
-    double gx, gy, gz, lap;
-    stencils(PH, gx, gy, gz, lap);
-
-    const bool own = zs >= 2 && zs < g.nz + 2;
-    if (WRITE && own) {
-        if (iy == 1) mirror_fields<2>(F, P, o, (long long)(zs - 2) * g.pl + ix);
-        if (ix == 1) mirror_fields<1>(F, P, o, (long long)(zs - 2) * g.pl + (long long)iy * NX);
-        if (ix == 1 && iy == 1) mirror_fields<3>(F, P, o, (long long)(zs - 2) * g.pl);
-    }
-
-    double rho, ux, uy, uz;
-    collide<FXY>(F, G, PH[0], gx, gy, gz, lap, P, rho, ux, uy, uz);
-
-    if (WRITE && own) {
-        const long long at = (long long)(zs - 2) * g.pl + idx;
-        o.rho[at] = rho; o.ux[at] = ux; o.uy[at] = uy; o.uz[at] = uz;
-    }
-
-    const bool border = ix == 1 || iy == 1 || ix == NX - 2 || iy == NY - 2;
-    if (!border) {
-        const int CX[19] = LBM3_CX, CY[19] = LBM3_CY, CZ[19] = LBM3_CZ;
-#pragma unroll
-        for (int k = 0; k < 19; k++) {
-            const long long t = pop_index(g, zs + CZ[k], k, idx + CY[k] * NX + CX[k]);
-            fout[t] = F[k];
-            gout[t] = G[k];
-        }
-    } else {
-        for (int k = 0; k < 19; k++) push_border(g, fout, gout, zs, ix, iy, k, F[k], G[k]);
-    }
+    collide_push_node<FXY, WRITE>(g, P, F, G, PH, fout, gout, o, zs, ix, iy);
 }
 
 // ---- the same node update through collide_streamed() ----------------------
