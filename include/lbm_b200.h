@@ -77,7 +77,8 @@ typedef struct {
     double force_ampl;         /* mrt.cpp:98 */
     int device;                /* CUDA device ordinal */
     int slab_rank, slab_count; /* z-slab decomposition (3-D only): this context owns slab `rank` of `count` */
-    int kernel_variant;        /* 0 = default (fastest), 1 = plain two-kernel path kept for cross-checks */
+    int kernel_variant;        /* 0 = default (fastest measured); other values select the alternative D3Q19 kernels
+                                  kept for cross-checks and measurements, see DESIGN.md section 6 */
 } lbm_config;
 
 /* Fills *cfg with the constants of the reference program for `model`

@@ -111,13 +111,16 @@ __global__ void __launch_bounds__(128) k_collide_rim(Geom g, Params P, const dou
     }
     const long long idx = (long long)iy * NX + ix, pl = g.pl;
     double F[19], G[19], PH[19];
-    const int CX[19] = LBM3_CX, CY[19] = LBM3_CY, CZ[19] = LBM3_CZ;
+    constexpr int CX[19] = LBM3_CX, CY[19] = LBM3_CY, CZ[19] = LBM3_CZ;
+#pragma unroll
     for (int k = 0; k < 19; k++) {
         F[k] = fin[lbm3::pop_index(g, zs, k, idx)];
         G[k] = gin[lbm3::pop_index(g, zs, k, idx)];
         PH[k] = phi[(long long)(zs + CZ[k]) * pl + idx + CY[k] * NX + CX[k]];
     }
-    lbm3::collide_push_node<FXY, WRITE, 2>(g, P, F, G, PH, fout, gout, o, zs, ix, iy);
+    // compile-time direction indices in the folded push (no table look-ups in local memory)
+    const double *Gp = G;
+    lbm3::collide_push_node_streamed<FXY, WRITE>(g, P, F, [Gp](int k) { return Gp[k]; }, PH, fout, gout, o, zs, ix, iy);
 }
 
 // Collide-push with every global load asynchronous and no block-wide barrier.
@@ -379,6 +382,7 @@ public:
             NcclApi *api = nccl_api(nullptr);
             if (api && api->CommDestroy) api->CommDestroy(comm_);
         }
+        if (side_) { cudaStreamDestroy(side_); cudaEventDestroy(ev_fork_); cudaEventDestroy(ev_join_); }
         for (int b = 0; b < 2; b++) { cudaFree(f_[b]); cudaFree(gq_[b]); }
         cudaFree(phi_); cudaFree(rho_); cudaFree(ux_); cudaFree(uy_); cudaFree(uz_); cudaFree(diag_);
     }
@@ -500,10 +504,57 @@ public:
         return rt_.launched("k_fused2_step");
     }
 
+    // kernel_variant 0: fused interior kernel + rim kernel
+    template <int TY, int MINB, int GEN>
+    lbm_status launch_fused3(int write_fields)
+    {
+        const size_t smem_bytes = GEN == 3 ? lbm3::Fused2Smem<TY>::bytes : (GEN == 4 ? lbm3::Fused4Smem<TY>::bytes : lbm3::Fused5Smem<TY>::bytes);
+        constexpr int NT = lbm3::FT_TX * TY;
+        const int a = cur_, b = 1 - cur_;
+        const int planes = g_.nz + 2;
+        const int gx = (g_.nx + lbm3::FT_TX - 1) / lbm3::FT_TX, gy = (g_.ny + TY - 1) / TY;
+        int nch = std::max((planes + 63) / 64, (148 * 16 + gx * gy - 1) / (gx * gy));
+        nch = std::max(1, std::min(nch, planes / 4));
+        const int chunk = (planes + nch - 1) / nch;
+        nch = (planes + chunk - 1) / chunk;
+        const dim3 grid(gx, gy, nch);
+        const FieldsOut o = fields_out();
+        const int rim = 2 * (g_.nx - 2) + 2 * std::max(0, g_.ny - 4) + g_.nx + g_.ny - 1;
+        const dim3 gr((rim + 127) / 128, g_.nz + 2);
+#define LBM_LAUNCH_FUSED3(FXY, WR)                                                                                       \
+    do {                                                                                                                 \
+        auto kern = GEN == 3 ? lbm3::k_fused3_step<TY, FXY, WR, MINB>                                                     \
+                             : (GEN == 4 ? lbm3::k_fused4_step<TY, FXY, WR, MINB> : lbm3::k_fused5_step<TY, FXY, WR, MINB>); \
+        LBM_CUDA(rt_, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));        \
+        rt_.about_to_launch();                                                                                           \
+        kern<<<grid, NT, smem_bytes, rt_.stream>>>(g_, P_, f_[a], gq_[a], f_[b], gq_[b], o, phi_, 1, g_.nz + 3, chunk);  \
+        LBM_TRY(rt_.launched(GEN == 3 ? "k_fused3_step" : (GEN == 4 ? "k_fused4_step" : "k_fused5_step")));                                                                          \
+        rt_.about_to_launch();                                                                                           \
+        k_collide_rim<FXY, WR><<<gr, 128, 0, rt_.stream>>>(g_, P_, f_[a], gq_[a], phi_, f_[b], gq_[b], o, 1);             \
+    } while (0)
+        if (fxy_) {
+            if (write_fields) LBM_LAUNCH_FUSED3(true, true); else LBM_LAUNCH_FUSED3(true, false);
+        } else {
+            if (write_fields) LBM_LAUNCH_FUSED3(false, true); else LBM_LAUNCH_FUSED3(false, false);
+        }
+#undef LBM_LAUNCH_FUSED3
+        return rt_.launched("k_collide_rim");
+    }
+
     lbm_status slab_collide(int write_fields) override
     {
         switch (cfg_.kernel_variant) {
-        case 0: return launch_fused2<4, 3, true>(write_fields);
+        case 70: return launch_fused3<4, 3, 3>(write_fields);
+        case 71: return launch_fused3<4, 2, 3>(write_fields);
+        case 72: return launch_fused3<8, 1, 3>(write_fields);
+        case 90: return launch_fused3<4, 3, 5>(write_fields);
+        case 91: return launch_fused3<4, 2, 5>(write_fields);
+        case 92: return launch_fused3<8, 1, 5>(write_fields);
+        case 93: return launch_fused3<4, 4, 5>(write_fields);
+        case 80: return launch_fused3<4, 3, 4>(write_fields);
+        case 81: return launch_fused3<4, 2, 4>(write_fields);
+        case 82: return launch_fused3<8, 1, 4>(write_fields);
+        case 3: return launch_fused2<4, 3, true>(write_fields);
         case 2: return launch_fused2<8, 1, true>(write_fields);
         case 20: return launch_fused2<4, 3, false>(write_fields);
         case 21: return launch_fused2<4, 4, true>(write_fields);
@@ -522,7 +573,38 @@ public:
         const dim3 grid = plane_grid(g_.nz + 2);
         const FieldsOut o = fields_out();
         rt_.about_to_launch();
-        if (cfg_.kernel_variant >= 60 && cfg_.kernel_variant <= 62) {
+        if (cfg_.kernel_variant == 63 || cfg_.kernel_variant == 64) {
+            // interior on the main stream, rim concurrently on a high-priority side stream: both read the
+            // front buffers and the phase field, and every (node, direction) slot of the back buffers has
+            // exactly one writer, so the two kernels are independent
+            LBM_TRY(ensure_side_stream());
+            const dim3 gi((unsigned)(((long long)g_.nx * g_.ny + 127) / 128), g_.nz + 2);
+            const int rim = 2 * (g_.nx - 2) + 2 * std::max(0, g_.ny - 4) + g_.nx + g_.ny - 1;
+            const dim3 gr((rim + 127) / 128, g_.nz + 2);
+            LBM_CUDA(rt_, cudaEventRecord(ev_fork_, rt_.stream));
+            LBM_CUDA(rt_, cudaStreamWaitEvent(side_, ev_fork_, 0));
+#define LBM_LAUNCH_SPLIT3(FXY, WR)                                                                                           \
+    do {                                                                                                                     \
+        k_collide_rim<FXY, WR><<<gr, 128, 0, side_>>>(g_, P_, f_[a], gq_[a], phi_, f_[b], gq_[b], o, 1);                      \
+        LBM_TRY(rt_.launched("k_collide_rim"));                                                                              \
+        rt_.about_to_launch();                                                                                               \
+        if (cfg_.kernel_variant == 63)                                                                                       \
+            k_collide_interior<FXY, WR, 3><<<gi, 128, 0, rt_.stream>>>(g_, P_, f_[a], gq_[a], phi_, f_[b], gq_[b], o, 1);     \
+        else                                                                                                                 \
+            k_collide_interior<FXY, WR, 2><<<gi, 128, 0, rt_.stream>>>(g_, P_, f_[a], gq_[a], phi_, f_[b], gq_[b], o, 1);     \
+    } while (0)
+            if (fxy_) {
+                if (write_fields) LBM_LAUNCH_SPLIT3(true, true); else LBM_LAUNCH_SPLIT3(true, false);
+            } else {
+                if (write_fields) LBM_LAUNCH_SPLIT3(false, true); else LBM_LAUNCH_SPLIT3(false, false);
+            }
+#undef LBM_LAUNCH_SPLIT3
+            LBM_TRY(rt_.launched("k_collide_interior"));
+            LBM_CUDA(rt_, cudaEventRecord(ev_join_, side_));
+            LBM_CUDA(rt_, cudaStreamWaitEvent(rt_.stream, ev_join_, 0));
+            return LBM_OK;
+        }
+        if (cfg_.kernel_variant == 0 || (cfg_.kernel_variant >= 60 && cfg_.kernel_variant <= 62)) {
             const dim3 gi((unsigned)(((long long)g_.nx * g_.ny + 127) / 128), g_.nz + 2);
             const int rim = 2 * (g_.nx - 2) + 2 * std::max(0, g_.ny - 4) + g_.nx + g_.ny - 1;
             const dim3 gr((rim + 127) / 128, g_.nz + 2);
@@ -530,7 +612,7 @@ public:
     do {                                                                                                                     \
         if (cfg_.kernel_variant == 60)                                                                                       \
             k_collide_interior<FXY, WR, 2><<<gi, 128, 0, rt_.stream>>>(g_, P_, f_[a], gq_[a], phi_, f_[b], gq_[b], o, 1);     \
-        else if (cfg_.kernel_variant == 61)                                                                                  \
+        else if (cfg_.kernel_variant == 61 || cfg_.kernel_variant == 0)                                                      \
             k_collide_interior<FXY, WR, 3><<<gi, 128, 0, rt_.stream>>>(g_, P_, f_[a], gq_[a], phi_, f_[b], gq_[b], o, 1);     \
         else                                                                                                                 \
             k_collide_interior<FXY, WR, 4><<<gi, 128, 0, rt_.stream>>>(g_, P_, f_[a], gq_[a], phi_, f_[b], gq_[b], o, 1);     \
@@ -807,6 +889,19 @@ private:
     double *f_[2] = {nullptr, nullptr}, *gq_[2] = {nullptr, nullptr};
     double *phi_ = nullptr, *rho_ = nullptr, *ux_ = nullptr, *uy_ = nullptr, *uz_ = nullptr, *diag_ = nullptr;
     void *comm_ = nullptr;
+    cudaStream_t side_ = nullptr;
+    cudaEvent_t ev_fork_ = nullptr, ev_join_ = nullptr;
+
+    lbm_status ensure_side_stream()
+    {
+        if (side_) return LBM_OK;
+        int lo = 0, hi = 0;
+        LBM_CUDA(rt_, cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        LBM_CUDA(rt_, cudaStreamCreateWithPriority(&side_, cudaStreamNonBlocking, hi));
+        LBM_CUDA(rt_, cudaEventCreateWithFlags(&ev_fork_, cudaEventDisableTiming));
+        LBM_CUDA(rt_, cudaEventCreateWithFlags(&ev_join_, cudaEventDisableTiming));
+        return LBM_OK;
+    }
 };
 
 }  // namespace

@@ -408,5 +408,440 @@ __global__ void __launch_bounds__(FT_TX *TY, MINB)
     }
 }
 
+// ---------------------------------------------------------------------------
+// Third fused kernel = k_fused2_step restricted to the interior nodes (2..NX-3 x 2..NY-3): no boundary
+// code in the collision, array form of the collision with all loads up front, 168 registers so that three
+// 128-thread blocks (12 warps) share an SM.  The one-node rim is collided afterwards by k_collide_rim
+// (d3q19_binary.cu), which reads the phase field from global memory; this kernel therefore records phi
+// for the three-node band next to the mirror lines and walls on every step.
+template <int TY, bool FXY, bool WRITE, int MINB>
+__global__ void __launch_bounds__(FT_TX *TY, MINB)
+    k_fused3_step(Geom g, Params P, const double *__restrict__ fin, const double *__restrict__ gin, double *__restrict__ fout,
+                  double *__restrict__ gout, FieldsOut o, double *__restrict__ phi_out, int zs_begin, int zs_end, int chunk)
+{
+    using S = Fused2Smem<TY>;
+    constexpr int NT = S::NT, RW = S::RW, RP = S::RP;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    double *Gs = reinterpret_cast<double *>(smem_raw);       // [2][19][NT]
+    double *ring = Gs + 2 * 19 * NT;                          // [4][RP]
+    int *e_owner = reinterpret_cast<int *>(ring + 4 * RP);
+    int *e_ring = e_owner + FT_NE;
+    int *e_flags = e_ring + FT_NE;
+    int *n_extra_p = e_flags + FT_NE;
+
+    const int NX = g.nx, NY = g.ny;
+    const int tid = threadIdx.x, tx = tid & 31, ty = tid >> 5;
+    const int ix0 = blockIdx.x * FT_TX, iy0 = blockIdx.y * TY;
+    const int ix = ix0 + tx, iy = iy0 + ty;
+    const bool in_dom = ix < NX && iy < NY;
+    const bool bulk = in_dom && ix >= 1 && ix <= NX - 2 && iy >= 1 && iy <= NY - 2;
+    const long long idx = (long long)iy * NX + ix;
+    const int zs0 = zs_begin + blockIdx.z * chunk;
+    const int zs1 = min(zs0 + chunk, zs_end);
+    if (zs0 >= zs1) return;
+
+    if (tid == 0) *n_extra_p = 0;
+    __syncthreads();
+    for (int p = tid; p < RP; p += NT) {
+        const int px = p % RW, py = p / RW;
+        const int ex = ix0 - 1 + px, ey = iy0 - 1 + py;
+        if (ex < 0 || ex > NX - 1 || ey < 0 || ey > NY - 1) continue;
+        const bool inside = px >= 1 && px <= FT_TX && py >= 1 && py <= TY;
+        const bool ebulk = ex >= 1 && ex <= NX - 2 && ey >= 1 && ey <= NY - 2;
+        if (inside && ebulk) continue;
+        const int ox = min(max(ex, 1), NX - 2), oy = min(max(ey, 1), NY - 2);
+        const int slot = atomicAdd(n_extra_p, 1);
+        e_owner[slot] = oy * NX + ox;
+        e_ring[slot] = p;
+        e_flags[slot] = (ex == 0 ? 1 : 0) | (ey == 0 ? 2 : 0) | ((ex == NX - 1 || ey == NY - 1) ? 4 : 0) | (inside ? 8 : 0);
+    }
+    __syncthreads();
+    const int n_extra = *n_extra_p;
+    const bool has_extra = tid < n_extra;
+    const int my_owner = has_extra ? e_owner[tid] : 0;
+    const int my_ring = has_extra ? e_ring[tid] : 0;
+    const int my_flags = has_extra ? e_flags[tid] : 0;
+    const long long pl = g.pl;
+    const bool band = ix <= 2 || ix >= NX - 3 || iy <= 2 || iy >= NY - 3;
+    const bool interior = in_dom && ix >= 2 && ix <= NX - 3 && iy >= 2 && iy <= NY - 3;
+
+    // phi of storage plane zs: own node (g kept in the shared slot when `keep`) and this thread's extra position
+    auto phase_plane = [&](int zs, bool keep) {
+        double *rp = ring + (size_t)(zs & 3) * RP;
+        // which block records phi(zs) in global memory: the one whose chunk holds the plane (the first /
+        // last chunk also take the outermost ghost planes).  Always for the three-node band along the
+        // mirror lines and walls (the rim kernel's stencils), everywhere on output steps.
+        const bool mine = (zs >= zs0 && zs < zs1) || (zs == zs0 - 1 && zs0 == zs_begin) || (zs == zs1 && zs1 == zs_end);
+        const bool store_all = WRITE && mine && zs >= 2 && zs < g.nz + 2;
+        double G[19], E[19];
+        if (bulk) {
+            const double *src = gin + pop_index(g, zs, 0, idx);
+#pragma unroll
+            for (int k = 0; k < 19; k++) G[k] = __ldg(src + k * pl);
+        }
+        if (has_extra) {
+            const double *src = gin + pop_index(g, zs, 0, my_owner);
+#pragma unroll
+            for (int k = 0; k < 19; k++) E[k] = __ldg(src + k * pl);
+        }
+        if (bulk) {
+            const double v = sum19(G);
+            rp[(ty + 1) * RW + tx + 1] = v;
+            if (keep) {
+                double *dst = Gs + (size_t)(zs & 1) * 19 * NT + tid;
+#pragma unroll
+                for (int k = 0; k < 19; k++) dst[k * NT] = G[k];
+            }
+            if (store_all || (mine && band)) phi_out[(long long)zs * pl + idx] = v;
+        }
+        if (has_extra) {
+            double v;
+            switch (my_flags & 3) {
+            case 0: v = sum19(E); break;
+            case 1: v = sum19_mirror<1>(E); break;
+            case 2: v = sum19_mirror<2>(E); break;
+            default: v = sum19_mirror<3>(E); break;
+            }
+            if (my_flags & 4) v = v - P.phase_gradient;
+            rp[my_ring] = v;
+            if (mine && (my_flags & 8)) {   // non-bulk nodes inside the tile are all within the band
+                const int px = my_ring % RW, py = my_ring / RW;
+                phi_out[(long long)zs * pl + (long long)(iy0 - 1 + py) * NX + (ix0 - 1 + px)] = v;
+            }
+        }
+    };
+
+    phase_plane(zs0 - 1, false);
+    phase_plane(zs0, true);
+
+    for (int zs = zs0; zs < zs1; zs++) {
+        double F[19];
+        if (interior) {   // issued early: in flight during the phi phase and the barrier
+            const double *src = fin + pop_index(g, zs, 0, idx);
+#pragma unroll
+            for (int k = 0; k < 19; k++) F[k] = __ldg(src + k * pl);
+        }
+        phase_plane(zs + 1, true);
+        __syncthreads();   // phi ring planes zs-1, zs, zs+1 complete
+        if (interior) {
+            double G[19], PH[19];
+            {
+                constexpr int CX[19] = LBM3_CX, CY[19] = LBM3_CY, CZ[19] = LBM3_CZ;
+#pragma unroll
+                for (int k = 0; k < 19; k++)
+                    PH[k] = ring[(size_t)((zs + CZ[k]) & 3) * RP + (ty + 1 + CY[k]) * RW + tx + 1 + CX[k]];
+            }
+            const double *gs = Gs + (size_t)(zs & 1) * 19 * NT + tid;
+#pragma unroll
+            for (int k = 0; k < 19; k++) G[k] = gs[k * NT];
+            collide_push_node<FXY, WRITE, 1>(g, P, F, G, PH, fout, gout, o, zs, ix, iy);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------
+// Fourth fused kernel: interior nodes only (rim by k_collide_rim), g and the extra (halo / non-bulk)
+// positions prefetched with cp.async one plane ahead into shared memory -- no registers held by loads in
+// flight --, f loaded with plain LDG at the top of the iteration, array form of the collision.
+// Shared memory per 128-thread block (TY = 4): g 2 x 19.5 KB, extras 19.5 KB, phi ring 6.5 KB = 65 KB,
+// so three blocks (12 warps) fit on an SM at <= 168 registers and one block's barrier is covered by the
+// other two.
+template <int TY>
+struct Fused4Smem {
+    static constexpr int NT = FT_TX * TY;
+    static constexpr int RW = FT_TX + 2, RH = TY + 2, RP = RW * RH;
+    static constexpr size_t doubles = (size_t)2 * 19 * NT + (size_t)19 * FT_NE + (size_t)4 * RP;
+    static constexpr size_t bytes = doubles * sizeof(double) + (size_t)3 * FT_NE * sizeof(int) + 16;
+};
+
+template <int TY, bool FXY, bool WRITE, int MINB>
+__global__ void __launch_bounds__(FT_TX *TY, MINB)
+    k_fused4_step(Geom g, Params P, const double *__restrict__ fin, const double *__restrict__ gin, double *__restrict__ fout,
+                  double *__restrict__ gout, FieldsOut o, double *__restrict__ phi_out, int zs_begin, int zs_end, int chunk)
+{
+    using S = Fused4Smem<TY>;
+    constexpr int NT = S::NT, RW = S::RW, RP = S::RP;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    double *Gs = reinterpret_cast<double *>(smem_raw);       // [2][19][NT]
+    double *Es = Gs + 2 * 19 * NT;                            // [19][FT_NE]
+    double *ring = Es + 19 * FT_NE;                           // [4][RP]
+    int *e_owner = reinterpret_cast<int *>(ring + 4 * RP);
+    int *e_ring = e_owner + FT_NE;
+    int *e_flags = e_ring + FT_NE;
+    int *n_extra_p = e_flags + FT_NE;
+
+    const int NX = g.nx, NY = g.ny;
+    const int tid = threadIdx.x, tx = tid & 31, ty = tid >> 5;
+    const int ix0 = blockIdx.x * FT_TX, iy0 = blockIdx.y * TY;
+    const int ix = ix0 + tx, iy = iy0 + ty;
+    const bool in_dom = ix < NX && iy < NY;
+    const bool bulk = in_dom && ix >= 1 && ix <= NX - 2 && iy >= 1 && iy <= NY - 2;
+    const bool interior = in_dom && ix >= 2 && ix <= NX - 3 && iy >= 2 && iy <= NY - 3;
+    const bool band = ix <= 2 || ix >= NX - 3 || iy <= 2 || iy >= NY - 3;
+    const long long idx = (long long)iy * NX + ix;
+    const long long pl = g.pl;
+    const int zs0 = zs_begin + blockIdx.z * chunk;
+    const int zs1 = min(zs0 + chunk, zs_end);
+    if (zs0 >= zs1) return;
+
+    if (tid == 0) *n_extra_p = 0;
+    __syncthreads();
+    for (int p = tid; p < RP; p += NT) {
+        const int px = p % RW, py = p / RW;
+        const int ex = ix0 - 1 + px, ey = iy0 - 1 + py;
+        if (ex < 0 || ex > NX - 1 || ey < 0 || ey > NY - 1) continue;
+        const bool inside = px >= 1 && px <= FT_TX && py >= 1 && py <= TY;
+        const bool ebulk = ex >= 1 && ex <= NX - 2 && ey >= 1 && ey <= NY - 2;
+        if (inside && ebulk) continue;
+        const int ox = min(max(ex, 1), NX - 2), oy = min(max(ey, 1), NY - 2);
+        const int slot = atomicAdd(n_extra_p, 1);
+        e_owner[slot] = oy * NX + ox;
+        e_ring[slot] = p;
+        e_flags[slot] = (ex == 0 ? 1 : 0) | (ey == 0 ? 2 : 0) | ((ex == NX - 1 || ey == NY - 1) ? 4 : 0) | (inside ? 8 : 0);
+    }
+    __syncthreads();
+    const int n_extra = *n_extra_p;
+    const bool has_extra = tid < n_extra;
+    const int my_owner = has_extra ? e_owner[tid] : 0;
+    const int my_ring = has_extra ? e_ring[tid] : 0;
+    const int my_flags = has_extra ? e_flags[tid] : 0;
+
+    auto myG = [&](int zs) { return Gs + (size_t)(zs & 1) * 19 * NT + tid; };
+    double *myE = Es + tid;
+    auto load_g = [&](int zs) {
+        if (bulk) {
+            const double *src = gin + pop_index(g, zs, 0, idx);
+            double *dst = myG(zs);
+#pragma unroll
+            for (int k = 0; k < 19; k++) cp_async8(dst + k * NT, src + k * pl);
+        }
+    };
+    auto load_e = [&](int zs) {
+        if (has_extra) {
+            const double *src = gin + pop_index(g, zs, 0, my_owner);
+#pragma unroll
+            for (int k = 0; k < 19; k++) cp_async8(myE + k * FT_NE, src + k * pl);
+        }
+    };
+    auto phase_own = [&](int zs) {
+        const bool mine = (zs >= zs0 && zs < zs1) || (zs == zs0 - 1 && zs0 == zs_begin) || (zs == zs1 && zs1 == zs_end);
+        if (bulk) {
+            const double v = smem_sum19<0>(myG(zs), NT);
+            ring[(size_t)(zs & 3) * RP + (ty + 1) * RW + tx + 1] = v;
+            if (mine && (band || (WRITE && zs >= 2 && zs < g.nz + 2))) phi_out[(long long)zs * pl + idx] = v;
+        }
+    };
+    auto phase_extra = [&](int zs) {
+        const bool mine = (zs >= zs0 && zs < zs1) || (zs == zs0 - 1 && zs0 == zs_begin) || (zs == zs1 && zs1 == zs_end);
+        if (has_extra) {
+            double v;
+            switch (my_flags & 3) {
+            case 0: v = smem_sum19<0>(myE, FT_NE); break;
+            case 1: v = smem_sum19<1>(myE, FT_NE); break;
+            case 2: v = smem_sum19<2>(myE, FT_NE); break;
+            default: v = smem_sum19<3>(myE, FT_NE); break;
+            }
+            if (my_flags & 4) v = v - P.phase_gradient;
+            ring[(size_t)(zs & 3) * RP + my_ring] = v;
+            if (mine && (my_flags & 8)) {
+                const int px = my_ring % RW, py = my_ring / RW;
+                phi_out[(long long)zs * pl + (long long)(iy0 - 1 + py) * NX + (ix0 - 1 + px)] = v;
+            }
+        }
+    };
+
+    // prologue: phi(zs0-1), phi(zs0); g(zs0) kept; g(zs0+1) and extras(zs0+1) in flight
+    load_e(zs0 - 1);
+    load_g(zs0 - 1);
+    load_g(zs0);
+    cp_async_commit();
+    cp_async_wait<0>();
+    phase_own(zs0 - 1);
+    phase_extra(zs0 - 1);
+    phase_own(zs0);
+    load_e(zs0);
+    cp_async_commit();
+    cp_async_wait<0>();
+    phase_extra(zs0);
+    load_e(zs0 + 1);
+    load_g(zs0 + 1);     // slot of plane zs0-1, already summed
+    cp_async_commit();
+
+    for (int zs = zs0; zs < zs1; zs++) {
+        double F[19];
+        if (interior) {
+            const double *src = fin + pop_index(g, zs, 0, idx);
+#pragma unroll
+            for (int k = 0; k < 19; k++) F[k] = __ldg(src + k * pl);
+        }
+        cp_async_wait<0>();          // g(zs+1), extras(zs+1)
+        phase_own(zs + 1);
+        phase_extra(zs + 1);
+        const bool more = zs + 1 < zs1;
+        if (more) load_e(zs + 2);    // the extras stage is free again
+        __syncthreads();             // phi ring planes zs-1, zs, zs+1 complete
+        double G[19];
+        if (interior) {
+            const double *gs = myG(zs);
+#pragma unroll
+            for (int k = 0; k < 19; k++) G[k] = gs[k * NT];
+        }
+        if (more) load_g(zs + 2);    // into the slot of plane zs, whose values now sit in registers
+        cp_async_commit();
+        if (interior) {
+            double PH[19];
+            constexpr int CX[19] = LBM3_CX, CY[19] = LBM3_CY, CZ[19] = LBM3_CZ;
+#pragma unroll
+            for (int k = 0; k < 19; k++)
+                PH[k] = ring[(size_t)((zs + CZ[k]) & 3) * RP + (ty + 1 + CY[k]) * RW + tx + 1 + CX[k]];
+            collide_push_node<FXY, WRITE, 1>(g, P, F, G, PH, fout, gout, o, zs, ix, iy);
+        }
+    }
+    cp_async_wait<0>();
+}
+
+// ---------------------------------------------------------------------------
+// Fifth fused kernel: as k_fused4_step, but the collision goes through collide_streamed() with g read
+// from shared memory at the point of use (cheap there, unlike from global memory), so nothing but the 19 f
+// values is held in registers; g gets a third slot so that plane zs+2 can be prefetched while plane zs is
+// still being read; the extra positions are loaded synchronously (a minority of threads).
+template <int TY>
+struct Fused5Smem {
+    static constexpr int NT = FT_TX * TY;
+    static constexpr int RW = FT_TX + 2, RH = TY + 2, RP = RW * RH;
+    static constexpr size_t doubles = (size_t)3 * 19 * NT + (size_t)4 * RP;
+    static constexpr size_t bytes = doubles * sizeof(double) + (size_t)3 * FT_NE * sizeof(int) + 16;
+};
+
+template <int TY, bool FXY, bool WRITE, int MINB>
+__global__ void __launch_bounds__(FT_TX *TY, MINB)
+    k_fused5_step(Geom g, Params P, const double *__restrict__ fin, const double *__restrict__ gin, double *__restrict__ fout,
+                  double *__restrict__ gout, FieldsOut o, double *__restrict__ phi_out, int zs_begin, int zs_end, int chunk)
+{
+    using S = Fused5Smem<TY>;
+    constexpr int NT = S::NT, RW = S::RW, RP = S::RP;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    double *Gs = reinterpret_cast<double *>(smem_raw);       // [3][19][NT]
+    double *ring = Gs + 3 * 19 * NT;                          // [4][RP]
+    int *e_owner = reinterpret_cast<int *>(ring + 4 * RP);
+    int *e_ring = e_owner + FT_NE;
+    int *e_flags = e_ring + FT_NE;
+    int *n_extra_p = e_flags + FT_NE;
+
+    const int NX = g.nx, NY = g.ny;
+    const int tid = threadIdx.x, tx = tid & 31, ty = tid >> 5;
+    const int ix0 = blockIdx.x * FT_TX, iy0 = blockIdx.y * TY;
+    const int ix = ix0 + tx, iy = iy0 + ty;
+    const bool in_dom = ix < NX && iy < NY;
+    const bool bulk = in_dom && ix >= 1 && ix <= NX - 2 && iy >= 1 && iy <= NY - 2;
+    const bool interior = in_dom && ix >= 2 && ix <= NX - 3 && iy >= 2 && iy <= NY - 3;
+    const bool band = ix <= 2 || ix >= NX - 3 || iy <= 2 || iy >= NY - 3;
+    const long long idx = (long long)iy * NX + ix;
+    const long long pl = g.pl;
+    const int zs0 = zs_begin + blockIdx.z * chunk;
+    const int zs1 = min(zs0 + chunk, zs_end);
+    if (zs0 >= zs1) return;
+
+    if (tid == 0) *n_extra_p = 0;
+    __syncthreads();
+    for (int p = tid; p < RP; p += NT) {
+        const int px = p % RW, py = p / RW;
+        const int ex = ix0 - 1 + px, ey = iy0 - 1 + py;
+        if (ex < 0 || ex > NX - 1 || ey < 0 || ey > NY - 1) continue;
+        const bool inside = px >= 1 && px <= FT_TX && py >= 1 && py <= TY;
+        const bool ebulk = ex >= 1 && ex <= NX - 2 && ey >= 1 && ey <= NY - 2;
+        if (inside && ebulk) continue;
+        const int ox = min(max(ex, 1), NX - 2), oy = min(max(ey, 1), NY - 2);
+        const int slot = atomicAdd(n_extra_p, 1);
+        e_owner[slot] = oy * NX + ox;
+        e_ring[slot] = p;
+        e_flags[slot] = (ex == 0 ? 1 : 0) | (ey == 0 ? 2 : 0) | ((ex == NX - 1 || ey == NY - 1) ? 4 : 0) | (inside ? 8 : 0);
+    }
+    __syncthreads();
+    const int n_extra = *n_extra_p;
+    const bool has_extra = tid < n_extra;
+    const int my_owner = has_extra ? e_owner[tid] : 0;
+    const int my_ring = has_extra ? e_ring[tid] : 0;
+    const int my_flags = has_extra ? e_flags[tid] : 0;
+
+    auto myG = [&](int zs) { return Gs + (size_t)(zs % 3) * 19 * NT + tid; };
+    auto load_g = [&](int zs) {
+        if (bulk) {
+            const double *src = gin + pop_index(g, zs, 0, idx);
+            double *dst = myG(zs);
+#pragma unroll
+            for (int k = 0; k < 19; k++) cp_async8(dst + k * NT, src + k * pl);
+        }
+    };
+    auto phase_own = [&](int zs) {
+        const bool mine = (zs >= zs0 && zs < zs1) || (zs == zs0 - 1 && zs0 == zs_begin) || (zs == zs1 && zs1 == zs_end);
+        if (bulk) {
+            const double v = smem_sum19<0>(myG(zs), NT);
+            ring[(size_t)(zs & 3) * RP + (ty + 1) * RW + tx + 1] = v;
+            if (mine && (band || (WRITE && zs >= 2 && zs < g.nz + 2))) phi_out[(long long)zs * pl + idx] = v;
+        }
+    };
+    auto phase_extra = [&](int zs) {   // synchronous: only some threads have an extra position
+        const bool mine = (zs >= zs0 && zs < zs1) || (zs == zs0 - 1 && zs0 == zs_begin) || (zs == zs1 && zs1 == zs_end);
+        if (has_extra) {
+            double E[19];
+            const double *src = gin + pop_index(g, zs, 0, my_owner);
+#pragma unroll
+            for (int k = 0; k < 19; k++) E[k] = __ldcg(src + k * pl);
+            double v;
+            switch (my_flags & 3) {
+            case 0: v = sum19(E); break;
+            case 1: v = sum19_mirror<1>(E); break;
+            case 2: v = sum19_mirror<2>(E); break;
+            default: v = sum19_mirror<3>(E); break;
+            }
+            if (my_flags & 4) v = v - P.phase_gradient;
+            ring[(size_t)(zs & 3) * RP + my_ring] = v;
+            if (mine && (my_flags & 8)) {
+                const int px = my_ring % RW, py = my_ring / RW;
+                phi_out[(long long)zs * pl + (long long)(iy0 - 1 + py) * NX + (ix0 - 1 + px)] = v;
+            }
+        }
+    };
+
+    // prologue: phi(zs0-1), phi(zs0); g(zs0) kept, g(zs0+1) in flight
+    load_g(zs0 - 1);
+    load_g(zs0);
+    cp_async_commit();
+    load_g(zs0 + 1);
+    cp_async_commit();
+    phase_extra(zs0 - 1);
+    phase_extra(zs0);
+    cp_async_wait<1>();
+    phase_own(zs0 - 1);
+    phase_own(zs0);
+
+    for (int zs = zs0; zs < zs1; zs++) {
+        double F[19];
+        if (interior) {
+            const double *src = fin + pop_index(g, zs, 0, idx);
+#pragma unroll
+            for (int k = 0; k < 19; k++) F[k] = __ldcg(src + k * pl);
+        }
+        const bool more = zs + 1 < zs1;
+        if (more) load_g(zs + 2);    // third slot: plane zs-1 was collided in the previous iteration
+        cp_async_commit();
+        phase_extra(zs + 1);
+        cp_async_wait<1>();          // g(zs+1)
+        phase_own(zs + 1);
+        __syncthreads();             // phi ring planes zs-1, zs, zs+1 complete
+        if (interior) {
+            double PH[19];
+            constexpr int CX[19] = LBM3_CX, CY[19] = LBM3_CY, CZ[19] = LBM3_CZ;
+#pragma unroll
+            for (int k = 0; k < 19; k++)
+                PH[k] = ring[(size_t)((zs + CZ[k]) & 3) * RP + (ty + 1 + CY[k]) * RW + tx + 1 + CX[k]];
+            const double *gs = myG(zs);
+            collide_push_node_streamed<FXY, WRITE, 1>(g, P, F, [gs](int k) { return gs[k * NT]; }, PH, fout, gout, o, zs, ix, iy);
+        }
+    }
+    cp_async_wait<0>();
+}
+
 }  // namespace lbm3
 #endif

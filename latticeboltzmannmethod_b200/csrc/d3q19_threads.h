@@ -192,8 +192,13 @@ struct PushInterior {
     {
         constexpr int CX[19] = LBM3_CX, CY[19] = LBM3_CY, CZ[19] = LBM3_CZ;
         const long long off = (long long)(CZ[K] * 19 + K) * g.pl + (CY[K] * g.nx + CX[K]);
+#if defined(__CUDA_ARCH__)
+        __stcg(fo + off, fv);   // streaming stores: keep them out of L1
+        __stcg(go + off, gv);
+#else
         fo[off] = fv;
         go[off] = gv;
+#endif
     }
 };
 struct PushBorder {
@@ -206,7 +211,7 @@ struct PushBorder {
 
 // One bulk node whose f populations are in registers (F), whose g populations come from `getG`
 // and whose 19 neighbour phase values are in PH.  Same reference lines as collide_push_thread.
-template <bool FXY, bool WRITE, class GetG>
+template <bool FXY, bool WRITE, int PART = 0, class GetG>
 LBM_HD void collide_push_node_streamed(const Geom &g, const Params &P, double *F, GetG getG, const double *PH, double *fout,
                                        double *gout, const FieldsOut &o, int zs, int ix, int iy)
 {
@@ -215,13 +220,13 @@ LBM_HD void collide_push_node_streamed(const Geom &g, const Params &P, double *F
     double gx, gy, gz, lap;
     stencils(PH, gx, gy, gz, lap);
     const bool own = zs >= 2 && zs < g.nz + 2;
-    if (WRITE && own) {
+    if (WRITE && own && PART != 1) {
         if (iy == 1) mirror_fields<2>(F, P, o, (long long)(zs - 2) * g.pl + ix);
         if (ix == 1) mirror_fields<1>(F, P, o, (long long)(zs - 2) * g.pl + (long long)iy * NX);
         if (ix == 1 && iy == 1) mirror_fields<3>(F, P, o, (long long)(zs - 2) * g.pl);
     }
     double rho, ux, uy, uz;
-    const bool border = ix == 1 || iy == 1 || ix == NX - 2 || iy == NY - 2;
+    const bool border = PART == 2 || (PART == 0 && (ix == 1 || iy == 1 || ix == NX - 2 || iy == NY - 2));
     if (!border) {
         const long long base = pop_index(g, zs, 0, idx);
         collide_streamed<FXY>(F, getG, PushInterior{g, fout + base, gout + base}, PH[0], gx, gy, gz, lap, P, rho, ux, uy, uz);
