@@ -166,6 +166,25 @@ lbm_status lbm_slab_after_init(lbm_ctx *ctx);
 lbm_status lbm_slab_collide(lbm_ctx *ctx, int write_fields); /* then exchange F,G, then lbm_slab_finish */
 lbm_status lbm_slab_finish(lbm_ctx *ctx);
 
+/* ---- allocation-free population sums ----
+ * No counterpart in the reference (its sums run on the host over arrays the program already owns).
+ * Same six sums as lbm_diagnostics -- sum f, sum f*cx, sum f*cy, sum f*cz, sum g, number of NaNs --
+ * over n_nodes consecutive nodes of structure-of-arrays populations (direction k of node i at
+ * f_dev[i + k*stride_k]; q = 9 or 19; g_dev may be NULL), written to sums6_dev (device memory, 6 doubles),
+ * queued on cuda_stream.  For callers that cannot allocate -- all device memory already committed to
+ * their own pool, or running where the implicit device-wide wait of cudaMalloc/cudaFree is not
+ * acceptable: it needs no context, and calls no cudaMalloc, cudaFree or any allocating routine.  The block
+ * partials live in a file-scope device array of LBM_NOALLOC_MAX_BLOCKS*6 doubles (768 KiB) that every
+ * GPU loading the library holds until exit; one block covers 8192 nodes, so n_nodes is limited to
+ * LBM_NOALLOC_MAX_BLOCKS*8192 = 134 217 728 (LBM_EINVAL beyond that).  All calls share that array: calls
+ * whose kernels overlap on one GPU race -- serialise them.  Nothing needs clearing between calls (each
+ * call overwrites every entry it reads).  The first call on a device looks the array's address up
+ * (cudaGetSymbolAddress); make that first call before any stream capture. */
+#define LBM_NOALLOC_MAX_BLOCKS 16384
+lbm_status lbm_population_sums_noalloc(const double *f_dev, const double *g_dev, int q, size_t n_nodes, size_t stride_k,
+                                       void *cuda_stream, double *sums6_dev);
+const char *lbm_noalloc_last_error(void);
+
 #ifdef __cplusplus
 }
 #endif

@@ -85,6 +85,8 @@ def load_library():
         "lbm_slab_after_init": (ci, [vp]),
         "lbm_slab_collide": (ci, [vp, ci]),
         "lbm_slab_finish": (ci, [vp]),
+        "lbm_population_sums_noalloc": (ci, [vp, vp, ci, sz, sz, vp, vp]),
+        "lbm_noalloc_last_error": (C.c_char_p, []),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)          # AttributeError if the library does not export it
@@ -98,7 +100,8 @@ EXPORTS = ["lbm_config_default", "lbm_create", "lbm_destroy", "lbm_last_error", 
            "lbm_sync", "lbm_diagnostics", "lbm_get_stream", "lbm_set_stream", "lbm_launch_count", "lbm_profile",
            "lbm_profile_report", "lbm_host_alloc",
            "lbm_host_free", "lbm_comm_unique_id", "lbm_comm_attach", "lbm_slab_halo", "lbm_slab_init_fields",
-           "lbm_slab_init_pops", "lbm_slab_after_init", "lbm_slab_collide", "lbm_slab_finish"]
+           "lbm_slab_init_pops", "lbm_slab_after_init", "lbm_slab_collide", "lbm_slab_finish",
+           "lbm_population_sums_noalloc", "lbm_noalloc_last_error"]
 
 
 def default_config(model):
@@ -239,6 +242,15 @@ class Context:
 
     def slab_finish(self):
         self._ck(self.L.lbm_slab_finish(self.h))
+
+
+def population_sums_noalloc(f_dev, g_dev, q, n_nodes, stride_k, cuda_stream, sums6_dev):
+    """lbm_population_sums_noalloc: raw device addresses in, six sums written to device memory; allocates nothing."""
+    L = load_library()
+    st = L.lbm_population_sums_noalloc(C.c_void_p(f_dev), C.c_void_p(g_dev) if g_dev else None, int(q), int(n_nodes),
+                                       int(stride_k), C.c_void_p(cuda_stream) if cuda_stream else None, C.c_void_p(sums6_dev))
+    if st:
+        raise LbmError(st, (L.lbm_noalloc_last_error() or b"").decode())
 
 
 def comm_unique_id():

@@ -15,7 +15,7 @@ PKG = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(PKG)
 CSRC = os.path.join(PKG, "csrc")
 LIB = os.path.join(PKG, "liblbm_b200.so")
-SOURCES = ["lbm_api.cu", "d3q19_binary.cu", "d2q9_models.cu", "diagnostics.cu"]
+SOURCES = ["lbm_api.cu", "d3q19_binary.cu", "d2q9_models.cu", "diagnostics.cu", "noalloc.cu"]
 HOST_CXX = "/usr/bin/g++"   # the image's /opt/gcc toolchain links libstdc++ statically; do not use it
 
 
