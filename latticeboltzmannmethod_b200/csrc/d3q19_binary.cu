@@ -54,7 +54,7 @@ __global__ void __launch_bounds__(128, MINB) k_collide_push_occ(Geom g, Params P
 // (nodes 2..NX-3 x 2..NY-3: every push is a plain shifted store), which removes the control-flow merges
 // and register moves the folded boundary path costs every thread; the rim kernel runs the one-node rim
 // (and, on output steps, the wall-node fields) -- 2(NX+NY) nodes per plane.
-template <bool FXY, bool WRITE, int MINB>
+template <bool FXY, bool WRITE, int MINB, bool XRIM = false>
 __global__ void __launch_bounds__(128, MINB) k_collide_interior(Geom g, Params P, const double *__restrict__ fin,
                                                                 const double *__restrict__ gin, const double *__restrict__ phi,
                                                                 double *__restrict__ fout, double *__restrict__ gout, FieldsOut o,
@@ -64,7 +64,9 @@ __global__ void __launch_bounds__(128, MINB) k_collide_interior(Geom g, Params P
     const int NX = g.nx, NY = g.ny;
     if (idx >= (long long)NX * NY) return;
     const int ix = (int)(idx % NX), iy = (int)(idx / NX), zs = zs0 + blockIdx.y;
-    if (ix < 2 || ix > NX - 3 || iy < 2 || iy > NY - 3) return;
+    // XRIM: the columns iX = 1 and iX = NX-2 are done here too (PART 3), only the rows iY = 1, NY-2 are left
+    // to the rim kernel -- column accesses from the rim kernel cost a 32-byte sector per 8-byte value
+    if (iy < 2 || iy > NY - 3 || ix < (XRIM ? 1 : 2) || ix > NX - (XRIM ? 2 : 3)) return;
     const long long pl = g.pl;
     double F[19], G[19], PH[19];
     const double *pf = fin + lbm3::pop_index(g, zs, 0, idx), *pg = gin + lbm3::pop_index(g, zs, 0, idx);
@@ -75,16 +77,16 @@ __global__ void __launch_bounds__(128, MINB) k_collide_interior(Geom g, Params P
         G[k] = __ldg(pg + k * pl);
         PH[k] = __ldg(phi + (long long)(zs + CZ[k]) * pl + idx + CY[k] * NX + CX[k]);
     }
-    lbm3::collide_push_node<FXY, WRITE, 1>(g, P, F, G, PH, fout, gout, o, zs, ix, iy);
+    lbm3::collide_push_node<FXY, WRITE, XRIM ? 3 : 1>(g, P, F, G, PH, fout, gout, o, zs, ix, iy);
 }
 
-template <bool FXY, bool WRITE>
+template <bool FXY, bool WRITE, bool ROWS_ONLY = false>
 __global__ void __launch_bounds__(128) k_collide_rim(Geom g, Params P, const double *__restrict__ fin,
                                                      const double *__restrict__ gin, const double *__restrict__ phi,
                                                      double *__restrict__ fout, double *__restrict__ gout, FieldsOut o, int zs0)
 {
     const int NX = g.nx, NY = g.ny, zs = zs0 + blockIdx.y;
-    const int rows = 2 * (NX - 2), cols = 2 * (NY - 4 > 0 ? NY - 4 : 0);
+    const int rows = 2 * (NX - 2), cols = ROWS_ONLY ? 0 : 2 * (NY - 4 > 0 ? NY - 4 : 0);
     int t = blockIdx.x * 128 + threadIdx.x;
     int ix, iy;
     if (t < rows) {
@@ -541,6 +543,36 @@ public:
         return rt_.launched("k_collide_rim");
     }
 
+    // default collide: interior incl. the x columns (168 registers, 12 warps/SM) + rim rows, for `count`
+    // storage planes starting at zs0; the phase field of planes zs0-1 .. zs0+count must be up to date
+    lbm_status collide_default(int zs0, int count, int write_fields)
+    {
+        if (count <= 0) return LBM_OK;
+        const int a = cur_, b = 1 - cur_;
+        const FieldsOut o = fields_out();
+        const dim3 gi((unsigned)(((long long)g_.nx * g_.ny + 127) / 128), count);
+        const int rim = 2 * (g_.nx - 2) + g_.nx + g_.ny - 1;
+        const dim3 gr((rim + 127) / 128, count);
+#define LBM_LAUNCH_DEFAULT(FXY, WR)                                                                                            \
+    do {                                                                                                                       \
+        rt_.about_to_launch();                                                                                                 \
+        if (cfg_.kernel_variant == 65)                                                                                         \
+            k_collide_interior<FXY, WR, 2, true><<<gi, 128, 0, rt_.stream>>>(g_, P_, f_[a], gq_[a], phi_, f_[b], gq_[b], o, zs0); \
+        else                                                                                                                   \
+            k_collide_interior<FXY, WR, 3, true><<<gi, 128, 0, rt_.stream>>>(g_, P_, f_[a], gq_[a], phi_, f_[b], gq_[b], o, zs0); \
+        LBM_TRY(rt_.launched("k_collide_interior"));                                                                           \
+        rt_.about_to_launch();                                                                                                 \
+        k_collide_rim<FXY, WR, true><<<gr, 128, 0, rt_.stream>>>(g_, P_, f_[a], gq_[a], phi_, f_[b], gq_[b], o, zs0);           \
+    } while (0)
+        if (fxy_) {
+            if (write_fields) LBM_LAUNCH_DEFAULT(true, true); else LBM_LAUNCH_DEFAULT(true, false);
+        } else {
+            if (write_fields) LBM_LAUNCH_DEFAULT(false, true); else LBM_LAUNCH_DEFAULT(false, false);
+        }
+#undef LBM_LAUNCH_DEFAULT
+        return rt_.launched("k_collide_rim");
+    }
+
     lbm_status slab_collide(int write_fields) override
     {
         switch (cfg_.kernel_variant) {
@@ -604,7 +636,8 @@ public:
             LBM_CUDA(rt_, cudaStreamWaitEvent(rt_.stream, ev_join_, 0));
             return LBM_OK;
         }
-        if (cfg_.kernel_variant == 0 || (cfg_.kernel_variant >= 60 && cfg_.kernel_variant <= 62)) {
+        if (cfg_.kernel_variant == 0 || cfg_.kernel_variant == 65) return collide_default(1, g_.nz + 2, write_fields);
+        if (cfg_.kernel_variant >= 60 && cfg_.kernel_variant <= 62) {
             const dim3 gi((unsigned)(((long long)g_.nx * g_.ny + 127) / 128), g_.nz + 2);
             const int rim = 2 * (g_.nx - 2) + 2 * std::max(0, g_.ny - 4) + g_.nx + g_.ny - 1;
             const dim3 gr((rim + 127) / 128, g_.nz + 2);
@@ -612,7 +645,7 @@ public:
     do {                                                                                                                     \
         if (cfg_.kernel_variant == 60)                                                                                       \
             k_collide_interior<FXY, WR, 2><<<gi, 128, 0, rt_.stream>>>(g_, P_, f_[a], gq_[a], phi_, f_[b], gq_[b], o, 1);     \
-        else if (cfg_.kernel_variant == 61 || cfg_.kernel_variant == 0)                                                      \
+        else if (cfg_.kernel_variant == 61)                                                                                  \
             k_collide_interior<FXY, WR, 3><<<gi, 128, 0, rt_.stream>>>(g_, P_, f_[a], gq_[a], phi_, f_[b], gq_[b], o, 1);     \
         else                                                                                                                 \
             k_collide_interior<FXY, WR, 4><<<gi, 128, 0, rt_.stream>>>(g_, P_, f_[a], gq_[a], phi_, f_[b], gq_[b], o, 1);     \
@@ -749,8 +782,9 @@ public:
     }
 
     // ---- exchange: with itself (one slab, z periodic) or with the ring neighbours over NCCL ----
-    lbm_status exchange(bool phi_only)
+    lbm_status exchange(bool phi_only, cudaStream_t st = nullptr)
     {
+        if (!st) st = rt_.stream;
         static const int kState[4][2] = {{LBM_HALO_S_F_UP, LBM_HALO_R_F_FROM_BELOW}, {LBM_HALO_S_G_UP, LBM_HALO_R_G_FROM_BELOW},
                                          {LBM_HALO_S_F_DOWN, LBM_HALO_R_F_FROM_ABOVE}, {LBM_HALO_S_G_DOWN, LBM_HALO_R_G_FROM_ABOVE}};
         static const int kPhi[2][2] = {{LBM_HALO_S_PHI_UP, LBM_HALO_R_PHI_FROM_BELOW}, {LBM_HALO_S_PHI_DOWN, LBM_HALO_R_PHI_FROM_ABOVE}};
@@ -762,7 +796,7 @@ public:
                 size_t ns, nr;
                 LBM_TRY(slab_halo(pairs[i][0], &s, &ns));
                 LBM_TRY(slab_halo(pairs[i][1], &r, &nr));
-                LBM_CUDA(rt_, cudaMemcpyAsync(r, s, ns * sizeof(double), cudaMemcpyDeviceToDevice, rt_.stream));
+                LBM_CUDA(rt_, cudaMemcpyAsync(r, s, ns * sizeof(double), cudaMemcpyDeviceToDevice, st));
             }
             return LBM_OK;
         }
@@ -778,14 +812,14 @@ public:
             size_t ns;
             LBM_TRY(slab_halo(pairs[i][0], &s, &ns));
             const bool to_up = i < npairs / 2;
-            rc = api->Send(s, ns, kNcclFloat64, to_up ? up : down, comm_, rt_.stream);
+            rc = api->Send(s, ns, kNcclFloat64, to_up ? up : down, comm_, st);
         }
         for (int i = 0; i < npairs && rc == 0; i++) {
             void *r;
             size_t nr;
             LBM_TRY(slab_halo(pairs[i][1], &r, &nr));
             const bool from_below = i < npairs / 2;
-            rc = api->Recv(r, nr, kNcclFloat64, from_below ? down : up, comm_, rt_.stream);
+            rc = api->Recv(r, nr, kNcclFloat64, from_below ? down : up, comm_, st);
         }
         const int rc2 = api->GroupEnd();
         if (rc == 0) rc = rc2;
@@ -817,9 +851,36 @@ public:
         LBM_TRY(slab_finish());
         return slab_after_init();
     }
+    // One step with the halo exchange hidden behind the bulk of the collision (replaces the blocking
+    // MPI_Sendrecv chain of solver.hpp:893-928): phase field, then the four planes at either end of the
+    // slab -- everything the outgoing messages depend on --, then the exchange on a side stream while the
+    // main stream collides the planes in between.
+    lbm_status step_overlapped(int write_fields)
+    {
+        LBM_TRY(ensure_side_stream());
+        const int nz = g_.nz;
+        rt_.about_to_launch();
+        k_phase<<<plane_grid(nz + 4), kThreads, 0, rt_.stream>>>(g_, P_, gq_[cur_], phi_, 0);
+        LBM_TRY(rt_.launched("k_phase"));
+        LBM_TRY(collide_default(1, 4, write_fields));            // z = -1 .. 2
+        LBM_TRY(collide_default(nz - 1, 4, write_fields));       // z = nz-3 .. nz
+        LBM_CUDA(rt_, cudaEventRecord(ev_fork_, rt_.stream));
+        LBM_CUDA(rt_, cudaStreamWaitEvent(side_, ev_fork_, 0));
+        LBM_TRY(exchange(false, side_));
+        LBM_CUDA(rt_, cudaEventRecord(ev_join_, side_));
+        LBM_TRY(collide_default(5, nz - 6, write_fields));       // z = 3 .. nz-4
+        LBM_CUDA(rt_, cudaStreamWaitEvent(rt_.stream, ev_join_, 0));
+        return slab_finish();
+    }
+
     lbm_status step(int nsteps) override
     {
+        const bool overlap = comm_ && cfg_.slab_count > 1 && (cfg_.kernel_variant == 0 || cfg_.kernel_variant == 65) && g_.nz >= 8;
         for (int t = 0; t < nsteps; t++) {
+            if (overlap) {
+                LBM_TRY(step_overlapped(t == nsteps - 1));
+                continue;
+            }
             LBM_TRY(slab_collide(t == nsteps - 1));
             LBM_TRY(exchange(false));
             LBM_TRY(slab_finish());

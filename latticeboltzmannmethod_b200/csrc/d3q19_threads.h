@@ -115,7 +115,9 @@ LBM_HD void mirror_fields(const double *F, const Params &P, const FieldsOut &o, 
 // ---- one bulk node whose 19+19 populations and 19 neighbour phase values are already in registers ----
 // PART 0: any bulk node; 1: a node at least two away from every mirror line / wall (no boundary code is
 // even compiled in: straight-line kernel for the interior); 2: a node of the one-node rim (always the
-// folded boundary push).
+// folded boundary push); 3: a node with 2 <= iY <= NY-3 and any bulk iX -- the x mirror line (iX = 1) and
+// the x wall (iX = NX-2) are folded in as an address select on the ten directions with cx != 0, so that
+// these two columns are stored by the same coalesced warps as their row neighbours.
 template <bool FXY, bool WRITE, int PART = 0>
 LBM_HD void collide_push_node(const Geom &g, const Params &P, double *F, double *G, const double *PH, double *fout,
                               double *gout, const FieldsOut &o, int zs, int ix, int iy)
@@ -126,9 +128,9 @@ LBM_HD void collide_push_node(const Geom &g, const Params &P, double *F, double 
     stencils(PH, gx, gy, gz, lap);
     const bool own = zs >= 2 && zs < g.nz + 2;
     if (WRITE && own && PART != 1) {
-        if (iy == 1) mirror_fields<2>(F, P, o, (long long)(zs - 2) * g.pl + ix);
+        if (PART != 3 && iy == 1) mirror_fields<2>(F, P, o, (long long)(zs - 2) * g.pl + ix);
         if (ix == 1) mirror_fields<1>(F, P, o, (long long)(zs - 2) * g.pl + (long long)iy * NX);
-        if (ix == 1 && iy == 1) mirror_fields<3>(F, P, o, (long long)(zs - 2) * g.pl);
+        if (PART != 3 && ix == 1 && iy == 1) mirror_fields<3>(F, P, o, (long long)(zs - 2) * g.pl);
     }
     double rho, ux, uy, uz;
     collide<FXY>(F, G, PH[0], gx, gy, gz, lap, P, rho, ux, uy, uz);
@@ -139,9 +141,20 @@ LBM_HD void collide_push_node(const Geom &g, const Params &P, double *F, double 
     const bool border = PART == 2 || (PART == 0 && (ix == 1 || iy == 1 || ix == NX - 2 || iy == NY - 2));
     if (!border) {
         const int CX[19] = LBM3_CX, CY[19] = LBM3_CY, CZ[19] = LBM3_CZ;
+        const int OPP[19] = {0, 2, 1, 4, 3, 6, 5, 10, 9, 8, 7, 14, 13, 12, 11, 18, 17, 16, 15};
+        const int SYMX[19] = {0, 2, 1, 3, 4, 5, 6, 8, 7, 10, 9, 11, 12, 13, 14, 16, 15, 18, 17};
+        const bool xlo = PART == 3 && ix == 1, xhi = PART == 3 && ix == NX - 2;
 #pragma unroll
         for (int k = 0; k < 19; k++) {
-            const long long t = pop_index(g, zs + CZ[k], k, idx + CY[k] * NX + CX[k]);
+            long long t = pop_index(g, zs + CZ[k], k, idx + CY[k] * NX + CX[k]);
+            if (PART == 3 && CX[k] == -1) {   // into the x mirror line: reflected, stays in column 1 (lattice.hpp:534-557)
+                const long long tm = pop_index(g, zs + CZ[k], SYMX[k], idx + CY[k] * NX);
+                t = xlo ? tm : t;
+            }
+            if (PART == 3 && CX[k] == 1) {    // into the x wall: back to its own node reversed (lattice.hpp:609-626)
+                const long long tb = pop_index(g, zs, OPP[k], idx);
+                t = xhi ? tb : t;
+            }
             fout[t] = F[k];
             gout[t] = G[k];
         }
@@ -180,6 +193,32 @@ LBM_HD void collide_push_thread(const Geom &g, const Params &P, const double *fi
         for (int k = 0; k < 19; k++) PH[k] = phi[(long long)(zs + CZ[k]) * g.pl + idx + CY[k] * NX + CX[k]];
     }
     collide_push_node<FXY, WRITE>(g, P, F, G, PH, fout, gout, o, zs, ix, iy);
+}
+
+// the default kernel pair as one per-node function (CPU unit test): rows iY = 1 and NY-2 take the rim
+// path, every other bulk node the PART 3 path of k_collide_interior
+template <bool FXY, bool WRITE>
+LBM_HD void collide_push_thread_rows(const Geom &g, const Params &P, const double *fin, const double *gin,
+                                     const double *phi, double *fout, double *gout, const FieldsOut &o, int zs, int ix, int iy)
+{
+    const int NX = g.nx, NY = g.ny;
+    if (ix < 1 || ix > NX - 2 || iy < 1 || iy > NY - 2) {
+        if (WRITE && zs >= 2 && zs < g.nz + 2 && ix < NX && iy < NY && (ix == NX - 1 || iy == NY - 1)) {
+            const long long at = (long long)(zs - 2) * g.pl + (long long)iy * NX + ix;
+            o.rho[at] = P.rho_wall; o.ux[at] = 0.0; o.uy[at] = 0.0; o.uz[at] = 0.0;
+        }
+        return;
+    }
+    const long long idx = (long long)iy * NX + ix;
+    double F[19], G[19], PH[19];
+    const int CX[19] = LBM3_CX, CY[19] = LBM3_CY, CZ[19] = LBM3_CZ;
+    for (int k = 0; k < 19; k++) {
+        F[k] = fin[pop_index(g, zs, k, idx)];
+        G[k] = gin[pop_index(g, zs, k, idx)];
+        PH[k] = phi[(long long)(zs + CZ[k]) * g.pl + idx + CY[k] * NX + CX[k]];
+    }
+    if (iy == 1 || iy == NY - 2) collide_push_node<FXY, WRITE, 2>(g, P, F, G, PH, fout, gout, o, zs, ix, iy);
+    else collide_push_node<FXY, WRITE, 3>(g, P, F, G, PH, fout, gout, o, zs, ix, iy);
 }
 
 // ---- the same node update through collide_streamed() ----------------------

@@ -1,0 +1,91 @@
+"""The drop-in host programs (hosts/*.cpp, C++ through the C ABI) write the same files as the reference
+programs: SHA-256 of the text output against the fingerprints BASELINE.md section 3 recorded from the
+unmodified reference (binary.cpp, mrt.cpp, another_mrt.cpp), and the .vts of the QuarterChannel drop-in
+parsed back and compared with the golden field samples."""
+import hashlib
+import os
+import struct
+import subprocess
+
+import numpy as np
+import pytest
+
+import golden_lib as gl
+from conftest import ROOT
+
+pytestmark = pytest.mark.gpu
+BIN = os.path.join(ROOT, "hosts", "bin")
+
+
+def _sha16(path):
+    return hashlib.sha256(open(path, "rb").read()).hexdigest()[:16]
+
+
+def _run(prog, args, cwd, env=None):
+    exe = os.path.join(BIN, prog)
+    if not os.path.exists(exe):
+        subprocess.run(["make", "-C", os.path.join(ROOT, "hosts")], check=True, capture_output=True)
+    r = subprocess.run([exe] + args, cwd=cwd, capture_output=True, text=True, env=dict(os.environ, **(env or {})), timeout=900)
+    assert r.returncode == 0, r.stderr[-500:]
+    return r.stdout
+
+
+def test_binary_program_files(tmp_path):
+    out = _run("binary", [], str(tmp_path))
+    assert "Time is 20000" in out
+    assert _sha16(tmp_path / "phase020000.dat") == "97765059e339cfbc"
+    assert _sha16(tmp_path / "velocityx020000.dat") == "adfd2c25b9864189"
+    assert _sha16(tmp_path / "velocityy020000.dat") == "db6ef2429f6716b2"
+    assert _sha16(tmp_path / "phase000100.dat") == "836c201b829113f9"
+    assert len([f for f in os.listdir(tmp_path) if f.endswith(".dat")]) == 603
+
+
+def test_mrt_program_files(tmp_path):
+    os.mkdir(tmp_path / "tmp")
+    out = _run("mrt", ["10", "10"], str(tmp_path))
+    assert out.startswith("Omega=1\nOmega_bulk=1\n0\n")
+    assert _sha16(tmp_path / "tmp" / "phase000800.dat") == "07ca3fdcfdd7cb4c"
+    assert _sha16(tmp_path / "tmp" / "proba000800.dat") == "2070cdc933cf2c1d"
+
+
+def test_another_mrt_program_files(tmp_path):
+    os.mkdir(tmp_path / "tmp")
+    _run("another_mrt", [], str(tmp_path))
+    assert _sha16(tmp_path / "tmp" / "phase000500.dat") == "efa99204039552d8"
+    assert _sha16(tmp_path / "tmp" / "proba000500.dat") == "45c1dd18a5ef069e"
+
+
+def test_shanchen_program_runs(tmp_path):
+    """Text output at 6 digits: compared value by value with the golden (shared-exp) rho of step 1000."""
+    out = _run("shanchen", ["1000"], str(tmp_path))
+    assert "Iteration is 1000" in out
+    rows = [ln.split() for ln in open(tmp_path / "density01000.dat").read().splitlines() if ln.strip()]
+    got = np.array(rows, dtype=np.float64).ravel()
+    ref, ent = gl.samples("shanchen_sharedexp_t1000", "rho")
+    assert ent.get("whole")
+    want = np.array([float("%.6g" % v) for v in ref])
+    assert np.array_equal(got, want)
+
+
+def _read_vts(path):
+    raw = open(path, "rb").read()
+    head, rest = raw.split(b"<AppendedData encoding=\"raw\">", 1)
+    data = rest[rest.index(b"_") + 1:]
+    import re
+    arrays = {}
+    for m in re.finditer(rb'<DataArray type="(\w+)" Name="(\w+)"[^>]*offset="(\d+)"', head):
+        typ, name, off = m.group(1).decode(), m.group(2).decode(), int(m.group(3))
+        nbytes = struct.unpack("<Q", data[off:off + 8])[0]
+        arrays[name] = np.frombuffer(data[off + 8:off + 8 + nbytes], dtype=np.float64 if typ == "Float64" else np.float32)
+    return arrays
+
+
+def test_microchannel_quarter_vts(tmp_path):
+    out = _run("microchannel_quarter", [], str(tmp_path), env={"LBM_NUMTIME": "101"})
+    assert "Output is done on the step 100" in out
+    a = _read_vts(tmp_path / "phase00100.vts")
+    assert list(a) == ["Velocity", "Phase", "Density", "Points"]
+    vel = a["Velocity"].reshape(-1, 3)
+    for name, arr in (("phase", a["Phase"]), ("rho", a["Density"]), ("ux", vel[:, 0]), ("uy", vel[:, 1]), ("uz", vel[:, 2])):
+        assert gl.check("quarter_t100", name, np.ascontiguousarray(arr))[0] == 0, name
+    assert a["Points"].reshape(-1, 3)[28].tolist() == [1.0, 1.0, 0.0]

@@ -44,7 +44,7 @@ GENERAL = [0.04, 0.04, 1.0, 0.05, 0.0, 0.5, 1.0, 2.5, 0.7, 1e-5, -2e-5, 3e-5]
     ((12, 10, 6), GENERAL, 3, (1, 3, 10), True),
     ((4, 4, 2), GENERAL, 1, (1, 3), True),
 ])
-@pytest.mark.parametrize("streamed", [0, 1, 2])
+@pytest.mark.parametrize("streamed", [0, 1, 2, 3])
 def test_d3q19_threads_match_oracle(emu_libs, shape, params, width, steps, rand, streamed):
     nx, ny, nz = shape
     n = nx * ny * nz
