@@ -573,12 +573,51 @@ public:
         return rt_.launched("k_collide_rim");
     }
 
+    // fused interior (phase pulled in, x columns folded) + rim rows
+    template <int TY, int MINB>
+    lbm_status launch_fused6(int write_fields)
+    {
+        using S = lbm3::Fused6Smem<TY>;
+        const int a = cur_, b = 1 - cur_;
+        const int planes = g_.nz + 2;
+        const int gx = (g_.nx + lbm3::FT_TX - 1) / lbm3::FT_TX, gy = (g_.ny + TY - 1) / TY;
+        int nch = std::max((planes + 63) / 64, (148 * 24 + gx * gy - 1) / (gx * gy));
+        nch = std::max(1, std::min(nch, planes / 4));
+        const int chunk = (planes + nch - 1) / nch;
+        nch = (planes + chunk - 1) / chunk;
+        const dim3 grid(gx, gy, nch);
+        const FieldsOut o = fields_out();
+        const int rim = 2 * (g_.nx - 2) + g_.nx + g_.ny - 1;
+        const dim3 gr((rim + 127) / 128, g_.nz + 2);
+#define LBM_LAUNCH_FUSED6(FXY, WR)                                                                                        \
+    do {                                                                                                                  \
+        auto kern = lbm3::k_fused6_step<TY, FXY, WR, MINB>;                                                               \
+        LBM_CUDA(rt_, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::bytes));           \
+        rt_.about_to_launch();                                                                                            \
+        kern<<<grid, S::NT, S::bytes, rt_.stream>>>(g_, P_, f_[a], gq_[a], f_[b], gq_[b], o, phi_, 1, g_.nz + 3, chunk);  \
+        LBM_TRY(rt_.launched("k_fused6_step"));                                                                           \
+        rt_.about_to_launch();                                                                                            \
+        k_collide_rim<FXY, WR, true><<<gr, 128, 0, rt_.stream>>>(g_, P_, f_[a], gq_[a], phi_, f_[b], gq_[b], o, 1);        \
+    } while (0)
+        if (fxy_) {
+            if (write_fields) LBM_LAUNCH_FUSED6(true, true); else LBM_LAUNCH_FUSED6(true, false);
+        } else {
+            if (write_fields) LBM_LAUNCH_FUSED6(false, true); else LBM_LAUNCH_FUSED6(false, false);
+        }
+#undef LBM_LAUNCH_FUSED6
+        return rt_.launched("k_collide_rim");
+    }
+
     lbm_status slab_collide(int write_fields) override
     {
         switch (cfg_.kernel_variant) {
         case 70: return launch_fused3<4, 3, 3>(write_fields);
         case 71: return launch_fused3<4, 2, 3>(write_fields);
         case 72: return launch_fused3<8, 1, 3>(write_fields);
+        case 100: return launch_fused6<4, 3>(write_fields);
+        case 101: return launch_fused6<4, 2>(write_fields);
+        case 102: return launch_fused6<8, 1>(write_fields);
+        case 103: return launch_fused6<2, 6>(write_fields);
         case 90: return launch_fused3<4, 3, 5>(write_fields);
         case 91: return launch_fused3<4, 2, 5>(write_fields);
         case 92: return launch_fused3<8, 1, 5>(write_fields);

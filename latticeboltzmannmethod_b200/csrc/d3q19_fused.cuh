@@ -843,5 +843,124 @@ __global__ void __launch_bounds__(FT_TX *TY, MINB)
     cp_async_wait<0>();
 }
 
+// ---------------------------------------------------------------------------
+// Sixth fused kernel: the plain interior kernel (k_collide_interior, PART 3: x columns folded in, 168
+// registers, three 128-thread blocks per SM) with the phase pass pulled in.  Only the phi ring lives in
+// shared memory (6.5 KB per block), so nearly the whole 228 KB stay L1: the g populations of plane z+1 are
+// loaded once for the phi sums (tile + halo positions) and again, one iteration later, for the collision --
+// by then they sit in L1/L2, HBM sees them once.  Rows iY = 1 and NY-2 are left to k_collide_rim, which
+// reads phi from global memory; this kernel records phi for the rows iY <= 2 and iY >= NY-3 on every step.
+template <int TY>
+struct Fused6Smem {
+    static constexpr int NT = FT_TX * TY;
+    static constexpr int RW = FT_TX + 2, RH = TY + 2, RP = RW * RH;
+    static constexpr size_t bytes = (size_t)4 * RP * sizeof(double) + (size_t)3 * FT_NE * sizeof(int) + 16;
+};
+
+template <int TY, bool FXY, bool WRITE, int MINB>
+__global__ void __launch_bounds__(FT_TX *TY, MINB)
+    k_fused6_step(Geom g, Params P, const double *__restrict__ fin, const double *__restrict__ gin, double *__restrict__ fout,
+                  double *__restrict__ gout, FieldsOut o, double *__restrict__ phi_out, int zs_begin, int zs_end, int chunk)
+{
+    using S = Fused6Smem<TY>;
+    constexpr int NT = S::NT, RW = S::RW, RP = S::RP;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    double *ring = reinterpret_cast<double *>(smem_raw);      // [4][RP]
+    int *e_owner = reinterpret_cast<int *>(ring + 4 * RP);
+    int *e_ring = e_owner + FT_NE;
+    int *e_flags = e_ring + FT_NE;
+    int *n_extra_p = e_flags + FT_NE;
+
+    const int NX = g.nx, NY = g.ny;
+    const int tid = threadIdx.x, tx = tid & 31, ty = tid >> 5;
+    const int ix0 = blockIdx.x * FT_TX, iy0 = blockIdx.y * TY;
+    const int ix = ix0 + tx, iy = iy0 + ty;
+    const bool in_dom = ix < NX && iy < NY;
+    const bool bulk = in_dom && ix >= 1 && ix <= NX - 2 && iy >= 1 && iy <= NY - 2;
+    const bool mine_to_collide = bulk && iy >= 2 && iy <= NY - 3;     // rows 1 and NY-2: rim kernel
+    const bool band = iy <= 2 || iy >= NY - 3;
+    const long long idx = (long long)iy * NX + ix;
+    const long long pl = g.pl;
+    const int zs0 = zs_begin + blockIdx.z * chunk;
+    const int zs1 = min(zs0 + chunk, zs_end);
+    if (zs0 >= zs1) return;
+
+    if (tid == 0) *n_extra_p = 0;
+    __syncthreads();
+    for (int p = tid; p < RP; p += NT) {
+        const int px = p % RW, py = p / RW;
+        const int ex = ix0 - 1 + px, ey = iy0 - 1 + py;
+        if (ex < 0 || ex > NX - 1 || ey < 0 || ey > NY - 1) continue;
+        const bool inside = px >= 1 && px <= FT_TX && py >= 1 && py <= TY;
+        const bool ebulk = ex >= 1 && ex <= NX - 2 && ey >= 1 && ey <= NY - 2;
+        if (inside && ebulk) continue;
+        const int ox = min(max(ex, 1), NX - 2), oy = min(max(ey, 1), NY - 2);
+        const int slot = atomicAdd(n_extra_p, 1);
+        e_owner[slot] = oy * NX + ox;
+        e_ring[slot] = p;
+        e_flags[slot] = (ex == 0 ? 1 : 0) | (ey == 0 ? 2 : 0) | ((ex == NX - 1 || ey == NY - 1) ? 4 : 0) |
+                        ((inside && (ey <= 2 || ey >= NY - 3)) ? 8 : 0) | (inside ? 16 : 0);
+    }
+    __syncthreads();
+    const int n_extra = *n_extra_p;
+    const bool has_extra = tid < n_extra;
+    const int my_owner = has_extra ? e_owner[tid] : 0;
+    const int my_ring = has_extra ? e_ring[tid] : 0;
+    const int my_flags = has_extra ? e_flags[tid] : 0;
+
+    auto phase_plane = [&](int zs) {
+        double *rp = ring + (size_t)(zs & 3) * RP;
+        const bool mine = (zs >= zs0 && zs < zs1) || (zs == zs0 - 1 && zs0 == zs_begin) || (zs == zs1 && zs1 == zs_end);
+        const bool all = WRITE && mine && zs >= 2 && zs < g.nz + 2;
+        if (bulk) {
+            double G[19];
+            const double *src = gin + pop_index(g, zs, 0, idx);
+#pragma unroll
+            for (int k = 0; k < 19; k++) G[k] = src[k * pl];
+            const double v = sum19(G);
+            rp[(ty + 1) * RW + tx + 1] = v;
+            if (all || (mine && band)) phi_out[(long long)zs * pl + idx] = v;
+        }
+        if (has_extra) {
+            double E[19];
+            const double *src = gin + pop_index(g, zs, 0, my_owner);
+#pragma unroll
+            for (int k = 0; k < 19; k++) E[k] = src[k * pl];
+            double v;
+            switch (my_flags & 3) {
+            case 0: v = sum19(E); break;
+            case 1: v = sum19_mirror<1>(E); break;
+            case 2: v = sum19_mirror<2>(E); break;
+            default: v = sum19_mirror<3>(E); break;
+            }
+            if (my_flags & 4) v = v - P.phase_gradient;
+            rp[my_ring] = v;
+            if ((mine && (my_flags & 8)) || (all && (my_flags & 16))) {
+                const int px = my_ring % RW, py = my_ring / RW;
+                phi_out[(long long)zs * pl + (long long)(iy0 - 1 + py) * NX + (ix0 - 1 + px)] = v;
+            }
+        }
+    };
+
+    phase_plane(zs0 - 1);
+    phase_plane(zs0);
+    for (int zs = zs0; zs < zs1; zs++) {
+        phase_plane(zs + 1);
+        __syncthreads();   // phi ring planes zs-1, zs, zs+1 complete
+        if (mine_to_collide) {
+            double F[19], G[19], PH[19];
+            const double *pf = fin + pop_index(g, zs, 0, idx), *pg = gin + pop_index(g, zs, 0, idx);
+            constexpr int CX[19] = LBM3_CX, CY[19] = LBM3_CY, CZ[19] = LBM3_CZ;
+#pragma unroll
+            for (int k = 0; k < 19; k++) {
+                F[k] = __ldg(pf + k * pl);
+                G[k] = pg[k * pl];      // read for the phi sums one iteration ago: L1 / L2
+                PH[k] = ring[(size_t)((zs + CZ[k]) & 3) * RP + (ty + 1 + CY[k]) * RW + tx + 1 + CX[k]];
+            }
+            collide_push_node<FXY, WRITE, 3>(g, P, F, G, PH, fout, gout, o, zs, ix, iy);
+        }
+    }
+}
+
 }  // namespace lbm3
 #endif
