@@ -275,19 +275,33 @@ def ours(args, rank, world, local_rank):
     roof = None
     if prof:
         name = max(prof, key=lambda k: prof[k]["ms"])
+        # one launch covers the whole slab on one GPU; the overlapped multi-GPU step cuts the same kernel
+        # into three launches (both slab ends, then the planes between), so bytes and time are per launch
+        # with launches_per_step launches making up one pass over the slab
+        launches_per_step = prof[name]["launches"] / args.steps
         per_launch_ms = prof[name]["ms"] / prof[name]["launches"]
         peak, which_peak = peaks()
-        achieved = B_ALG * nloc / (per_launch_ms * 1e-3) / 1e9
+        achieved = B_ALG * nloc / launches_per_step / (per_launch_ms * 1e-3) / 1e9
         traffic = None
         tp = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tp):
             traffic = json.load(open(tp)).get(name, {}).get("dram_bytes_per_lattice_update")
             if traffic is not None:
-                traffic = traffic * nloc
+                traffic = traffic * nloc / launches_per_step
         roof = {"bound": "hbm", "kernel": name, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": traffic, "peak_source": which_peak, "algorithmic_bytes_per_launch": B_ALG * nloc,
-                "avg_launch_ms": per_launch_ms, "share_of_step": prof[name]["ms"] / sum(v["ms"] for v in prof.values()),
+                "traffic": traffic, "peak_source": which_peak, "algorithmic_bytes_per_launch": B_ALG * nloc / launches_per_step,
+                "launches_per_step": launches_per_step, "avg_launch_ms": per_launch_ms, "share_of_step": prof[name]["ms"] / sum(v["ms"] for v in prof.values()),
                 "kernels": prof}
+
+    # every rank's own view (the step time above is the max over ranks; a slab waits for its neighbours, so
+    # one slow GPU sets the pace): kernel time per step, wall per step, median SM clock
+    per_rank = None
+    if dist is not None:
+        mine = torch.tensor([sum(v["ms"] for v in prof.values()) / args.steps if prof else 0.0, ms / args.steps,
+                             float(clk.get("sm_mhz") or 0)], dtype=torch.float64, device="cuda")
+        allr = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(allr, mine)
+        per_rank = [{"kernel_ms_per_step": round(float(a[0]), 4), "ms_per_step": round(float(a[1]), 4), "sm_mhz": int(a[2])} for a in allr]
 
     # ---- end to end through the C ABI with host buffers: H2D initial fields, init, S steps, D2H result fields ----
     e2e = None
@@ -325,6 +339,8 @@ def ours(args, rank, world, local_rank):
                            "parallelism": "z-slab x%d" % world},
                 "mlups_per_gpu": value / world, "roofline": roof, "cpu_baseline": cb, "e2e": e2e, "clocks": clk,
                 "gpu_launches": launches}
+        if per_rank:
+            line["per_rank"] = per_rank
         print(json.dumps(line), flush=True)
     ctx.close()
     for ptr, _ in host.values():

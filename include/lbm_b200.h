@@ -58,7 +58,8 @@ typedef enum {
     LBM_BINARY_D2Q9 = 1,       /* FreeEnergy/binary.cpp */
     LBM_MRT_GS_D2Q9 = 2,       /* MRT/mrt.cpp */
     LBM_MRT_HERMITE_D2Q9 = 3,  /* MRT/another_mrt.cpp */
-    LBM_BINARY_D3Q19 = 4       /* Microchannel3D/{FullChannel,QuarterChannel} */
+    LBM_BINARY_D3Q19 = 4,      /* Microchannel3D/{FullChannel,QuarterChannel} */
+    LBM_TRT_DIFFUSION_D2Q9 = 5 /* DiffusionCylinder/cylinder.cpp: TRT advection-diffusion, anti-bounce-back on a masked domain */
 } lbm_model;
 
 typedef enum { LBM_RHO = 0, LBM_PHASE = 1, LBM_UX = 2, LBM_UY = 3, LBM_UZ = 4 } lbm_field;
@@ -75,6 +76,7 @@ typedef struct {
     double force[3];           /* main.cpp:58-60 (FullChannel: :50-53) */
     double omega, omega_bulk;  /* mrt.cpp:53-54; another_mrt.cpp:52-53 */
     double force_ampl;         /* mrt.cpp:98 */
+    double ce, conc_wall;      /* cylinder.cpp:43,33; the TRT rates are omega_minus = omega, omega_plus = 2 - omega (:38-40) */
     int device;                /* CUDA device ordinal */
     int slab_rank, slab_count; /* z-slab decomposition (3-D only): this context owns slab `rank` of `count` */
     int kernel_variant;        /* 0 = default (fastest measured); other values select the alternative D3Q19 kernels
@@ -101,8 +103,16 @@ size_t lbm_local_nodes(const lbm_ctx *ctx); /* nx*ny*nz_local */
  * 2-D programs' direct writes to rho/phase/u.  n = lbm_local_nodes(). */
 lbm_status lbm_set_field(lbm_ctx *ctx, int field, const double *host, size_t n);
 
+/* LBM_TRT_DIFFUSION_D2Q9 only.  Replaces: the geometry array the program builds in
+ * initialize_geometry() (cylinder.cpp:224-283) together with bb_nodes/dirs (:264-283, :303-312), which the
+ * library derives from it.  mask[iY*nx+iX]: 1 fluid, 0 anti-bounce-back boundary node, -1 solid;
+ * n = lbm_local_nodes().  LBM_EINVAL if a fluid node lies on the edge of the array or touches a solid
+ * node (the reference would stream from outside the array / from a node it never updates).  Call before
+ * lbm_init. */
+lbm_status lbm_set_geometry(lbm_ctx *ctx, const int *mask, size_t n);
+
 /* Replaces: init() of binary.cpp:122-198; the init loops of shanchen.cpp:87-114
- * (from the rho field) and mrt.cpp:97-120 / another_mrt.cpp:89-110 (from rho,ux,uy);
+ * (from the rho field), mrt.cpp:97-120 / another_mrt.cpp:89-110 and cylinder.cpp:97-124 (from rho,ux,uy);
  * Solver::init (solver.hpp:871-879) incl. its phase halo exchange. */
 lbm_status lbm_init(lbm_ctx *ctx);
 
@@ -112,7 +122,8 @@ lbm_status lbm_set_populations(lbm_ctx *ctx, int set, const double *host_aos, si
 lbm_status lbm_get_populations(lbm_ctx *ctx, int set, double *host_aos, size_t n);
 
 /* Replaces the body of the time loop: shanchen.cpp:120-188, binary.cpp:336-350
- * (collide_bulk, update_bounce_back, streaming), mrt.cpp:144-251,
+ * (collide_bulk, update_bounce_back, streaming), mrt.cpp:144-251, cylinder.cpp:355-358
+ * (collide, update_bounce_back, stream),
  * another_mrt.cpp:112-214, Solver::collide_stream (solver.hpp:881-891: updateMacro,
  * updatePhase, Lattice::collide_stream, propagate, exchangeMatrices).
  * Asynchronous: returns once the work is queued; any call that reads results waits. */

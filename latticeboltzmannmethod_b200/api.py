@@ -12,7 +12,8 @@ import numpy as np
 _PKG = os.path.dirname(os.path.abspath(__file__))
 _LIB = os.path.join(_PKG, "liblbm_b200.so")
 
-MODELS = dict(shanchen_d2q9=0, binary_d2q9=1, mrt_gs_d2q9=2, mrt_hermite_d2q9=3, binary_d3q19=4)
+MODELS = dict(shanchen_d2q9=0, binary_d2q9=1, mrt_gs_d2q9=2, mrt_hermite_d2q9=3, binary_d3q19=4,
+              trt_diffusion_d2q9=5)
 FIELDS = dict(rho=0, phase=1, ux=2, uy=3, uz=4)
 HALO = dict(S_F_UP=0, S_G_UP=1, S_F_DOWN=2, S_G_DOWN=3, R_F_FROM_BELOW=4, R_G_FROM_BELOW=5, R_F_FROM_ABOVE=6,
             R_G_FROM_ABOVE=7, S_PHI_UP=8, S_PHI_DOWN=9, R_PHI_FROM_BELOW=10, R_PHI_FROM_ABOVE=11)
@@ -34,6 +35,7 @@ class Config(C.Structure):
                 ("tau_gas", C.c_double), ("tau_liq", C.c_double), ("tau_phi", C.c_double),
                 ("wall_gradient", C.c_double), ("rho_wall", C.c_double), ("force", C.c_double * 3),
                 ("omega", C.c_double), ("omega_bulk", C.c_double), ("force_ampl", C.c_double),
+                ("ce", C.c_double), ("conc_wall", C.c_double),
                 ("device", C.c_int), ("slab_rank", C.c_int), ("slab_count", C.c_int), ("kernel_variant", C.c_int)]
 
 
@@ -64,6 +66,7 @@ def load_library():
         "lbm_local_nodes": (sz, [vp]),
         "lbm_set_field": (ci, [vp, ci, vp, sz]),
         "lbm_get_field": (ci, [vp, ci, vp, sz]),
+        "lbm_set_geometry": (ci, [vp, vp, sz]),
         "lbm_init": (ci, [vp]),
         "lbm_set_populations": (ci, [vp, ci, vp, sz]),
         "lbm_get_populations": (ci, [vp, ci, vp, sz]),
@@ -96,7 +99,7 @@ def load_library():
 
 
 EXPORTS = ["lbm_config_default", "lbm_create", "lbm_destroy", "lbm_last_error", "lbm_slab_extent", "lbm_local_nodes",
-           "lbm_set_field", "lbm_get_field", "lbm_init", "lbm_set_populations", "lbm_get_populations", "lbm_step",
+           "lbm_set_field", "lbm_get_field", "lbm_set_geometry", "lbm_init", "lbm_set_populations", "lbm_get_populations", "lbm_step",
            "lbm_sync", "lbm_diagnostics", "lbm_get_stream", "lbm_set_stream", "lbm_launch_count", "lbm_profile",
            "lbm_profile_report", "lbm_host_alloc",
            "lbm_host_free", "lbm_comm_unique_id", "lbm_comm_attach", "lbm_slab_halo", "lbm_slab_init_fields",
@@ -166,6 +169,12 @@ class Context:
             host = np.ascontiguousarray(host, dtype=np.float64).ravel()
             assert host.size == self.local_nodes, (host.size, self.local_nodes)
         self._ck(self.L.lbm_set_field(self.h, FIELDS[field] if isinstance(field, str) else field, _ptr(host), self.local_nodes))
+
+    def set_geometry(self, mask):
+        """mask: int array, 1 fluid / 0 boundary / -1 solid, node i = iY*nx+iX (TRT diffusion model only)."""
+        mask = np.ascontiguousarray(mask, dtype=np.int32).ravel()
+        self._keep = mask
+        self._ck(self.L.lbm_set_geometry(self.h, mask.ctypes.data, mask.size))
 
     def get_field(self, field, out=None):
         if out is None:
@@ -315,6 +324,40 @@ def mrt_initial_fields(variant="gs", nx=40, ny=3, ampl=0.001, force_ampl=0.002):
             u = ampl * math.cos(float(ix) / float(nx) * 2 * pi)
         ux[ix * ny:(ix + 1) * ny] = u
     return rho, ux, uy
+
+
+def trt_config(nx=129, ny=129, omega=None, ce=None, conc_wall=None, device=0):
+    """DiffusionCylinder/cylinder.cpp:226-227,33-43."""
+    c = default_config("trt_diffusion_d2q9")
+    c.nx, c.ny, c.device = nx, ny, device
+    if omega is not None:
+        c.omega = omega
+    if ce is not None:
+        c.ce = ce
+    if conc_wall is not None:
+        c.conc_wall = conc_wall
+    return c
+
+
+def trt_cylinder_setup(nx=129, ny=129, radius=40, conc_wall=1.0):
+    """cylinder.cpp:224-296: the disc, its ring of boundary nodes, and the initial concentration
+    (0 in the fluid, conc_wall on the ring, -1 in the solid).  Returns mask, rho, ux, uy flat [iY*nx+iX]."""
+    iy, ix = np.meshgrid(np.arange(ny), np.arange(nx), indexing="ij")
+    inside = (ix - (nx - 1) // 2) ** 2 + (iy - (ny - 1) // 2) ** 2 <= radius * radius
+    mask = np.where(inside, 1, -1).astype(np.int32)
+
+    def touches(m, value):
+        pad = np.pad(m, 1, constant_values=2)
+        hit = np.zeros(m.shape, bool)
+        for dy in (-1, 0, 1):
+            for dx in (-1, 0, 1):
+                hit |= pad[1 + dy:1 + dy + ny, 1 + dx:1 + dx + nx] == value
+        return hit
+
+    mask[(mask == 1) & touches(mask, -1)] = 0          # fluid next to solid becomes a boundary node
+    mask[(mask == 0) & ~touches(mask, 1)] = -1         # boundary nodes with no fluid neighbour are solid
+    rho = np.where(mask == 0, conc_wall, np.where(mask == -1, -1.0, 0.0)).astype(np.float64)
+    return mask.ravel(), rho.ravel(), np.zeros(nx * ny), np.zeros(nx * ny)
 
 
 def microchannel_config(which="quarter", nx=None, ny=None, nz=None, device=0, slab_rank=0, slab_count=1):

@@ -1,6 +1,6 @@
-// d2q9_models.cu -- the three D2Q9 programs on one GPU: Shan-Chen
-// (ShanChen/shanchen.cpp), binary liquid (FreeEnergy/binary.cpp) and MRT
-// (MRT/mrt.cpp, MRT/another_mrt.cpp).  Per-thread arithmetic: d2q9_threads.h.
+// d2q9_models.cu -- the D2Q9 programs on one GPU: Shan-Chen
+// (ShanChen/shanchen.cpp), binary liquid (FreeEnergy/binary.cpp), MRT
+// (MRT/mrt.cpp, MRT/another_mrt.cpp) and TRT diffusion (DiffusionCylinder/cylinder.cpp).  Per-thread arithmetic: d2q9_threads.h.
 #include <vector>
 
 #include "d2q9_host.h"
@@ -66,6 +66,20 @@ __global__ void __launch_bounds__(kThreads) k_mrt_step(lbm2::MrtParams P, const 
 {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < (long long)P.nx * P.ny) lbm2::mrt_thread(P, f, force, f2, rho, ux, uy, (int)(i / P.ny), (int)(i % P.ny));
+}
+// ---- TRT diffusion kernels (node index i = iY*nx+iX) ----
+__global__ void __launch_bounds__(kThreads) k_trt_init(lbm2::TrtParams P, const double *rho, const double *ux, const double *uy,
+                                                        double *fa, double *fb)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < (long long)P.nx * P.ny) lbm2::trt_init_thread(P, rho, ux, uy, fa, fb, i);
+}
+__global__ void __launch_bounds__(kThreads) k_trt_step(lbm2::TrtParams P, const double *__restrict__ f,
+                                                        const unsigned short *__restrict__ links, const double *__restrict__ ux,
+                                                        const double *__restrict__ uy, double *__restrict__ f2, double *__restrict__ rho)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < (long long)P.nx * P.ny) lbm2::trt_thread(P, f, links, ux, uy, f2, rho, i);
 }
 // ---- AoS <-> SoA at the boundary ----
 __global__ void __launch_bounds__(kThreads) k_aos_to_soa9(long long n, const double *aos, double *soa)
@@ -299,6 +313,84 @@ private:
     lbm2::MrtParams P_{};
 };
 
+// DiffusionCylinder/cylinder.cpp: one launch per step; the geometry mask becomes one 16-bit link word per node
+class Trt : public Model2D {
+public:
+    Trt(Runtime &rt, const lbm_config &cfg) : Model2D(rt, cfg, 1) {}
+    ~Trt() override { cudaFree(links_); }
+    lbm_status setup()
+    {
+        LBM_TRY(alloc_common());
+        P_ = lbm2::TrtParams{cfg_.nx, cfg_.ny, 2.0 - cfg_.omega, cfg_.omega, cfg_.ce, cfg_.conc_wall};   // cylinder.cpp:38-40
+        LBM_CUDA(rt_, cudaMalloc(&links_, n_ * sizeof(unsigned short)));
+        LBM_CUDA(rt_, cudaMemset(links_, 0, n_ * sizeof(unsigned short)));
+        return LBM_OK;
+    }
+    bool has_field(int f) const override { return f == LBM_RHO || f == LBM_UX || f == LBM_UY; }
+    lbm_status set_geometry(const int *mask) override
+    {
+        const int nx = cfg_.nx, ny = cfg_.ny;
+        const int CX[9] = LBM2_CX, CY[9] = LBM2_CY;
+        std::vector<unsigned short> links((size_t)n_);
+        for (long long i = 0; i < n_; i++) {
+            if (mask[i] < -1 || mask[i] > 1) return rt_.fail(LBM_EINVAL, "lbm_set_geometry: mask values are 1 (fluid), 0 (boundary), -1 (solid)");
+            if (mask[i] != 1) continue;
+            const int ix = (int)(i % nx), iy = (int)(i / nx);
+            if (ix == 0 || iy == 0 || ix == nx - 1 || iy == ny - 1)
+                return rt_.fail(LBM_EINVAL, "lbm_set_geometry: a fluid node lies on the edge of the array");
+            for (int k = 1; k < 9; k++)
+                if (mask[i + CY[k] * nx + CX[k]] == -1)
+                    return rt_.fail(LBM_EINVAL, "lbm_set_geometry: a fluid node touches a solid node (no boundary node between them)");
+            links[(size_t)i] = lbm2::trt_links_thread(P_, mask, i);
+        }
+        LBM_CUDA(rt_, cudaMemcpyAsync(links_, links.data(), (size_t)n_ * sizeof(unsigned short), cudaMemcpyHostToDevice, rt_.stream));
+        LBM_CUDA(rt_, cudaStreamSynchronize(rt_.stream));
+        have_geometry_ = true;
+        return LBM_OK;
+    }
+    lbm_status init() override
+    {
+        if (!have_geometry_) return rt_.fail(LBM_ESTATE, "TRT diffusion: call lbm_set_geometry before lbm_init");
+        k_trt_init<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, fields_[LBM_RHO], fields_[LBM_UX], fields_[LBM_UY], f_[0], f_[1]);
+        return rt_.launched("k_trt_init");
+    }
+    lbm_status step(int nsteps) override
+    {
+        for (int t = 0; t < nsteps; t++) {
+            rt_.about_to_launch();
+            k_trt_step<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, f_[cur_], links_, fields_[LBM_UX], fields_[LBM_UY], f_[1 - cur_],
+                                                                    fields_[LBM_RHO]);
+            LBM_TRY(rt_.launched("k_trt_step"));
+            cur_ = 1 - cur_;
+        }
+        return LBM_OK;
+    }
+    // boundary and solid nodes are never streamed into, so a load must reach both buffers
+    lbm_status after_set_populations(int) override
+    {
+        return rt_.cuda(cudaMemcpyAsync(f_[1 - cur_], f_[cur_], 9 * n_ * sizeof(double), cudaMemcpyDeviceToDevice, rt_.stream), "copy populations");
+    }
+    lbm_status diagnostics(double *mass, double *mom, double *pm, int *has_nan) override
+    {
+        DiagLayout L;
+        L.f = f_[cur_]; L.g = nullptr;
+        L.stride_k = n_; L.plane_stride = 0; L.planes = 1; L.nx = cfg_.nx; L.ny = cfg_.ny; L.q = 9;
+        L.skip_border = 0; L.node_major_x = 1; L.fluid = links_;
+        double out[6];
+        LBM_TRY(run_diagnostics(rt_, L, diag_, diagnostics_scratch_blocks(), out));
+        if (mass) *mass = out[0];
+        if (mom) { mom[0] = out[1]; mom[1] = out[2]; mom[2] = 0.0; }
+        if (pm) *pm = 0.0;
+        if (has_nan) *has_nan = out[5] != 0.0;
+        return LBM_OK;
+    }
+
+private:
+    lbm2::TrtParams P_{};
+    unsigned short *links_ = nullptr;
+    bool have_geometry_ = false;
+};
+
 template <class T>
 Model *make(Runtime &rt, const lbm_config &cfg, lbm_status *st)
 {
@@ -316,5 +408,6 @@ Model *make(Runtime &rt, const lbm_config &cfg, lbm_status *st)
 Model *make_d2q9_shanchen(Runtime &rt, const lbm_config &cfg, lbm_status *st) { return make<ShanChen>(rt, cfg, st); }
 Model *make_d2q9_binary(Runtime &rt, const lbm_config &cfg, lbm_status *st) { return make<Binary2D>(rt, cfg, st); }
 Model *make_d2q9_mrt(Runtime &rt, const lbm_config &cfg, lbm_status *st) { return make<Mrt>(rt, cfg, st); }
+Model *make_d2q9_trt(Runtime &rt, const lbm_config &cfg, lbm_status *st) { return make<Trt>(rt, cfg, st); }
 
 }  // namespace lbm

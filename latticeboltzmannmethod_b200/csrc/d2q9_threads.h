@@ -371,5 +371,103 @@ LBM_HD void mrt_init_thread(const MrtParams &P, const double *rho_i, const doubl
     }
 }
 
+// ======================= TRT diffusion with anti-bounce-back (DiffusionCylinder/cylinder.cpp) =======================
+// Node index i = iY*nx+iX (cylinder.cpp:127).  `links` is built once from the geometry mask (1 fluid, 0
+// boundary, -1 solid; cylinder.cpp:224-283): bit 0 = this node is fluid, bit k (1..8) = the neighbour in
+// direction k is a boundary node.  The reference collides every fluid node (cylinder.cpp:126-205), then
+// writes -f2[fluid][opp] + 2 w C into the boundary node (:208-221) and pulls (:337-347); pushed from the
+// fluid node, the population sent towards a boundary node comes straight back into its own opposite slot.
+struct TrtParams {
+    int nx, ny;
+    double omega_plus, omega_minus, ce, conc_wall;   // cylinder.cpp:33,38-43
+};
+
+// bit k of the link word (16 bits: fluid flag + 8 directions) from the mask; the host validates that no fluid node touches the array edge or a solid node
+LBM_HD unsigned short trt_links_thread(const TrtParams &P, const int *mask, long long i)
+{
+    const int CX[9] = LBM2_CX, CY[9] = LBM2_CY;
+    if (mask[i] != 1) return 0;
+    unsigned short b = 1;
+    for (int k = 1; k < 9; k++)
+        if (mask[i + CY[k] * P.nx + CX[k]] == 0) b |= (unsigned short)(1u << k);
+    // bit 0 doubles as "fluid"; k = 0 never leaves the node
+    return b;
+}
+
+// cylinder.cpp:97-124: second-order equilibrium on every node, into both buffers (non-fluid nodes keep it)
+LBM_HD void trt_init_thread(const TrtParams &P, const double *rho_i, const double *ux_i, const double *uy_i, double *fa, double *fb,
+                            long long i)
+{
+    const long long n = (long long)P.nx * P.ny;
+    const int CX[9] = LBM2_CX, CY[9] = LBM2_CY;
+    const double W[9] = LBM2_W;
+    const double dense_temp = rho_i[i], ux_temp = ux_i[i], uy_temp = uy_i[i];
+    for (int k = 0; k < 9; k++) {
+        const int cx = CX[k], cy = CY[k];
+        const double feq = W[k] * (dense_temp + 3.0 * dense_temp * (cx * ux_temp + cy * uy_temp) +
+                                   4.5 * dense_temp * ((cx * cx - 1.0 / 3.0) * ux_temp * ux_temp + (cy * cy - 1.0 / 3.0) * uy_temp * uy_temp +
+                                                       2.0 * ux_temp * uy_temp * cx * cy));
+        fa[k * n + i] = feq;
+        fb[k * n + i] = feq;
+    }
+}
+
+// the even/odd pair (k, opposite k) of cylinder.cpp:147-200; wt = weights_trt[k], cu = cx[k]*ux+cy[k]*uy
+struct TrtPair {
+    double plus, minus, eq_plus, eq_minus;
+};
+LBM_HD TrtPair trt_pair(double fk, double fo, double wt, double dense, double cu, double u_sq, double ce)
+{
+    TrtPair r;
+    r.plus = 0.5 * (fk + fo);
+    r.minus = 0.5 * (fk - fo);
+    r.eq_minus = wt * dense * cu;
+    r.eq_plus = wt * dense * (ce + 0.5 * (3.0 * cu * cu - u_sq));
+    return r;
+}
+
+LBM_HD void trt_thread(const TrtParams &P, const double *f, const unsigned short *links, const double *ux_i, const double *uy_i,
+                       double *f2, double *rho_o, long long i)
+{
+    const unsigned link = links[i];
+    if (!(link & 1u)) return;
+    const long long n = (long long)P.nx * P.ny;
+    const int CX[9] = LBM2_CX, CY[9] = LBM2_CY, OPP[9] = LBM2_OPP;
+    const double W[9] = LBM2_W;
+    double fl[9];
+#pragma unroll
+    for (int k = 0; k < 9; k++) fl[k] = f[k * n + i];
+    double sum = 0;
+#pragma unroll
+    for (int k = 0; k < 9; k++) sum += fl[k];
+    rho_o[i] = sum;
+    const double dense_temp = sum, ux_temp = ux_i[i], uy_temp = uy_i[i];
+    const double u_sq = ux_temp * ux_temp + uy_temp * uy_temp;
+    // pairs (1,3), (2,4), (5,7), (6,8); weights_trt = 1/3 on the axes, 1/12 on the diagonals (cylinder.cpp:50)
+    const TrtPair a = trt_pair(fl[1], fl[3], 1.0 / 3.0, dense_temp, 1 * ux_temp + 0 * uy_temp, u_sq, P.ce);
+    const TrtPair b = trt_pair(fl[2], fl[4], 1.0 / 3.0, dense_temp, 0 * ux_temp + 1 * uy_temp, u_sq, P.ce);
+    const TrtPair c = trt_pair(fl[5], fl[7], 1.0 / 12.0, dense_temp, 1 * ux_temp + 1 * uy_temp, u_sq, P.ce);
+    const TrtPair d = trt_pair(fl[6], fl[8], 1.0 / 12.0, dense_temp, -1 * ux_temp + 1 * uy_temp, u_sq, P.ce);
+    const double eq_plus0 = dense_temp - 2.0 * (a.eq_plus + b.eq_plus + c.eq_plus + d.eq_plus);   // cylinder.cpp:196
+    double out[9];
+    out[0] = fl[0] - P.omega_plus * (fl[0] - eq_plus0) - P.omega_minus * (0.0 - 0.0);
+    out[1] = fl[1] - P.omega_plus * (a.plus - a.eq_plus) - P.omega_minus * (a.minus - a.eq_minus);
+    out[3] = fl[3] - P.omega_plus * (a.plus - a.eq_plus) - P.omega_minus * (-a.minus - -a.eq_minus);
+    out[2] = fl[2] - P.omega_plus * (b.plus - b.eq_plus) - P.omega_minus * (b.minus - b.eq_minus);
+    out[4] = fl[4] - P.omega_plus * (b.plus - b.eq_plus) - P.omega_minus * (-b.minus - -b.eq_minus);
+    out[5] = fl[5] - P.omega_plus * (c.plus - c.eq_plus) - P.omega_minus * (c.minus - c.eq_minus);
+    out[7] = fl[7] - P.omega_plus * (c.plus - c.eq_plus) - P.omega_minus * (-c.minus - -c.eq_minus);
+    out[6] = fl[6] - P.omega_plus * (d.plus - d.eq_plus) - P.omega_minus * (d.minus - d.eq_minus);
+    out[8] = fl[8] - P.omega_plus * (d.plus - d.eq_plus) - P.omega_minus * (-d.minus - -d.eq_minus);
+    f2[i] = out[0];
+#pragma unroll
+    for (int k = 1; k < 9; k++) {
+        if (link & (1u << k))
+            f2[OPP[k] * n + i] = -out[k] + 2 * W[OPP[k]] * P.conc_wall;   // cylinder.cpp:217
+        else
+            f2[k * n + i + CY[k] * P.nx + CX[k]] = out[k];
+    }
+}
+
 }  // namespace lbm2
 #endif

@@ -64,6 +64,7 @@ __global__ void __launch_bounds__(kDiagThreads) k_diag_partial(DiagLayout L, dou
             const int iy = (int)(idx % L.ny);
             if (iy < 1 || iy > L.ny - 2) continue;
         }
+        if (L.fluid && !(L.fluid[idx] & 1)) continue;
         const long long base = (long long)plane * L.plane_stride + idx;
 #pragma unroll
         for (int k = 0; k < Q; k++) {

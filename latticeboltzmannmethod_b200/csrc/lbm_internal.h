@@ -90,6 +90,7 @@ public:
     virtual int q() const = 0;
     virtual int nsets() const = 0;  // 1 = f only, 2 = f and g
     virtual lbm_status set_field(int field, const double *host) = 0;
+    virtual lbm_status set_geometry(const int *) { return LBM_EINVAL; }  // masked models only
     virtual lbm_status get_field(int field, double *host) = 0;
     virtual lbm_status init() = 0;
     virtual lbm_status step(int nsteps) = 0;
@@ -111,6 +112,7 @@ Model *make_d3q19_binary(Runtime &rt, const lbm_config &cfg, lbm_status *st);
 Model *make_d2q9_shanchen(Runtime &rt, const lbm_config &cfg, lbm_status *st);
 Model *make_d2q9_binary(Runtime &rt, const lbm_config &cfg, lbm_status *st);
 Model *make_d2q9_mrt(Runtime &rt, const lbm_config &cfg, lbm_status *st);
+Model *make_d2q9_trt(Runtime &rt, const lbm_config &cfg, lbm_status *st);
 
 // diagnostics: block-level partial sums into scratch, then one block folds them.
 // sums[0..4] = sum f, sum f*cx, sum f*cy, sum f*cz, sum g ; sums[5] = NaN count
@@ -125,6 +127,7 @@ struct DiagLayout {
     int planes, nx, ny, q;
     int skip_border;          // 1: only 1<=ix<=nx-2, 1<=iy<=ny-2 count (3-D); 2: only 1<=fast<=ny-2 (binary 2-D)
     int node_major_x;         // in-plane index = iy*nx+ix (1) or ix*ny+iy (0)
+    const unsigned short *fluid = nullptr;  // optional per-node link word, bit 0 = counts (masked 2-D model)
 };
 lbm_status run_diagnostics(Runtime &rt, const DiagLayout &L, double *scratch, int scratch_blocks, double *host_out6);
 int diagnostics_scratch_blocks();

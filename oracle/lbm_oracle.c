@@ -1054,3 +1054,144 @@ void lbomrt_get_pops(lbomrt *s, double *f)
     for (size_t i = 0; i < s->n; i++)
         for (int k = 0; k < 9; k++) f[i * 9 + k] = s->f[k * s->n + i];
 }
+
+/* ====================================================================== */
+/* D2Q9 TRT diffusion with anti-bounce-back: DiffusionCylinder/cylinder.cpp */
+/* ====================================================================== */
+static const double WTRT[9] = {0.0, 1.0 / 3.0, 1.0 / 3.0, 1.0 / 3.0, 1.0 / 3.0, 1.0 / 12.0, 1.0 / 12.0, 1.0 / 12.0, 1.0 / 12.0};
+
+struct lbotrt {
+    int nx, ny;
+    size_t n;
+    double omega_plus, omega_minus, ce, conc_wall;
+    int *mask;
+    double *f, *f2, *rho, *ux, *uy;   /* f SoA [k][iY*nx+iX] */
+};
+
+lbotrt *lbotrt_create(int nx, int ny, double omega, double ce, double conc_wall, const int *mask)
+{
+    lbotrt *s = (lbotrt *)calloc(1, sizeof *s);
+    s->nx = nx; s->ny = ny; s->n = (size_t)nx * ny;
+    s->omega_plus = 2.0 - omega;      /* cylinder.cpp:39-40 */
+    s->omega_minus = omega;
+    s->ce = ce; s->conc_wall = conc_wall;
+    s->mask = (int *)malloc(s->n * sizeof(int));
+    memcpy(s->mask, mask, s->n * sizeof(int));
+    s->f = (double *)calloc(9 * s->n, sizeof(double));
+    s->f2 = (double *)calloc(9 * s->n, sizeof(double));
+    s->rho = (double *)calloc(s->n, sizeof(double));
+    s->ux = (double *)calloc(s->n, sizeof(double));
+    s->uy = (double *)calloc(s->n, sizeof(double));
+    return s;
+}
+void lbotrt_destroy(lbotrt *s)
+{
+    if (!s) return;
+    free(s->mask); free(s->f); free(s->f2); free(s->rho); free(s->ux); free(s->uy); free(s);
+}
+/* cylinder.cpp:224-296: circle, then fluid nodes touching solid become boundary nodes, boundary nodes
+ * touching no fluid become solid; initial concentration 0 in the fluid, conc_wall on the boundary, -1 in
+ * the solid.  The reference indexes iX*NY+iY here and iY*NX+iX elsewhere; NX == NY and the circle is
+ * symmetric, so the flat array is the same. */
+void lbotrt_reference_setup(int nx, int ny, int radius, double conc_wall, int *mask, double *rho, double *ux, double *uy)
+{
+    for (int ix = 0; ix < nx; ix++)
+        for (int iy = 0; iy < ny; iy++) {
+            int c = ix * ny + iy;
+            mask[c] = ((ix - (nx - 1) / 2) * (ix - (nx - 1) / 2) + (iy - (ny - 1) / 2) * (iy - (ny - 1) / 2) > radius * radius) ? -1 : 1;
+        }
+    for (int ix = 0; ix < nx; ix++)
+        for (int iy = 0; iy < ny; iy++) {
+            int c = ix * ny + iy;
+            if (mask[c] == 1) {
+                int flag = 0;
+                for (int k = 0; k < 9; k++)
+                    if (mask[(ix + C2X[k]) * ny + iy + C2Y[k]] == -1) flag = 1;
+                if (flag) mask[c] = 0;
+            }
+        }
+    for (int ix = 0; ix < nx; ix++)
+        for (int iy = 0; iy < ny; iy++) {
+            int c = ix * ny + iy;
+            if (mask[c] == 0) {
+                int flag = 0;
+                for (int k = 0; k < 9; k++)
+                    if (mask[(ix + C2X[k]) * ny + iy + C2Y[k]] == 1) flag = 1;
+                if (!flag) mask[c] = -1;
+            }
+        }
+    for (int c = 0; c < nx * ny; c++) {
+        rho[c] = mask[c] == 0 ? conc_wall : (mask[c] == -1 ? -1.0 : 0.0);
+        ux[c] = 0.0; uy[c] = 0.0;
+    }
+}
+void lbotrt_init(lbotrt *s, const double *rho, const double *ux, const double *uy)
+{
+    memcpy(s->rho, rho, s->n * sizeof(double));
+    memcpy(s->ux, ux, s->n * sizeof(double));
+    memcpy(s->uy, uy, s->n * sizeof(double));
+    for (size_t c = 0; c < s->n; c++) {
+        double d = s->rho[c], u = s->ux[c], v = s->uy[c];
+        for (int k = 0; k < 9; k++) {
+            int cx = C2X[k], cy = C2Y[k];
+            s->f[k * s->n + c] = W2[k] * (d + 3.0 * d * (cx * u + cy * v) +
+                                          4.5 * d * ((cx * cx - 1.0 / 3.0) * u * u + (cy * cy - 1.0 / 3.0) * v * v + 2.0 * u * v * cx * cy));
+        }
+    }
+    /* boundary and solid nodes are never streamed into (cylinder.cpp:340): they keep these values in f for good */
+    memcpy(s->f2, s->f, 9 * s->n * sizeof(double));
+}
+static void step_trt(lbotrt *s)
+{
+    const size_t n = s->n;
+    const int NX = s->nx;
+    for (size_t c = 0; c < n; c++) {
+        if (s->mask[c] != 1) continue;
+        double F[9], fo[9];
+        double sum = 0;
+        for (int k = 0; k < 9; k++) { F[k] = s->f[k * n + c]; sum += F[k]; }
+        s->rho[c] = sum;
+        double d = sum, u = s->ux[c], v = s->uy[c];
+        double f_plus[9], f_minus[9], feq_plus[9], feq_minus[9];
+        f_plus[0] = F[0];
+        f_plus[1] = 0.5 * (F[1] + F[3]); f_plus[2] = 0.5 * (F[2] + F[4]); f_plus[3] = f_plus[1]; f_plus[4] = f_plus[2];
+        f_plus[5] = 0.5 * (F[5] + F[7]); f_plus[6] = 0.5 * (F[6] + F[8]); f_plus[7] = f_plus[5]; f_plus[8] = f_plus[6];
+        f_minus[0] = 0.0;
+        f_minus[1] = 0.5 * (F[1] - F[3]); f_minus[2] = 0.5 * (F[2] - F[4]); f_minus[3] = -f_minus[1]; f_minus[4] = -f_minus[2];
+        f_minus[5] = 0.5 * (F[5] - F[7]); f_minus[6] = 0.5 * (F[6] - F[8]); f_minus[7] = -f_minus[5]; f_minus[8] = -f_minus[6];
+        feq_minus[0] = 0.0;
+        feq_minus[1] = WTRT[1] * d * (C2X[1] * u + C2Y[1] * v);
+        feq_minus[2] = WTRT[2] * d * (C2X[2] * u + C2Y[2] * v);
+        feq_minus[3] = -feq_minus[1]; feq_minus[4] = -feq_minus[2];
+        feq_minus[5] = WTRT[5] * d * (C2X[5] * u + C2Y[5] * v);
+        feq_minus[6] = WTRT[6] * d * (C2X[6] * u + C2Y[6] * v);
+        feq_minus[7] = -feq_minus[5]; feq_minus[8] = -feq_minus[6];
+        double u_sq = u * u + v * v;
+        feq_plus[1] = WTRT[1] * d * (s->ce + 0.5 * (3.0 * (C2X[1] * u + C2Y[1] * v) * (C2X[1] * u + C2Y[1] * v) - u_sq));
+        feq_plus[2] = WTRT[2] * d * (s->ce + 0.5 * (3.0 * (C2X[2] * u + C2Y[2] * v) * (C2X[2] * u + C2Y[2] * v) - u_sq));
+        feq_plus[3] = feq_plus[1]; feq_plus[4] = feq_plus[2];
+        feq_plus[5] = WTRT[5] * d * (s->ce + 0.5 * (3.0 * (C2X[5] * u + C2Y[5] * v) * (C2X[5] * u + C2Y[5] * v) - u_sq));
+        feq_plus[6] = WTRT[6] * d * (s->ce + 0.5 * (3.0 * (C2X[6] * u + C2Y[6] * v) * (C2X[6] * u + C2Y[6] * v) - u_sq));
+        feq_plus[7] = feq_plus[5]; feq_plus[8] = feq_plus[6];
+        feq_plus[0] = d - 2.0 * (feq_plus[1] + feq_plus[2] + feq_plus[5] + feq_plus[6]);
+        for (int k = 0; k < 9; k++)
+            fo[k] = F[k] - s->omega_plus * (f_plus[k] - feq_plus[k]) - s->omega_minus * (f_minus[k] - feq_minus[k]);
+        /* cylinder.cpp:208-221 (anti-bounce-back on the boundary nodes) and :337-347 (pull) as one push:
+         * a population heading into a boundary node comes back reversed, negated, plus 2 w C */
+        for (int k = 0; k < 9; k++) {
+            size_t t = c + C2Y[k] * NX + C2X[k];
+            if (s->mask[t] == 0)
+                s->f2[OPP2[k] * n + c] = -fo[k] + 2 * W2[OPP2[k]] * s->conc_wall;
+            else
+                s->f2[k * n + t] = fo[k];
+        }
+    }
+    double *t = s->f; s->f = s->f2; s->f2 = t;
+}
+void lbotrt_step(lbotrt *s, int nsteps) { for (int t = 0; t < nsteps; t++) step_trt(s); }
+void lbotrt_get_rho(lbotrt *s, double *rho) { memcpy(rho, s->rho, s->n * sizeof(double)); }
+void lbotrt_get_pops(lbotrt *s, double *f)
+{
+    for (size_t i = 0; i < s->n; i++)
+        for (int k = 0; k < 9; k++) f[i * 9 + k] = s->f[k * s->n + i];
+}

@@ -113,6 +113,18 @@ void lbomrt_step(lbomrt *, int n);
 void lbomrt_get_fields(lbomrt *, double *rho, double *ux, double *uy);
 void lbomrt_get_pops(lbomrt *, double *f);
 
+/* ---------------- D2Q9 TRT diffusion in a masked domain (DiffusionCylinder/cylinder.cpp) ---------------- */
+typedef struct lbotrt lbotrt;
+/* mask: 1 fluid, 0 anti-bounce-back boundary node, -1 solid; node i = iY*nx+iX (cylinder.cpp:127,135) */
+lbotrt *lbotrt_create(int nx, int ny, double omega, double ce, double conc_wall, const int *mask);
+void lbotrt_destroy(lbotrt *);
+void lbotrt_init(lbotrt *, const double *rho, const double *ux, const double *uy);   /* cylinder.cpp:97-124 */
+void lbotrt_step(lbotrt *, int n);                                                    /* :128-205, :208-221, :337-347 */
+void lbotrt_get_rho(lbotrt *, double *rho);
+void lbotrt_get_pops(lbotrt *, double *f);                                            /* [i*9+k] */
+/* the reference's geometry and initial fields (cylinder.cpp:224-312): fills mask[nx*ny], rho, ux, uy */
+void lbotrt_reference_setup(int nx, int ny, int radius, double conc_wall, int *mask, double *rho, double *ux, double *uy);
+
 #ifdef __cplusplus
 }
 #endif

@@ -9,6 +9,7 @@ using namespace lbm2;
 
 struct EmuSc { ScParams P; std::vector<double> f[2], rho, psi, u1, u2; int cur = 0; };
 struct EmuB2 { B2Params P; std::vector<double> f[2], g[2], phase, rho, ux, uy; int cur = 0; };
+struct EmuTrt { TrtParams P; std::vector<double> f[2], rho, ux, uy; std::vector<unsigned short> links; int cur = 0; };
 struct EmuMrt { MrtParams P; std::vector<double> f[2], force, rho, ux, uy; int cur = 0; };
 
 extern "C" {
@@ -125,5 +126,40 @@ void emumrt_get(EmuMrt *e, double *rho, double *ux, double *uy, double *f)
 void emumrt_wave(int variant, int nx, int ny, double ampl, double force_ampl, double *rho, double *ux, double *uy)
 {
     mrt_reference_wave(variant, nx, ny, ampl, force_ampl, rho, ux, uy);
+}
+// ---- TRT diffusion ----
+EmuTrt *emutrt_create(int nx, int ny, double omega, double ce, double conc_wall, const int *mask)
+{
+    EmuTrt *e = new EmuTrt;
+    e->P = TrtParams{nx, ny, 2.0 - omega, omega, ce, conc_wall};
+    size_t n = (size_t)nx * ny;
+    for (int i = 0; i < 2; i++) e->f[i].assign(9 * n, 0.0);
+    e->rho.assign(n, 0.0); e->ux.assign(n, 0.0); e->uy.assign(n, 0.0);
+    e->links.assign(n, 0);
+    for (size_t i = 0; i < n; i++) e->links[i] = trt_links_thread(e->P, mask, (long long)i);
+    return e;
+}
+void emutrt_destroy(EmuTrt *e) { delete e; }
+void emutrt_init(EmuTrt *e, const double *rho, const double *ux, const double *uy)
+{
+    size_t n = (size_t)e->P.nx * e->P.ny;
+    memcpy(e->rho.data(), rho, n * 8); memcpy(e->ux.data(), ux, n * 8); memcpy(e->uy.data(), uy, n * 8);
+    for (size_t i = 0; i < n; i++) trt_init_thread(e->P, e->rho.data(), e->ux.data(), e->uy.data(), e->f[0].data(), e->f[1].data(), i);
+}
+void emutrt_step(EmuTrt *e, int steps)
+{
+    size_t n = (size_t)e->P.nx * e->P.ny;
+    for (int t = 0; t < steps; t++) {
+        int a = e->cur, b = 1 - a;
+        for (size_t i = 0; i < n; i++)
+            trt_thread(e->P, e->f[a].data(), e->links.data(), e->ux.data(), e->uy.data(), e->f[b].data(), e->rho.data(), (long long)i);
+        e->cur = b;
+    }
+}
+void emutrt_get(EmuTrt *e, double *rho, double *f)
+{
+    size_t n = (size_t)e->P.nx * e->P.ny;
+    memcpy(rho, e->rho.data(), n * 8);
+    for (size_t i = 0; i < n; i++) for (int k = 0; k < 9; k++) f[i * 9 + k] = e->f[e->cur][k * n + i];
 }
 }

@@ -14,8 +14,14 @@ _meta = None
 def _load():
     global _npz, _meta
     if _npz is None:
-        _npz = np.load(os.path.join(HERE, "golden", "golden.npz"))
-        _meta = json.load(open(os.path.join(HERE, "golden", "golden.json")))
+        # golden.npz/json (make_golden.py) plus the additive sets golden_<name>.npz/json (make_golden_<name>.py)
+        import glob
+        _npz, _meta = {}, {}
+        for jf in sorted(glob.glob(os.path.join(HERE, "golden", "golden*.json"))):
+            _meta.update(json.load(open(jf)))
+            with np.load(jf[:-5] + ".npz") as z:
+                for k in z.files:
+                    _npz[k] = z[k]
     return _npz, _meta
 
 

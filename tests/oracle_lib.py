@@ -77,6 +77,14 @@ def oracle():
         L.lbomrt_step.argtypes = [C.c_void_p, C.c_int]
         L.lbomrt_get_fields.argtypes = [C.c_void_p, dp, dp, dp]
         L.lbomrt_get_pops.argtypes = [C.c_void_p, dp]
+        L.lbotrt_create.restype = C.c_void_p
+        L.lbotrt_create.argtypes = [C.c_int, C.c_int, C.c_double, C.c_double, C.c_double, C.c_void_p]
+        L.lbotrt_destroy.argtypes = [C.c_void_p]
+        L.lbotrt_init.argtypes = [C.c_void_p, dp, dp, dp]
+        L.lbotrt_step.argtypes = [C.c_void_p, C.c_int]
+        L.lbotrt_get_rho.argtypes = [C.c_void_p, dp]
+        L.lbotrt_get_pops.argtypes = [C.c_void_p, dp]
+        L.lbotrt_reference_setup.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double, C.c_void_p, dp, dp, dp]
         _oracle = L
     return _oracle
 
@@ -312,6 +320,97 @@ class OracleMRT:
         f = np.empty(self.n * 9)
         self.L.lbomrt_get_pops(self.h, _p(f))
         return f.reshape(-1, 9)
+
+
+TRT_OMEGA = 1.0 / (0.5 + 0.5 / 32.0)   # cylinder.cpp:38
+
+
+class OracleTRT:
+    """DiffusionCylinder/cylinder.cpp restated (oracle/lbm_oracle.c, lbotrt_*); node i = iY*nx+iX."""
+
+    def __init__(self, nx, ny, mask, omega=TRT_OMEGA, ce=1.0 / 3.0, conc_wall=1.0):
+        self.L = oracle()
+        self.nx, self.ny, self.n = nx, ny, nx * ny
+        self.mask = np.ascontiguousarray(mask, dtype=np.int32).ravel()
+        self.h = self.L.lbotrt_create(nx, ny, omega, ce, conc_wall, self.mask.ctypes.data)
+
+    def close(self):
+        if self.h:
+            self.L.lbotrt_destroy(self.h)
+            self.h = None
+
+    def init(self, rho, ux, uy):
+        a = [np.ascontiguousarray(x, dtype=np.float64).ravel() for x in (rho, ux, uy)]
+        self.L.lbotrt_init(self.h, *[_p(x) for x in a])
+
+    def step(self, n):
+        self.L.lbotrt_step(self.h, n)
+
+    def rho(self):
+        r = np.empty(self.n)
+        self.L.lbotrt_get_rho(self.h, _p(r))
+        return r
+
+    def pops(self):
+        f = np.empty(self.n * 9)
+        self.L.lbotrt_get_pops(self.h, _p(f))
+        return f.reshape(-1, 9)
+
+
+def trt_reference_setup(nx=129, ny=129, radius=40, conc_wall=1.0):
+    """cylinder.cpp:224-296 through the oracle: mask, rho, ux, uy."""
+    n = nx * ny
+    mask, rho, ux, uy = np.zeros(n, np.int32), np.empty(n), np.empty(n), np.empty(n)
+    oracle().lbotrt_reference_setup(nx, ny, radius, conc_wall, mask.ctypes.data, _p(rho), _p(ux), _p(uy))
+    return mask, rho, ux, uy
+
+
+def trt_random_case(nx, ny, seed, speed=0.05):
+    """A random blob geometry that satisfies lbm_set_geometry's rules, with random rho and a random
+    velocity field: fluid = a thresholded smooth random field kept off the array edge."""
+    rng = np.random.default_rng(seed)
+    a = rng.standard_normal((ny, nx))
+    for _ in range(3):
+        a = (a + np.roll(a, 1, 0) + np.roll(a, -1, 0) + np.roll(a, 1, 1) + np.roll(a, -1, 1)) / 5.0
+    fluid = a > 0.0
+    fluid[:2, :] = fluid[-2:, :] = False
+    fluid[:, :2] = fluid[:, -2:] = False
+    pad = np.pad(fluid, 1)
+    near = np.zeros_like(fluid)
+    for dy in (-1, 0, 1):
+        for dx in (-1, 0, 1):
+            near |= pad[1 + dy:1 + dy + ny, 1 + dx:1 + dx + nx]
+    mask = np.where(fluid, 1, np.where(near, 0, -1)).astype(np.int32)
+    rho = rng.uniform(0.0, 1.0, (ny, nx))
+    ux, uy = rng.uniform(-speed, speed, (ny, nx)), rng.uniform(-speed, speed, (ny, nx))
+    return mask.ravel(), rho.ravel(), ux.ravel(), uy.ravel()
+
+
+def hashed_uniform(n, salt):
+    """n doubles in [0,1) from integer arithmetic only (identical on every machine and numpy version)."""
+    i = np.arange(n, dtype=np.uint64)
+    return (((i * np.uint64(2654435761) + np.uint64(salt) * np.uint64(40503)) % np.uint64(2 ** 32)).astype(np.float64)) / 2.0 ** 32
+
+
+def trt_advected_fields(mask, conc_wall, speed=0.05):
+    """A non-trivial initial state on the reference geometry: hashed rho in the fluid, hashed velocity everywhere."""
+    n = mask.size
+    rho = np.where(mask == 1, hashed_uniform(n, 1), np.where(mask == 0, conc_wall, -1.0))
+    ux = (hashed_uniform(n, 2) - 0.5) * (2 * speed)
+    uy = (hashed_uniform(n, 3) - 0.5) * (2 * speed)
+    return rho, ux, uy
+
+
+def ref_cylinder_run(steps, omega=0.0, ce=0.0, conc_wall=0.0, rho=None, ux=None, uy=None):
+    """The unmodified cylinder.cpp (129x129, radius 40) for `steps` loop iterations; omega <= 0 keeps its constants."""
+    L = C.CDLL(os.path.join(REF_DIR, "libref_cylinder.so"))
+    L.refcyl_run.argtypes = [C.c_int, C.c_double, C.c_double, C.c_double, dp, dp, dp, dp, dp, C.c_void_p]
+    n = 129 * 129
+    keep = [None if x is None else np.ascontiguousarray(x, dtype=np.float64).ravel() for x in (rho, ux, uy)]
+    r, f, g = np.empty(n), np.empty(n * 9), np.zeros(n, np.int32)
+    rc = L.refcyl_run(steps, omega, ce, conc_wall, *[None if x is None else _p(x) for x in keep], _p(r), _p(f), g.ctypes.data)
+    assert rc == 0, rc
+    return dict(nx=129, ny=129, rho=r, f=f.reshape(-1, 9), geometry=g)
 
 
 def _scratch():

@@ -89,3 +89,16 @@ def test_microchannel_quarter_vts(tmp_path):
     for name, arr in (("phase", a["Phase"]), ("rho", a["Density"]), ("ux", vel[:, 0]), ("uy", vel[:, 1]), ("uz", vel[:, 2])):
         assert gl.check("quarter_t100", name, np.ascontiguousarray(arr))[0] == 0, name
     assert a["Points"].reshape(-1, 3)[28].tolist() == [1.0, 1.0, 0.0]
+
+
+def test_cylinder_program_files(tmp_path):
+    """hosts/cylinder.cpp: the complete 64001-iteration run; fingerprints taken from the unmodified
+    DiffusionCylinder/cylinder.cpp built with g++ -O2 -ffp-contract=off and run in an empty directory
+    holding ./antibb (321 files)."""
+    os.mkdir(tmp_path / "antibb")
+    out = _run("cylinder", [], str(tmp_path))
+    assert hashlib.sha256(out.encode()).hexdigest()[:16] == "6363b74654d9bd53"
+    assert _sha16(tmp_path / "antibb" / "density0000000.dat") == "57cf3c67cd2af58f"
+    assert _sha16(tmp_path / "antibb" / "density0000200.dat") == "3d0afc83ee2ff0a7"
+    assert _sha16(tmp_path / "antibb" / "density0064000.dat") == "b719d0f7297f1ed1"
+    assert len(os.listdir(tmp_path / "antibb")) == 321

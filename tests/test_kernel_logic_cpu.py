@@ -91,6 +91,11 @@ def _emu2(path):
     L.emub2_init.argtypes = [C.c_void_p, dp]
     L.emub2_step.argtypes = [C.c_void_p, C.c_int]
     L.emub2_get.argtypes = [C.c_void_p] + [dp] * 6
+    L.emutrt_create.restype = C.c_void_p
+    L.emutrt_create.argtypes = [C.c_int, C.c_int, C.c_double, C.c_double, C.c_double, C.c_void_p]
+    L.emutrt_init.argtypes = [C.c_void_p] + [dp] * 3
+    L.emutrt_step.argtypes = [C.c_void_p, C.c_int]
+    L.emutrt_get.argtypes = [C.c_void_p] + [dp] * 2
     L.emumrt_create.restype = C.c_void_p
     L.emumrt_create.argtypes = [C.c_int] * 3 + [C.c_double] * 3
     L.emumrt_init.argtypes = [C.c_void_p] + [dp] * 3
@@ -169,4 +174,35 @@ def test_mrt_threads_match_oracle(emu_libs, variant, om, ob, fa, shape):
         for i, k in enumerate(("rho", "ux", "uy")):
             assert ndiff(a[k], out[i]) == 0, (k, s)
         assert ndiff(o.pops().ravel(), out[3]) == 0
+    o.close()
+
+
+@pytest.mark.parametrize("case", ["cylinder", "cylinder_advected", "blobs_40x33", "blobs_97x61"])
+def test_trt_threads_match_oracle(emu_libs, case):
+    """k_trt_init / k_trt_step thread functions (push with folded anti-bounce-back, link bytes) against the oracle."""
+    L = _emu2(emu_libs["d2q9"])
+    omega, ce, cw = ol.TRT_OMEGA, 1.0 / 3.0, 1.0
+    if case.startswith("cylinder"):
+        nx = ny = 129
+        mask, rho, ux, uy = ol.trt_reference_setup()
+        if case == "cylinder_advected":
+            omega, ce, cw = 1.3, 0.25, 0.7
+            rho, ux, uy = ol.trt_advected_fields(mask, cw)
+    else:
+        nx, ny = [int(v) for v in case.split("_")[1].split("x")]
+        mask, rho, ux, uy = ol.trt_random_case(nx, ny, seed=nx)
+        omega, ce, cw = 0.9, 0.3, 1.5
+    n = nx * ny
+    o = ol.OracleTRT(nx, ny, mask, omega, ce, cw)
+    o.init(rho, ux, uy)
+    e = L.emutrt_create(nx, ny, omega, ce, cw, mask.ctypes.data)
+    L.emutrt_init(e, _p(rho), _p(ux), _p(uy))
+    for s in (0, 1, 2, 150):
+        o.step(s)
+        L.emutrt_step(e, s)
+        r, f = np.empty(n), np.empty(9 * n)
+        L.emutrt_get(e, _p(r), _p(f))
+        assert ndiff(o.rho(), r) == 0, s
+        assert ndiff(o.pops().ravel(), f) == 0, s
+    L.emutrt_destroy(e)
     o.close()

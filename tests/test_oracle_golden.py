@@ -105,3 +105,29 @@ def test_shared_exp_vs_libm_spread():
     a = a[::ent["stride"]]
     spread = np.max(np.abs(a - b)) / np.max(np.abs(b))
     assert 0 < spread < 1e-3
+
+
+@pytest.mark.parametrize("steps", [1, 2, 201, 4001])
+def test_trt_cylinder(steps):
+    """DiffusionCylinder/cylinder.cpp as shipped (zero velocity)."""
+    tag = "trt_t%d" % steps
+    mask, rho, ux, uy = ol.trt_reference_setup()
+    assert ol.ndiff(mask.astype(np.float64), gl.samples("trt_geometry", "mask")[0]) == 0
+    o = ol.OracleTRT(129, 129, mask)
+    o.init(rho, ux, uy)
+    o.step(steps)
+    _exact(tag, dict(rho=o.rho(), f=o.pops()))
+    o.close()
+
+
+@pytest.mark.parametrize("steps", [1, 500])
+def test_trt_cylinder_advected(steps):
+    """The same program with a velocity field and other constants (set through its globals)."""
+    m = gl.meta("trt_adv_t%d" % steps)
+    mask, _, _, _ = ol.trt_reference_setup()
+    rho, ux, uy = ol.trt_advected_fields(mask, m["conc_wall"])
+    o = ol.OracleTRT(129, 129, mask, m["omega"], m["ce"], m["conc_wall"])
+    o.init(rho, ux, uy)
+    o.step(steps)
+    _exact("trt_adv_t%d" % steps, dict(rho=o.rho(), f=o.pops()))
+    o.close()

@@ -89,3 +89,19 @@ def test_shanchen(shared):
         assert ol.ndiff(r[k], fl[k]) == 0, k
     assert ol.ndiff(r["f"], o.pops()) == 0
     o.close()
+
+
+@pytest.mark.skipif(not ol.ref_available("cylinder"), reason="oracle/_ref not built")
+@pytest.mark.parametrize("omega,ce,cw", [(0.0, 0.0, 0.0), (0.8, 0.3, 2.0)])
+def test_trt_cylinder(omega, ce, cw):
+    mask, rho0, _, _ = ol.trt_reference_setup(conc_wall=cw if omega > 0 else 1.0)
+    rho, ux, uy = ol.trt_advected_fields(mask, cw if omega > 0 else 1.0, speed=0.08)
+    args = (omega, ce, cw) if omega > 0 else ()
+    for steps in (0, 1, 3, 120):
+        o = ol.OracleTRT(129, 129, mask, *args)
+        o.init(rho, ux, uy)
+        o.step(steps)
+        r = ol.ref_cylinder_run(steps, omega, ce, cw, rho, ux, uy)
+        assert ol.ndiff(r["geometry"], mask) == 0
+        assert ol.ndiff(r["rho"], o.rho()) == 0 and ol.ndiff(r["f"], o.pops()) == 0, steps
+        o.close()

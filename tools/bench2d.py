@@ -59,6 +59,22 @@ def main():
         ms = timed(ctx, 20)
         out.append(("mrt_%s_d2q9" % variant, ms, 144))
         ctx.close()
+    # TRT diffusion: the reference disc scaled to the grid (radius 40/129 of the side); updates = fluid nodes
+    mask, rho, ux, uy = api.trt_cylinder_setup(n, n, radius=int(n * 40 / 129))
+    ctx = api.Context(api.trt_config(n, n))
+    ctx.set_geometry(mask)
+    ctx.set_field("rho", rho)
+    ctx.set_field("ux", ux)
+    ctx.set_field("uy", uy)
+    ctx.init()
+    ms = timed(ctx, 20)
+    fluid = int((mask == 1).sum())
+    ctx.close()
+    # 9 reads + 9 writes + rho write + ux, uy reads = 168 B per fluid node, + 2 B link word per node of the array
+    print(json.dumps({"model": "trt_diffusion_d2q9", "grid": [n, n], "fluid_nodes": fluid, "ms_per_step": ms,
+                      "mlups": fluid / ms / 1e3, "bytes_per_update": 168,
+                      "achieved_gbs": (fluid * 168 + n * n * 2) / ms / 1e6,
+                      "frac_of_measured_hbm": (fluid * 168 + n * n * 2) / ms / 1e6 / peak}))
     for name, ms, b in out:
         mlups = n * n / ms / 1e3
         print(json.dumps({"model": name, "grid": [n, n], "ms_per_step": ms, "mlups": mlups, "bytes_per_update": b,
