@@ -59,7 +59,8 @@ typedef enum {
     LBM_MRT_GS_D2Q9 = 2,       /* MRT/mrt.cpp */
     LBM_MRT_HERMITE_D2Q9 = 3,  /* MRT/another_mrt.cpp */
     LBM_BINARY_D3Q19 = 4,      /* Microchannel3D/{FullChannel,QuarterChannel} */
-    LBM_TRT_DIFFUSION_D2Q9 = 5 /* DiffusionCylinder/cylinder.cpp: TRT advection-diffusion, anti-bounce-back on a masked domain */
+    LBM_TRT_DIFFUSION_D2Q9 = 5, /* DiffusionCylinder/cylinder.cpp: TRT advection-diffusion, anti-bounce-back on a masked domain */
+    LBM_BINARY_SHAPE_D2Q9 = 6  /* CurvedSolid/binary_shape.cpp: binary liquid around a curved solid, wetting through the wall-normal phase gradient */
 } lbm_model;
 
 typedef enum { LBM_RHO = 0, LBM_PHASE = 1, LBM_UX = 2, LBM_UY = 3, LBM_UZ = 4 } lbm_field;
@@ -71,9 +72,9 @@ typedef struct {
     double tau, g;             /* Shan-Chen: shanchen.cpp:21,27 */
     double aconst, kconst, gammaconst;      /* binary.cpp:29-31; main.cpp:49-51 */
     double tau_gas, tau_liq, tau_phi;       /* binary.cpp:36-41 (omega_phi = 1/tau_phi); main.cpp:55-57 */
-    double wall_gradient;      /* binary.cpp:32; 3-D: phase_gradient, main.cpp:52 */
+    double wall_gradient;      /* binary.cpp:32; binary_shape.cpp:31; 3-D: phase_gradient, main.cpp:52 */
     double rho_wall;           /* main.cpp:54 */
-    double force[3];           /* main.cpp:58-60 (FullChannel: :50-53) */
+    double force[3];           /* main.cpp:58-60 (FullChannel: :50-53); binary_shape.cpp:39-40 (x, y) */
     double omega, omega_bulk;  /* mrt.cpp:53-54; another_mrt.cpp:52-53 */
     double force_ampl;         /* mrt.cpp:98 */
     double ce, conc_wall;      /* cylinder.cpp:43,33; the TRT rates are omega_minus = omega, omega_plus = 2 - omega (:38-40) */
@@ -103,16 +104,20 @@ size_t lbm_local_nodes(const lbm_ctx *ctx); /* nx*ny*nz_local */
  * 2-D programs' direct writes to rho/phase/u.  n = lbm_local_nodes(). */
 lbm_status lbm_set_field(lbm_ctx *ctx, int field, const double *host, size_t n);
 
-/* LBM_TRT_DIFFUSION_D2Q9 only.  Replaces: the geometry array the program builds in
- * initialize_geometry() (cylinder.cpp:224-283) together with bb_nodes/dirs (:264-283, :303-312), which the
- * library derives from it.  mask[iY*nx+iX]: 1 fluid, 0 anti-bounce-back boundary node, -1 solid;
- * n = lbm_local_nodes().  LBM_EINVAL if a fluid node lies on the edge of the array or touches a solid
- * node (the reference would stream from outside the array / from a node it never updates).  Call before
- * lbm_init. */
+/* The two masked models.  Replaces: the geometry array the program builds in initialize_geometry()
+ * (cylinder.cpp:224-283; binary_shape.cpp:439-480) together with bb_nodes/dirs/main_dir (cylinder.cpp:264-283,
+ * :303-312; binary_shape.cpp:485-588), which the library derives from it.  mask[iY*nx+iX]: 1 fluid,
+ * 0 boundary (anti-bounce-back / bounce-back) node, -1 solid; n = lbm_local_nodes().  Call before lbm_init.
+ * LBM_EINVAL where the reference itself would read outside its arrays or from nodes it never updates:
+ *   both: a fluid node touches a solid node;
+ *   LBM_TRT_DIFFUSION_D2Q9 (not periodic): a fluid node lies on the edge of the array;
+ *   LBM_BINARY_SHAPE_D2Q9 (periodic): a boundary node lies on the edge of the array, or its wall normal
+ *   (binary_shape.cpp:556-588) does not exist or does not point at a fluid node. */
 lbm_status lbm_set_geometry(lbm_ctx *ctx, const int *mask, size_t n);
 
 /* Replaces: init() of binary.cpp:122-198; the init loops of shanchen.cpp:87-114
- * (from the rho field), mrt.cpp:97-120 / another_mrt.cpp:89-110 and cylinder.cpp:97-124 (from rho,ux,uy);
+ * (from the rho field), mrt.cpp:97-120 / another_mrt.cpp:89-110 and cylinder.cpp:97-124 (from rho,ux,uy),
+ * binary_shape.cpp:222-258 (from rho,phase,ux,uy);
  * Solver::init (solver.hpp:871-879) incl. its phase halo exchange. */
 lbm_status lbm_init(lbm_ctx *ctx);
 
@@ -123,7 +128,8 @@ lbm_status lbm_get_populations(lbm_ctx *ctx, int set, double *host_aos, size_t n
 
 /* Replaces the body of the time loop: shanchen.cpp:120-188, binary.cpp:336-350
  * (collide_bulk, update_bounce_back, streaming), mrt.cpp:144-251, cylinder.cpp:355-358
- * (collide, update_bounce_back, stream),
+ * (collide, update_bounce_back, stream), binary_shape.cpp:666-669 (update_phase, collide_bulk,
+ * update_bounce_back, stream),
  * another_mrt.cpp:112-214, Solver::collide_stream (solver.hpp:881-891: updateMacro,
  * updatePhase, Lattice::collide_stream, propagate, exchangeMatrices).
  * Asynchronous: returns once the work is queued; any call that reads results waits. */

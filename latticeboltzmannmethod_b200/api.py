@@ -13,7 +13,7 @@ _PKG = os.path.dirname(os.path.abspath(__file__))
 _LIB = os.path.join(_PKG, "liblbm_b200.so")
 
 MODELS = dict(shanchen_d2q9=0, binary_d2q9=1, mrt_gs_d2q9=2, mrt_hermite_d2q9=3, binary_d3q19=4,
-              trt_diffusion_d2q9=5)
+              trt_diffusion_d2q9=5, binary_shape_d2q9=6)
 FIELDS = dict(rho=0, phase=1, ux=2, uy=3, uz=4)
 HALO = dict(S_F_UP=0, S_G_UP=1, S_F_DOWN=2, S_G_DOWN=3, R_F_FROM_BELOW=4, R_G_FROM_BELOW=5, R_F_FROM_ABOVE=6,
             R_G_FROM_ABOVE=7, S_PHI_UP=8, S_PHI_DOWN=9, R_PHI_FROM_BELOW=10, R_PHI_FROM_ABOVE=11)
@@ -358,6 +358,44 @@ def trt_cylinder_setup(nx=129, ny=129, radius=40, conc_wall=1.0):
     mask[(mask == 0) & ~touches(mask, 1)] = -1         # boundary nodes with no fluid neighbour are solid
     rho = np.where(mask == 0, conc_wall, np.where(mask == -1, -1.0, 0.0)).astype(np.float64)
     return mask.ravel(), rho.ravel(), np.zeros(nx * ny), np.zeros(nx * ny)
+
+
+def shape_config(nx=301, ny=301, wall_gradient=None, device=0, **kw):
+    """CurvedSolid/binary_shape.cpp:17-48; kw: aconst, kconst, gammaconst, tau_gas, tau_liq, tau_phi."""
+    c = default_config("binary_shape_d2q9")
+    c.nx, c.ny, c.device = nx, ny, device
+    if wall_gradient is not None:
+        c.wall_gradient = wall_gradient
+    for k, v in kw.items():
+        setattr(c, k, v)
+    return c
+
+
+def shape_setup(nx=301, ny=301, radius=50, radius_droplet=10, num_droplets=3):
+    """binary_shape.cpp:439-520: a solid disc in the centre of a periodic box, the solid nodes that touch
+    fluid turned into bounce-back nodes, `num_droplets` droplets (phi = +1) sitting on the disc in a phi = -1
+    bath; rho = 1 in the fluid, rho_wall = 0.5 and phi_wall = 1.5 elsewhere.
+    Returns mask, rho, phi, ux, uy flat [iY*nx+iX]."""
+    import math
+    iy, ix = np.meshgrid(np.arange(ny), np.arange(nx), indexing="ij")
+    solid = (ix - (nx - 1) // 2) ** 2 + (iy - (ny - 1) // 2) ** 2 < radius * radius
+    mask = np.where(solid, -1, 1).astype(np.int32)
+    near_fluid = np.zeros(mask.shape, bool)
+    for dy in (-1, 0, 1):
+        for dx in (-1, 0, 1):
+            if dx or dy:
+                near_fluid |= np.roll(np.roll(mask, -dy, 0), -dx, 1) == 1
+    mask[(mask == -1) & near_fluid] = 0
+    rho = np.where(mask == 1, 1.0, 0.5)
+    pi = 4.0 * math.atan(1.0)
+    angle = 360 // num_droplets
+    drop = np.zeros(mask.shape, bool)
+    for d in range(num_droplets):
+        cx = (nx - 1) // 2 - math.sin(angle * (d - 1) * pi / 180.0) * (radius_droplet + radius)
+        cy = (ny - 1) // 2 + math.cos(angle * (d - 1) * pi / 180.0) * (radius_droplet + radius)
+        drop |= ((ix - cx) * (ix - cx) + (iy - cy) * (iy - cy) <= radius_droplet * radius_droplet) & (mask == 1)
+    phi = np.where(drop, 1.0, np.where(mask == 1, -1.0, 1.5))
+    return mask.ravel(), rho.ravel().astype(np.float64), phi.ravel().astype(np.float64), np.zeros(nx * ny), np.zeros(nx * ny)
 
 
 def microchannel_config(which="quarter", nx=None, ny=None, nz=None, device=0, slab_rank=0, slab_count=1):

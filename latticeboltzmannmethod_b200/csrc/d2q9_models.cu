@@ -1,6 +1,7 @@
 // d2q9_models.cu -- the D2Q9 programs on one GPU: Shan-Chen
 // (ShanChen/shanchen.cpp), binary liquid (FreeEnergy/binary.cpp), MRT
-// (MRT/mrt.cpp, MRT/another_mrt.cpp) and TRT diffusion (DiffusionCylinder/cylinder.cpp).  Per-thread arithmetic: d2q9_threads.h.
+// (MRT/mrt.cpp, MRT/another_mrt.cpp), TRT diffusion (DiffusionCylinder/cylinder.cpp) and the
+// binary liquid around a curved solid (CurvedSolid/binary_shape.cpp).  Per-thread arithmetic: d2q9_threads.h.
 #include <vector>
 
 #include "d2q9_host.h"
@@ -80,6 +81,27 @@ __global__ void __launch_bounds__(kThreads) k_trt_step(lbm2::TrtParams P, const 
 {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < (long long)P.nx * P.ny) lbm2::trt_thread(P, f, links, ux, uy, f2, rho, i);
+}
+// ---- binary liquid around a curved solid (node index i = iY*nx+iX) ----
+__global__ void __launch_bounds__(kThreads) k_bs_init(lbm2::BsParams P, const double *rho, const double *phi, const double *ux,
+                                                       const double *uy, double *fa, double *ga, double *fb, double *gb)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < (long long)P.nx * P.ny) lbm2::bs_init_thread(P, rho, phi, ux, uy, fa, ga, fb, gb, i);
+}
+__global__ void __launch_bounds__(kThreads) k_bs_phase(lbm2::BsParams P, const double *__restrict__ g,
+                                                        const unsigned short *__restrict__ links, double *__restrict__ phi)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < (long long)P.nx * P.ny) lbm2::bs_phase_thread(P, g, links, phi, i);
+}
+__global__ void __launch_bounds__(kThreads) k_bs_collide(lbm2::BsParams P, const double *__restrict__ f, const double *__restrict__ g,
+                                                          const double *__restrict__ phi, const unsigned short *__restrict__ links,
+                                                          double *__restrict__ f2, double *__restrict__ g2, double *__restrict__ rho,
+                                                          double *__restrict__ ux, double *__restrict__ uy)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < (long long)P.nx * P.ny) lbm2::bs_collide_thread(P, f, g, phi, links, f2, g2, rho, ux, uy, i);
 }
 // ---- AoS <-> SoA at the boundary ----
 __global__ void __launch_bounds__(kThreads) k_aos_to_soa9(long long n, const double *aos, double *soa)
@@ -391,6 +413,97 @@ private:
     bool have_geometry_ = false;
 };
 
+// CurvedSolid/binary_shape.cpp: phase pass + collide/push pass per step on a masked periodic domain
+class BinaryShape : public Model2D {
+public:
+    BinaryShape(Runtime &rt, const lbm_config &cfg) : Model2D(rt, cfg, 2) {}
+    ~BinaryShape() override { cudaFree(links_); }
+    lbm_status setup()
+    {
+        LBM_TRY(alloc_common());
+        P_ = lbm2::BsParams{cfg_.nx, cfg_.ny, cfg_.aconst, cfg_.kconst, cfg_.gammaconst, cfg_.wall_gradient, cfg_.tau_gas,
+                            cfg_.tau_liq - cfg_.tau_gas, 1.0 / cfg_.tau_phi, cfg_.force[0], cfg_.force[1]};
+        LBM_CUDA(rt_, cudaMalloc(&links_, n_ * sizeof(unsigned short)));
+        LBM_CUDA(rt_, cudaMemset(links_, 0, n_ * sizeof(unsigned short)));
+        return LBM_OK;
+    }
+    bool has_field(int f) const override { return f == LBM_RHO || f == LBM_PHASE || f == LBM_UX || f == LBM_UY; }
+    lbm_status set_geometry(const int *mask) override
+    {
+        const int nx = cfg_.nx, ny = cfg_.ny;
+        const int CX[9] = LBM2_CX, CY[9] = LBM2_CY;
+        std::vector<unsigned short> links((size_t)n_);
+        for (long long i = 0; i < n_; i++) {
+            if (mask[i] < -1 || mask[i] > 1) return rt_.fail(LBM_EINVAL, "lbm_set_geometry: mask values are 1 (fluid), 0 (bounce-back), -1 (solid)");
+            const int ix = (int)(i % nx), iy = (int)(i / nx);
+            if (mask[i] == 0) {
+                // binary_shape.cpp:364,430 index the neighbours of a bounce-back node without the periodic wrap
+                if (ix == 0 || iy == 0 || ix == nx - 1 || iy == ny - 1)
+                    return rt_.fail(LBM_EINVAL, "lbm_set_geometry: a bounce-back node lies on the edge of the array");
+                const int dir = lbm2::bs_main_dir(mask, nx, i);
+                if (dir == 0 || mask[i + CY[dir] * nx + CX[dir]] != 1)
+                    return rt_.fail(LBM_EINVAL, "lbm_set_geometry: a bounce-back node has no wall normal pointing at a fluid node "
+                                                "(binary_shape.cpp:556-588 would misalign main_dir)");
+            } else if (mask[i] == 1) {
+                for (int k = 1; k < 9; k++)
+                    if (mask[(long long)((iy + CY[k] + ny) % ny) * nx + (ix + CX[k] + nx) % nx] == -1)
+                        return rt_.fail(LBM_EINVAL, "lbm_set_geometry: a fluid node touches a solid node (no bounce-back node between them)");
+            }
+            links[(size_t)i] = lbm2::bs_links_thread(P_, mask, i);
+        }
+        LBM_CUDA(rt_, cudaMemcpyAsync(links_, links.data(), (size_t)n_ * sizeof(unsigned short), cudaMemcpyHostToDevice, rt_.stream));
+        LBM_CUDA(rt_, cudaStreamSynchronize(rt_.stream));
+        have_geometry_ = true;
+        return LBM_OK;
+    }
+    lbm_status init() override
+    {
+        if (!have_geometry_) return rt_.fail(LBM_ESTATE, "curved-solid binary liquid: call lbm_set_geometry before lbm_init");
+        k_bs_init<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, fields_[LBM_RHO], fields_[LBM_PHASE], fields_[LBM_UX], fields_[LBM_UY],
+                                                               f_[0], g_[0], f_[1], g_[1]);
+        return rt_.launched("k_bs_init");
+    }
+    lbm_status step(int nsteps) override
+    {
+        for (int t = 0; t < nsteps; t++) {
+            rt_.about_to_launch();
+            k_bs_phase<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, g_[cur_], links_, fields_[LBM_PHASE]);
+            LBM_TRY(rt_.launched("k_bs_phase"));
+            rt_.about_to_launch();
+            k_bs_collide<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, f_[cur_], g_[cur_], fields_[LBM_PHASE], links_, f_[1 - cur_],
+                                                                      g_[1 - cur_], fields_[LBM_RHO], fields_[LBM_UX], fields_[LBM_UY]);
+            LBM_TRY(rt_.launched("k_bs_collide"));
+            cur_ = 1 - cur_;
+        }
+        return LBM_OK;
+    }
+    // bounce-back and solid nodes are never streamed into, so a load must reach both buffers
+    lbm_status after_set_populations(int set) override
+    {
+        double *src = set == 0 ? f_[cur_] : g_[cur_], *dst = set == 0 ? f_[1 - cur_] : g_[1 - cur_];
+        return rt_.cuda(cudaMemcpyAsync(dst, src, 9 * n_ * sizeof(double), cudaMemcpyDeviceToDevice, rt_.stream), "copy populations");
+    }
+    lbm_status diagnostics(double *mass, double *mom, double *pm, int *has_nan) override
+    {
+        DiagLayout L;
+        L.f = f_[cur_]; L.g = g_[cur_];
+        L.stride_k = n_; L.plane_stride = 0; L.planes = 1; L.nx = cfg_.nx; L.ny = cfg_.ny; L.q = 9;
+        L.skip_border = 0; L.node_major_x = 1; L.fluid = links_;
+        double out[6];
+        LBM_TRY(run_diagnostics(rt_, L, diag_, diagnostics_scratch_blocks(), out));
+        if (mass) *mass = out[0];
+        if (mom) { mom[0] = out[1]; mom[1] = out[2]; mom[2] = 0.0; }
+        if (pm) *pm = out[4];
+        if (has_nan) *has_nan = out[5] != 0.0;
+        return LBM_OK;
+    }
+
+private:
+    lbm2::BsParams P_{};
+    unsigned short *links_ = nullptr;
+    bool have_geometry_ = false;
+};
+
 template <class T>
 Model *make(Runtime &rt, const lbm_config &cfg, lbm_status *st)
 {
@@ -409,5 +522,6 @@ Model *make_d2q9_shanchen(Runtime &rt, const lbm_config &cfg, lbm_status *st) { 
 Model *make_d2q9_binary(Runtime &rt, const lbm_config &cfg, lbm_status *st) { return make<Binary2D>(rt, cfg, st); }
 Model *make_d2q9_mrt(Runtime &rt, const lbm_config &cfg, lbm_status *st) { return make<Mrt>(rt, cfg, st); }
 Model *make_d2q9_trt(Runtime &rt, const lbm_config &cfg, lbm_status *st) { return make<Trt>(rt, cfg, st); }
+Model *make_d2q9_binary_shape(Runtime &rt, const lbm_config &cfg, lbm_status *st) { return make<BinaryShape>(rt, cfg, st); }
 
 }  // namespace lbm

@@ -469,5 +469,172 @@ LBM_HD void trt_thread(const TrtParams &P, const double *f, const unsigned short
     }
 }
 
+// ======================= binary liquid around a curved solid (CurvedSolid/binary_shape.cpp) =======================
+// Node index i = iY*nx+iX, periodic in both directions (binary_shape.cpp:287-288,628-629).  Geometry mask as for
+// the TRT model (1 fluid, 0 bounce-back node, -1 solid; :449-480).  One 16-bit link word per node, built once on
+// the host: fluid nodes carry bit 0 and bit k (1..8) = "the neighbour in direction k is a bounce-back node";
+// bounce-back nodes carry their wall normal main_dir (:556-588) in bits 9..12.  Half-way bounce-back
+// (:358-372) + pull streaming (:617-637) become a push in which a population sent towards a bounce-back node
+// comes straight back into the node's own opposite slot.
+struct BsParams {
+    int nx, ny;
+    double aconst, kconst, gammaconst, wall_gradient, tau_gas, tau_liq_minus_gas, omega_phi, force_x, force_y;
+};
+#define LBM_BS_WXX {0.0, 1.0 / 3.0, -1.0 / 6.0, 1.0 / 3.0, -1.0 / 6.0, -1.0 / 24.0, -1.0 / 24.0, -1.0 / 24.0, -1.0 / 24.0}
+#define LBM_BS_WYY {0.0, -1.0 / 6.0, 1.0 / 3.0, -1.0 / 6.0, 1.0 / 3.0, -1.0 / 24.0, -1.0 / 24.0, -1.0 / 24.0, -1.0 / 24.0}
+#define LBM_BS_WXY {0.0, 0.0, 0.0, 0.0, 0.0, 1.0 / 4.0, -1.0 / 4.0, 1.0 / 4.0, -1.0 / 4.0}
+#define LBM_BS_GX {0.0, 4.0 / 12.0, 0.0, -4.0 / 12.0, 0.0, 1.0 / 12.0, -1.0 / 12.0, -1.0 / 12.0, 1.0 / 12.0}
+#define LBM_BS_GY {0.0, 0.0, 4.0 / 12.0, 0.0, -4.0 / 12.0, 1.0 / 12.0, 1.0 / 12.0, -1.0 / 12.0, -1.0 / 12.0}
+#define LBM_BS_LAP {-20.0 / 6.0, 4.0 / 6.0, 4.0 / 6.0, 4.0 / 6.0, 4.0 / 6.0, 1.0 / 6.0, 1.0 / 6.0, 1.0 / 6.0, 1.0 / 6.0}
+
+// the wall normal of a bounce-back node: the lattice direction equal to the sum of the axis directions that
+// lead to fluid, or, when there is none, of the diagonal ones (:556-588); 0 = no such direction
+LBM_HD int bs_main_dir(const int *mask, int nx, long long c)
+{
+    const int CX[9] = LBM2_CX, CY[9] = LBM2_CY;
+    int sx = 0, sy = 0;
+    bool any = false;
+    for (int k = 1; k < 5; k++)
+        if (mask[c + CY[k] * nx + CX[k]] == 1) { any = true; sx += CX[k]; sy += CY[k]; }
+    if (!any)
+        for (int k = 5; k < 9; k++)
+            if (mask[c + CY[k] * nx + CX[k]] == 1) { sx += CX[k]; sy += CY[k]; }
+    for (int k = 1; k < 9; k++)
+        if (sx == CX[k] && sy == CY[k]) return k;
+    return 0;
+}
+
+// link word of node i (the host has already checked the geometry rules)
+LBM_HD unsigned short bs_links_thread(const BsParams &P, const int *mask, long long i)
+{
+    const int CX[9] = LBM2_CX, CY[9] = LBM2_CY;
+    if (mask[i] == 0) return (unsigned short)(bs_main_dir(mask, P.nx, i) << 9);
+    if (mask[i] != 1) return 0;
+    const int ix = (int)(i % P.nx), iy = (int)(i / P.nx);
+    unsigned short b = 1;
+    for (int k = 1; k < 9; k++) {
+        const long long t = (long long)((iy + CY[k] + P.ny) % P.ny) * P.nx + (ix + CX[k] + P.nx) % P.nx;
+        if (mask[t] == 0) b |= (unsigned short)(1u << k);
+    }
+    return b;
+}
+
+// :222-258: equilibrium of every node from rho, phi, ux, uy, into both buffers
+LBM_HD void bs_init_thread(const BsParams &P, const double *rho_i, const double *phi_i, const double *ux_i, const double *uy_i,
+                           double *fa, double *ga, double *fb, double *gb, long long i)
+{
+    const long long n = (long long)P.nx * P.ny;
+    const int CX[9] = LBM2_CX, CY[9] = LBM2_CY;
+    const double W[9] = LBM2_W;
+    const double dense_temp = rho_i[i], phase_temp = phi_i[i], ux_temp = ux_i[i], uy_temp = uy_i[i];
+    for (int k = 0; k < 9; k++) {
+        const int cx = CX[k], cy = CY[k];
+        const double feq = W[k] * (dense_temp + 3.0 * dense_temp * (cx * ux_temp + cy * uy_temp) +
+                                   4.5 * dense_temp * ((cx * cx - 1.0 / 3.0) * ux_temp * ux_temp + (cy * cy - 1.0 / 3.0) * uy_temp * uy_temp +
+                                                       2.0 * ux_temp * uy_temp * cx * cy));
+        const double geq = W[k] * (phase_temp + 3.0 * phase_temp * (cx * ux_temp + cy * uy_temp) +
+                                   4.5 * phase_temp * ((cx * cx - 1.0 / 3.0) * ux_temp * ux_temp + (cy * cy - 1.0 / 3.0) * uy_temp * uy_temp +
+                                                       2.0 * ux_temp * uy_temp * cx * cy));
+        fa[k * n + i] = feq; fb[k * n + i] = feq;
+        ga[k * n + i] = geq; gb[k * n + i] = geq;
+    }
+}
+
+// update_phase (:413-435): phi = sum of g on fluid nodes; a bounce-back node takes the phi of the fluid node
+// its wall normal points at, minus wall_gradient -- recomputed here from that node's g (same sum, same order)
+// so that the kernel needs no second pass
+LBM_HD void bs_phase_thread(const BsParams &P, const double *g, const unsigned short *links, double *phi, long long i)
+{
+    const unsigned link = links[i];
+    const int dir = (int)(link >> 9);
+    if (!(link & 1u) && dir == 0) return;
+    const long long n = (long long)P.nx * P.ny;
+    const int CX[9] = LBM2_CX, CY[9] = LBM2_CY;
+    const long long src = dir ? i + CY[dir] * P.nx + CX[dir] : i;
+    double phase_temp = 0.0;
+#pragma unroll
+    for (int k = 0; k < 9; k++) phase_temp += g[k * n + src];
+    phi[i] = dir ? phase_temp - P.wall_gradient : phase_temp;
+}
+
+// collide_bulk (:260-356) of one fluid node, then update_bounce_back + stream folded into the push
+LBM_HD void bs_collide_thread(const BsParams &P, const double *f, const double *g, const double *phi, const unsigned short *links,
+                              double *f2, double *g2, double *rho_o, double *ux_o, double *uy_o, long long i)
+{
+    const unsigned link = links[i];
+    if (!(link & 1u)) return;
+    const long long n = (long long)P.nx * P.ny;
+    const int CX[9] = LBM2_CX, CY[9] = LBM2_CY, OPP[9] = LBM2_OPP;
+    const double W[9] = LBM2_W;
+    const double WXX[9] = LBM_BS_WXX, WYY[9] = LBM_BS_WYY, WXY[9] = LBM_BS_WXY;
+    const double GX[9] = LBM_BS_GX, GY[9] = LBM_BS_GY, LAP[9] = LBM_BS_LAP;
+    const int ix = (int)(i % P.nx), iy = (int)(i / P.nx);
+    // periodic neighbours: (iX+cx+NX)%NX, (iY+cy+NY)%NY
+    const int xs[3] = {ix == 0 ? P.nx - 1 : ix - 1, ix, ix == P.nx - 1 ? 0 : ix + 1};
+    const int ys[3] = {iy == 0 ? P.ny - 1 : iy - 1, iy, iy == P.ny - 1 ? 0 : iy + 1};
+    long long nb[9];
+#pragma unroll
+    for (int k = 0; k < 9; k++) nb[k] = (long long)ys[CY[k] + 1] * P.nx + xs[CX[k] + 1];
+
+    double fl[9], gl[9];
+    double dense_temp = 0.0, ux_temp = 0.0, uy_temp = 0.0;
+    const double phase_temp = phi[i];
+#pragma unroll
+    for (int k = 0; k < 9; k++) {
+        fl[k] = f[k * n + i];
+        gl[k] = g[k * n + i];
+        dense_temp += fl[k];
+        ux_temp += fl[k] * CX[k];
+        uy_temp += fl[k] * CY[k];
+    }
+    ux_temp = (ux_temp + 0.5 * P.force_x) / dense_temp;
+    uy_temp = (uy_temp + 0.5 * P.force_y) / dense_temp;
+    rho_o[i] = dense_temp; ux_o[i] = ux_temp; uy_o[i] = uy_temp;
+
+    double laplace_temp = 0.0, gradx_temp = 0.0, grady_temp = 0.0;
+#pragma unroll
+    for (int k = 0; k < 9; k++) {
+        const double ph = phi[nb[k]];
+        laplace_temp += LAP[k] * ph;
+        gradx_temp += GX[k] * ph;
+        grady_temp += GY[k] * ph;
+    }
+    double sum = 0.0, sum_phase = 0.0;
+    const double phase_square = phase_temp * phase_temp;
+    const double pressure_bulk = dense_temp / 3.0 + P.aconst * (-0.5 * phase_square + 3.0 / 4.0 * phase_square * phase_square) -
+                                 P.kconst * phase_temp * laplace_temp;
+    const double chemical_pot = P.gammaconst * (P.aconst * (-phase_temp + phase_temp * phase_temp * phase_temp) - P.kconst * laplace_temp);
+    double feqeq[9], geqeq[9];
+#pragma unroll
+    for (int k = 1; k < 9; k++) {
+        const int cx = CX[k], cy = CY[k];
+        feqeq[k] = W[k] * (3.0 * pressure_bulk + 3.0 * dense_temp * (cx * ux_temp + cy * uy_temp) +
+                           4.5 * dense_temp * ((cx * cx - 1.0 / 3.0) * ux_temp * ux_temp + (cy * cy - 1.0 / 3.0) * uy_temp * uy_temp +
+                                               2.0 * ux_temp * uy_temp * cx * cy)) +
+                   P.kconst * (WXX[k] * gradx_temp * gradx_temp + WYY[k] * grady_temp * grady_temp + WXY[k] * gradx_temp * grady_temp);
+        geqeq[k] = W[k] * (3.0 * chemical_pot + 3.0 * phase_temp * (cx * ux_temp + cy * uy_temp) +
+                           4.5 * phase_temp * ((cx * cx - 1.0 / 3.0) * ux_temp * ux_temp + (cy * cy - 1.0 / 3.0) * uy_temp * uy_temp +
+                                               2.0 * ux_temp * uy_temp * cx * cy));
+        sum += feqeq[k];
+        sum_phase += geqeq[k];
+    }
+    feqeq[0] = dense_temp - sum;
+    geqeq[0] = phase_temp - sum_phase;
+    const double tau_rho = P.tau_gas + (phase_temp + 1.0) / 2.0 * P.tau_liq_minus_gas;
+    const double omega_rho = 1.0 / tau_rho;
+#pragma unroll
+    for (int k = 0; k < 9; k++) {
+        const double fo = fl[k] * (1.0 - omega_rho) + omega_rho * feqeq[k];
+        const double go = gl[k] * (1.0 - P.omega_phi) + P.omega_phi * geqeq[k];
+        if (link & (1u << k)) {      // bit 0 (the fluid flag) sends the rest population to slot OPP[0] = 0 of the node itself
+            f2[OPP[k] * n + i] = fo;
+            g2[OPP[k] * n + i] = go;
+        } else {
+            f2[k * n + nb[k]] = fo;
+            g2[k * n + nb[k]] = go;
+        }
+    }
+}
+
 }  // namespace lbm2
 #endif

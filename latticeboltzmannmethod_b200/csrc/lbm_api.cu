@@ -47,6 +47,10 @@ lbm_status lbm_config_default(lbm_config *c, int model)
     case LBM_TRT_DIFFUSION_D2Q9:  // cylinder.cpp:226-227,33,38,43
         c->nx = 129; c->ny = 129; c->omega = 1.0 / (0.5 + 0.5 / 32.0); c->ce = 1.0 / 3.0; c->conc_wall = 1.0;
         break;
+    case LBM_BINARY_SHAPE_D2Q9:  // binary_shape.cpp:17-18,31,37-48
+        c->nx = 301; c->ny = 301; c->aconst = 0.04; c->kconst = 0.04; c->gammaconst = 1.0; c->wall_gradient = -0.05;
+        c->tau_gas = 1.0; c->tau_liq = 1.0; c->tau_phi = 1.0;
+        break;
     case LBM_BINARY_D3Q19:  // QuarterChannel/main.cpp:18-20,48-62
         c->nx = 27; c->ny = 27; c->nz = 52; c->aconst = 0.04; c->kconst = 0.04; c->gammaconst = 1.0;
         c->wall_gradient = 0.0; c->rho_wall = 0.5; c->tau_phi = 2.0; c->tau_liq = 2.5; c->tau_gas = 0.7;
@@ -89,6 +93,7 @@ lbm_status lbm_create(const lbm_config *cfg, lbm_ctx **out)
         case LBM_MRT_HERMITE_D2Q9: ctx->model = lbm::make_d2q9_mrt(ctx->rt, ctx->cfg, &st); break;
         case LBM_BINARY_D3Q19: ctx->model = lbm::make_d3q19_binary(ctx->rt, ctx->cfg, &st); break;
         case LBM_TRT_DIFFUSION_D2Q9: ctx->model = lbm::make_d2q9_trt(ctx->rt, ctx->cfg, &st); break;
+        case LBM_BINARY_SHAPE_D2Q9: ctx->model = lbm::make_d2q9_binary_shape(ctx->rt, ctx->cfg, &st); break;
         default: st = ctx->rt.fail(LBM_EINVAL, "unknown model");
         }
     }
@@ -135,7 +140,7 @@ lbm_status lbm_set_field(lbm_ctx *ctx, int field, const double *host, size_t n)
 lbm_status lbm_set_geometry(lbm_ctx *ctx, const int *mask, size_t n)
 {
     LBM_ENTER(ctx);
-    if (ctx->cfg.model != LBM_TRT_DIFFUSION_D2Q9) return ctx->rt.fail(LBM_EINVAL, "lbm_set_geometry: this model has no geometry mask");
+    if (ctx->cfg.model != LBM_TRT_DIFFUSION_D2Q9 && ctx->cfg.model != LBM_BINARY_SHAPE_D2Q9) return ctx->rt.fail(LBM_EINVAL, "lbm_set_geometry: this model has no geometry mask");
     if (!mask || n != ctx->model->local_nodes()) return ctx->rt.fail(LBM_EINVAL, "lbm_set_geometry: n must equal lbm_local_nodes()");
     return ctx->model->set_geometry(mask);
 }

@@ -113,6 +113,7 @@ Model *make_d2q9_shanchen(Runtime &rt, const lbm_config &cfg, lbm_status *st);
 Model *make_d2q9_binary(Runtime &rt, const lbm_config &cfg, lbm_status *st);
 Model *make_d2q9_mrt(Runtime &rt, const lbm_config &cfg, lbm_status *st);
 Model *make_d2q9_trt(Runtime &rt, const lbm_config &cfg, lbm_status *st);
+Model *make_d2q9_binary_shape(Runtime &rt, const lbm_config &cfg, lbm_status *st);
 
 // diagnostics: block-level partial sums into scratch, then one block folds them.
 // sums[0..4] = sum f, sum f*cx, sum f*cy, sum f*cz, sum g ; sums[5] = NaN count

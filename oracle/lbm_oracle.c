@@ -1195,3 +1195,205 @@ void lbotrt_get_pops(lbotrt *s, double *f)
     for (size_t i = 0; i < s->n; i++)
         for (int k = 0; k < 9; k++) f[i * 9 + k] = s->f[k * s->n + i];
 }
+
+/* ====================================================================== */
+/* D2Q9 binary liquid around a curved solid: CurvedSolid/binary_shape.cpp  */
+/* ====================================================================== */
+/* binary_shape.cpp:74-87 -- double tables here (binary.cpp's are float) */
+static const double BS_WXX[9] = {0.0, 1.0 / 3.0, -1.0 / 6.0, 1.0 / 3.0, -1.0 / 6.0, -1.0 / 24.0, -1.0 / 24.0, -1.0 / 24.0, -1.0 / 24.0};
+static const double BS_WYY[9] = {0.0, -1.0 / 6.0, 1.0 / 3.0, -1.0 / 6.0, 1.0 / 3.0, -1.0 / 24.0, -1.0 / 24.0, -1.0 / 24.0, -1.0 / 24.0};
+static const double BS_WXY[9] = {0.0, 0.0, 0.0, 0.0, 0.0, 1.0 / 4.0, -1.0 / 4.0, 1.0 / 4.0, -1.0 / 4.0};
+static const double BS_GX[9] = {0.0, 4.0 / 12.0, 0.0, -4.0 / 12.0, 0.0, 1.0 / 12.0, -1.0 / 12.0, -1.0 / 12.0, 1.0 / 12.0};
+static const double BS_GY[9] = {0.0, 0.0, 4.0 / 12.0, 0.0, -4.0 / 12.0, 1.0 / 12.0, 1.0 / 12.0, -1.0 / 12.0, -1.0 / 12.0};
+static const double BS_LAP[9] = {-20.0 / 6.0, 4.0 / 6.0, 4.0 / 6.0, 4.0 / 6.0, 4.0 / 6.0, 1.0 / 6.0, 1.0 / 6.0, 1.0 / 6.0, 1.0 / 6.0};
+
+struct lbobs {
+    int nx, ny;
+    size_t n;
+    double aconst, kconst, gammaconst, wall_gradient, tau_gas, tau_liq, omega_phi, force_x, force_y;
+    int *mask;
+    int nbb, *bb, *bb_src;       /* bounce-back nodes in ascending index order and the node their phi is copied from */
+    double *f, *g, *f2, *g2, *phi, *rho, *ux, *uy;   /* populations SoA [k][i] */
+};
+
+/* binary_shape.cpp:556-588: sum of the axis directions that lead to fluid, else of the diagonal ones; the
+ * wall normal is the lattice direction equal to that sum */
+static int bs_main_dir(const int *mask, int nx, int c)
+{
+    int sx = 0, sy = 0, flag = 0;
+    for (int k = 1; k < 5; k++)
+        if (mask[c + C2Y[k] * nx + C2X[k]] == 1) { flag = 1; sx += C2X[k]; sy += C2Y[k]; }
+    if (!flag)
+        for (int k = 5; k < 9; k++)
+            if (mask[c + C2Y[k] * nx + C2X[k]] == 1) { sx += C2X[k]; sy += C2Y[k]; }
+    for (int k = 1; k < 9; k++)
+        if (sx == C2X[k] && sy == C2Y[k]) return k;
+    return 0;
+}
+
+lbobs *lbobs_create(int nx, int ny, const double *p, const int *mask)
+{
+    lbobs *s = (lbobs *)calloc(1, sizeof *s);
+    s->nx = nx; s->ny = ny; s->n = (size_t)nx * ny;
+    s->aconst = p[0]; s->kconst = p[1]; s->gammaconst = p[2]; s->wall_gradient = p[3];
+    s->tau_gas = p[4]; s->tau_liq = p[5]; s->omega_phi = p[6]; s->force_x = p[7]; s->force_y = p[8];
+    s->mask = (int *)malloc(s->n * sizeof(int));
+    memcpy(s->mask, mask, s->n * sizeof(int));
+    s->bb = (int *)malloc(s->n * sizeof(int));
+    s->bb_src = (int *)malloc(s->n * sizeof(int));
+    for (size_t c = 0; c < s->n; c++) {
+        if (mask[c] != 0) continue;
+        int ix = (int)(c % nx), iy = (int)(c / nx);
+        int k = (ix == 0 || iy == 0 || ix == nx - 1 || iy == ny - 1) ? 0 : bs_main_dir(mask, nx, (int)c);
+        if (k == 0 || mask[c + C2Y[k] * nx + C2X[k]] != 1) { lbobs_destroy(s); return NULL; }
+        s->bb[s->nbb] = (int)c;
+        s->bb_src[s->nbb++] = (int)c + C2Y[k] * nx + C2X[k];
+    }
+    double **arr[] = {&s->f, &s->g, &s->f2, &s->g2};
+    for (int a = 0; a < 4; a++) *arr[a] = (double *)calloc(9 * s->n, sizeof(double));
+    double **fld[] = {&s->phi, &s->rho, &s->ux, &s->uy};
+    for (int a = 0; a < 4; a++) *fld[a] = (double *)calloc(s->n, sizeof(double));
+    return s;
+}
+void lbobs_destroy(lbobs *s)
+{
+    if (!s) return;
+    free(s->mask); free(s->bb); free(s->bb_src);
+    free(s->f); free(s->g); free(s->f2); free(s->g2); free(s->phi); free(s->rho); free(s->ux); free(s->uy);
+    free(s);
+}
+
+/* binary_shape.cpp:439-520 with NX, NY, radius, radius_droplet as arguments (rho_wall 0.5, phi_wall 1.5,
+ * three droplets 120 degrees apart) */
+void lbobs_reference_setup(int nx, int ny, int radius, int radius_droplet, int *mask, double *rho, double *phi, double *ux, double *uy)
+{
+    const double pi = 4.0 * atan(1.0), phi_wall = 1.5, rho_wall = 0.5;
+    const int angle = 360 / 3, n = nx * ny;
+    for (int c = 0; c < n; c++) {
+        int ix = c % nx, iy = c / nx;
+        mask[c] = ((ix - (nx - 1) / 2) * (ix - (nx - 1) / 2) + (iy - (ny - 1) / 2) * (iy - (ny - 1) / 2) < radius * radius) ? -1 : 1;
+    }
+    for (int c = 0; c < n; c++) {
+        int flag = 0;
+        if (mask[c] == -1) {
+            int ix = c % nx, iy = c / nx;
+            for (int k = 1; k < 9; k++)
+                if (mask[((iy + C2Y[k] + ny) % ny) * nx + (ix + C2X[k] + nx) % nx] == 1) flag = 1;
+        }
+        if (flag) mask[c] = 0;
+    }
+    for (int c = 0; c < n; c++) {
+        ux[c] = 0.0; uy[c] = 0.0;
+        rho[c] = mask[c] == 1 ? 1.0 : rho_wall;
+    }
+    for (int c = 0; c < n; c++) {
+        int ix = c % nx, iy = c / nx, in_droplet = 0;
+        for (int d = 0; d < 3; d++) {
+            double center_x = (nx - 1) / 2 - sin(angle * (d - 1) * pi / 180.0) * (radius_droplet + radius);
+            double center_y = (ny - 1) / 2 + cos(angle * (d - 1) * pi / 180.0) * (radius_droplet + radius);
+            if (((ix - center_x) * (ix - center_x) + (iy - center_y) * (iy - center_y) <= radius_droplet * radius_droplet) && mask[c] == 1) {
+                phi[c] = 1.0;
+                in_droplet = 1;
+            }
+        }
+        if (!in_droplet) phi[c] = mask[c] == 1 ? -1.0 : phi_wall;
+    }
+}
+
+void lbobs_init(lbobs *s, const double *rho, const double *phi, const double *ux, const double *uy)
+{
+    const size_t n = s->n;
+    memcpy(s->rho, rho, n * sizeof(double)); memcpy(s->phi, phi, n * sizeof(double));
+    memcpy(s->ux, ux, n * sizeof(double)); memcpy(s->uy, uy, n * sizeof(double));
+    for (size_t c = 0; c < n; c++) {
+        double d = rho[c], u = ux[c], v = uy[c], ph = phi[c];
+        for (int k = 0; k < 9; k++) {
+            int cx = C2X[k], cy = C2Y[k];
+            s->f[k * n + c] = W2[k] * (d + 3.0 * d * (cx * u + cy * v) +
+                                       4.5 * d * ((cx * cx - 1.0 / 3.0) * u * u + (cy * cy - 1.0 / 3.0) * v * v + 2.0 * u * v * cx * cy));
+            s->g[k * n + c] = W2[k] * (ph + 3.0 * ph * (cx * u + cy * v) +
+                                       4.5 * ph * ((cx * cx - 1.0 / 3.0) * u * u + (cy * cy - 1.0 / 3.0) * v * v + 2.0 * u * v * cx * cy));
+        }
+    }
+    /* bounce-back and solid nodes are never streamed into: they keep these values in f and g for good */
+    memcpy(s->f2, s->f, 9 * n * sizeof(double));
+    memcpy(s->g2, s->g, 9 * n * sizeof(double));
+}
+
+static void step_bs(lbobs *s)
+{
+    const size_t n = s->n;
+    const int NX = s->nx, NY = s->ny;
+    /* update_phase */
+    for (size_t c = 0; c < n; c++)
+        if (s->mask[c] == 1) {
+            double ph = 0.0;
+            for (int k = 0; k < 9; k++) ph += s->g[k * n + c];
+            s->phi[c] = ph;
+        }
+    for (int b = 0; b < s->nbb; b++) s->phi[s->bb[b]] = s->phi[s->bb_src[b]] - s->wall_gradient;
+    /* collide_bulk, then bounce-back and pull streaming as one push */
+    for (size_t c = 0; c < n; c++) {
+        if (s->mask[c] != 1) continue;
+        const int ix = (int)(c % NX), iy = (int)(c / NX);
+        double F[9], G[9];
+        double d = 0.0, ph = s->phi[c], u = 0.0, v = 0.0;
+        for (int k = 0; k < 9; k++) {
+            F[k] = s->f[k * n + c]; G[k] = s->g[k * n + c];
+            d += F[k]; u += F[k] * C2X[k]; v += F[k] * C2Y[k];
+        }
+        u = (u + 0.5 * s->force_x) / d;
+        v = (v + 0.5 * s->force_y) / d;
+        s->rho[c] = d; s->ux[c] = u; s->uy[c] = v;
+        double lap = 0.0, gx = 0.0, gy = 0.0;
+        size_t nb[9];
+        for (int k = 0; k < 9; k++) {
+            nb[k] = (size_t)((iy + C2Y[k] + NY) % NY) * NX + (ix + C2X[k] + NX) % NX;
+            lap += BS_LAP[k] * s->phi[nb[k]];
+            gx += BS_GX[k] * s->phi[nb[k]];
+            gy += BS_GY[k] * s->phi[nb[k]];
+        }
+        double sum = 0.0, sum_phase = 0.0, sq = ph * ph;
+        double pb = d / 3.0 + s->aconst * (-0.5 * sq + 3.0 / 4.0 * sq * sq) - s->kconst * ph * lap;
+        double mu = s->gammaconst * (s->aconst * (-ph + ph * ph * ph) - s->kconst * lap);
+        double feq[9], geq[9];
+        for (int k = 1; k < 9; k++) {
+            int cx = C2X[k], cy = C2Y[k];
+            feq[k] = W2[k] * (3.0 * pb + 3.0 * d * (cx * u + cy * v) +
+                              4.5 * d * ((cx * cx - 1.0 / 3.0) * u * u + (cy * cy - 1.0 / 3.0) * v * v + 2.0 * u * v * cx * cy)) +
+                     s->kconst * (BS_WXX[k] * gx * gx + BS_WYY[k] * gy * gy + BS_WXY[k] * gx * gy);
+            geq[k] = W2[k] * (3.0 * mu + 3.0 * ph * (cx * u + cy * v) +
+                              4.5 * ph * ((cx * cx - 1.0 / 3.0) * u * u + (cy * cy - 1.0 / 3.0) * v * v + 2.0 * u * v * cx * cy));
+            sum += feq[k];
+            sum_phase += geq[k];
+        }
+        feq[0] = d - sum;
+        geq[0] = ph - sum_phase;
+        double tau_rho = s->tau_gas + (ph + 1.0) / 2.0 * (s->tau_liq - s->tau_gas);
+        double omega_rho = 1.0 / tau_rho;
+        for (int k = 0; k < 9; k++) {
+            double fo = F[k] * (1.0 - omega_rho) + omega_rho * feq[k];
+            double go = G[k] * (1.0 - s->omega_phi) + s->omega_phi * geq[k];
+            if (s->mask[nb[k]] == 0) {      /* :358-372 + :617-637: comes back reversed from the bounce-back node */
+                s->f2[OPP2[k] * n + c] = fo;
+                s->g2[OPP2[k] * n + c] = go;
+            } else {
+                s->f2[k * n + nb[k]] = fo;
+                s->g2[k * n + nb[k]] = go;
+            }
+        }
+    }
+    double *t = s->f; s->f = s->f2; s->f2 = t;
+    t = s->g; s->g = s->g2; s->g2 = t;
+}
+void lbobs_step(lbobs *s, int nsteps) { for (int t = 0; t < nsteps; t++) step_bs(s); }
+void lbobs_get_fields(lbobs *s, double *phi, double *rho, double *ux, double *uy)
+{
+    memcpy(phi, s->phi, s->n * sizeof(double)); memcpy(rho, s->rho, s->n * sizeof(double));
+    memcpy(ux, s->ux, s->n * sizeof(double)); memcpy(uy, s->uy, s->n * sizeof(double));
+}
+void lbobs_get_pops(lbobs *s, double *f, double *g)
+{
+    for (size_t i = 0; i < s->n; i++)
+        for (int k = 0; k < 9; k++) { f[i * 9 + k] = s->f[k * s->n + i]; g[i * 9 + k] = s->g[k * s->n + i]; }
+}

@@ -125,6 +125,22 @@ void lbotrt_get_pops(lbotrt *, double *f);                                      
 /* the reference's geometry and initial fields (cylinder.cpp:224-312): fills mask[nx*ny], rho, ux, uy */
 void lbotrt_reference_setup(int nx, int ny, int radius, double conc_wall, int *mask, double *rho, double *ux, double *uy);
 
+/* ---------------- D2Q9 binary liquid around a curved solid (CurvedSolid/binary_shape.cpp) ---------------- */
+typedef struct lbobs lbobs;
+/* p[9] = aconst, kconst, gammaconst, wall_gradient, tau_gas, tau_liq, omega_phi, force_x, force_y
+ * (binary_shape.cpp:31,37-48); mask: 1 fluid, 0 bounce-back node, -1 solid, node i = iY*nx+iX (:449-480).
+ * Returns NULL when a bounce-back node has no wall normal that points at a fluid node (the reference
+ * would then misalign main_dir, :583-587) or lies on the edge of the array. */
+lbobs *lbobs_create(int nx, int ny, const double *p, const int *mask);
+void lbobs_destroy(lbobs *);
+void lbobs_init(lbobs *, const double *rho, const double *phi, const double *ux, const double *uy);  /* :222-258 */
+void lbobs_step(lbobs *, int n);                 /* update_phase :413-435, collide_bulk :260-356, update_bounce_back :358-372, stream :617-637 */
+void lbobs_get_fields(lbobs *, double *phi, double *rho, double *ux, double *uy);
+void lbobs_get_pops(lbobs *, double *f, double *g);   /* [i*9+k] */
+/* the reference's geometry and initial fields (:439-520) for any size: disc of `radius` in the centre, three
+ * droplets of radius_droplet on it; fills mask, rho, phi, ux, uy */
+void lbobs_reference_setup(int nx, int ny, int radius, int radius_droplet, int *mask, double *rho, double *phi, double *ux, double *uy);
+
 #ifdef __cplusplus
 }
 #endif

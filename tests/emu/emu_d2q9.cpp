@@ -10,6 +10,7 @@ using namespace lbm2;
 struct EmuSc { ScParams P; std::vector<double> f[2], rho, psi, u1, u2; int cur = 0; };
 struct EmuB2 { B2Params P; std::vector<double> f[2], g[2], phase, rho, ux, uy; int cur = 0; };
 struct EmuTrt { TrtParams P; std::vector<double> f[2], rho, ux, uy; std::vector<unsigned short> links; int cur = 0; };
+struct EmuBs { BsParams P; std::vector<double> f[2], g[2], phi, rho, ux, uy; std::vector<unsigned short> links; int cur = 0; };
 struct EmuMrt { MrtParams P; std::vector<double> f[2], force, rho, ux, uy; int cur = 0; };
 
 extern "C" {
@@ -161,5 +162,45 @@ void emutrt_get(EmuTrt *e, double *rho, double *f)
     size_t n = (size_t)e->P.nx * e->P.ny;
     memcpy(rho, e->rho.data(), n * 8);
     for (size_t i = 0; i < n; i++) for (int k = 0; k < 9; k++) f[i * 9 + k] = e->f[e->cur][k * n + i];
+}
+// ---- binary liquid around a curved solid ----
+// p[9] = aconst, kconst, gammaconst, wall_gradient, tau_gas, tau_liq, omega_phi, force_x, force_y
+EmuBs *emubs_create(int nx, int ny, const double *p, const int *mask)
+{
+    EmuBs *e = new EmuBs;
+    e->P = BsParams{nx, ny, p[0], p[1], p[2], p[3], p[4], p[5] - p[4], p[6], p[7], p[8]};
+    size_t n = (size_t)nx * ny;
+    for (int i = 0; i < 2; i++) { e->f[i].assign(9 * n, 0.0); e->g[i].assign(9 * n, 0.0); }
+    e->phi.assign(n, 0.0); e->rho.assign(n, 0.0); e->ux.assign(n, 0.0); e->uy.assign(n, 0.0);
+    e->links.assign(n, 0);
+    for (size_t i = 0; i < n; i++) e->links[i] = bs_links_thread(e->P, mask, (long long)i);
+    return e;
+}
+void emubs_destroy(EmuBs *e) { delete e; }
+void emubs_init(EmuBs *e, const double *rho, const double *phi, const double *ux, const double *uy)
+{
+    size_t n = (size_t)e->P.nx * e->P.ny;
+    memcpy(e->rho.data(), rho, n * 8); memcpy(e->phi.data(), phi, n * 8); memcpy(e->ux.data(), ux, n * 8); memcpy(e->uy.data(), uy, n * 8);
+    for (size_t i = 0; i < n; i++)
+        bs_init_thread(e->P, e->rho.data(), e->phi.data(), e->ux.data(), e->uy.data(), e->f[0].data(), e->g[0].data(), e->f[1].data(),
+                       e->g[1].data(), (long long)i);
+}
+void emubs_step(EmuBs *e, int steps)
+{
+    size_t n = (size_t)e->P.nx * e->P.ny;
+    for (int t = 0; t < steps; t++) {
+        int a = e->cur, b = 1 - a;
+        for (size_t i = 0; i < n; i++) bs_phase_thread(e->P, e->g[a].data(), e->links.data(), e->phi.data(), (long long)i);
+        for (size_t i = 0; i < n; i++)
+            bs_collide_thread(e->P, e->f[a].data(), e->g[a].data(), e->phi.data(), e->links.data(), e->f[b].data(), e->g[b].data(),
+                              e->rho.data(), e->ux.data(), e->uy.data(), (long long)i);
+        e->cur = b;
+    }
+}
+void emubs_get(EmuBs *e, double *phi, double *rho, double *ux, double *uy, double *f, double *g)
+{
+    size_t n = (size_t)e->P.nx * e->P.ny;
+    memcpy(phi, e->phi.data(), n * 8); memcpy(rho, e->rho.data(), n * 8); memcpy(ux, e->ux.data(), n * 8); memcpy(uy, e->uy.data(), n * 8);
+    for (size_t i = 0; i < n; i++) for (int k = 0; k < 9; k++) { f[i * 9 + k] = e->f[e->cur][k * n + i]; g[i * 9 + k] = e->g[e->cur][k * n + i]; }
 }
 }

@@ -85,6 +85,14 @@ def oracle():
         L.lbotrt_get_rho.argtypes = [C.c_void_p, dp]
         L.lbotrt_get_pops.argtypes = [C.c_void_p, dp]
         L.lbotrt_reference_setup.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double, C.c_void_p, dp, dp, dp]
+        L.lbobs_create.restype = C.c_void_p
+        L.lbobs_create.argtypes = [C.c_int, C.c_int, dp, C.c_void_p]
+        L.lbobs_destroy.argtypes = [C.c_void_p]
+        L.lbobs_init.argtypes = [C.c_void_p] + [dp] * 4
+        L.lbobs_step.argtypes = [C.c_void_p, C.c_int]
+        L.lbobs_get_fields.argtypes = [C.c_void_p] + [dp] * 4
+        L.lbobs_get_pops.argtypes = [C.c_void_p, dp, dp]
+        L.lbobs_reference_setup.argtypes = [C.c_int] * 4 + [C.c_void_p] + [dp] * 4
         _oracle = L
     return _oracle
 
@@ -411,6 +419,108 @@ def ref_cylinder_run(steps, omega=0.0, ce=0.0, conc_wall=0.0, rho=None, ux=None,
     rc = L.refcyl_run(steps, omega, ce, conc_wall, *[None if x is None else _p(x) for x in keep], _p(r), _p(f), g.ctypes.data)
     assert rc == 0, rc
     return dict(nx=129, ny=129, rho=r, f=f.reshape(-1, 9), geometry=g)
+
+
+# binary_shape.cpp:31,37-48: aconst, kconst, gammaconst, wall_gradient, tau_gas, tau_liq, omega_phi, force_x, force_y
+PARAMS_SHAPE = [0.04, 0.04, 1.0, -0.05, 1.0, 1.0, 1.0, 0.0, 0.0]
+
+
+class OracleShape:
+    """CurvedSolid/binary_shape.cpp restated (oracle/lbm_oracle.c, lbobs_*); node i = iY*nx+iX."""
+
+    def __init__(self, nx, ny, mask, params=PARAMS_SHAPE):
+        self.L = oracle()
+        self.nx, self.ny, self.n = nx, ny, nx * ny
+        self.mask = np.ascontiguousarray(mask, dtype=np.int32).ravel()
+        p = np.array(params, dtype=np.float64)
+        self.h = self.L.lbobs_create(nx, ny, _p(p), self.mask.ctypes.data)
+        if not self.h:
+            raise ValueError("geometry rejected (a bounce-back node without a wall normal towards fluid)")
+
+    def close(self):
+        if self.h:
+            self.L.lbobs_destroy(self.h)
+            self.h = None
+
+    def init(self, rho, phi, ux, uy):
+        a = [np.ascontiguousarray(x, dtype=np.float64).ravel() for x in (rho, phi, ux, uy)]
+        self.L.lbobs_init(self.h, *[_p(x) for x in a])
+
+    def step(self, n):
+        self.L.lbobs_step(self.h, n)
+
+    def fields(self):
+        out = [np.empty(self.n) for _ in range(4)]
+        self.L.lbobs_get_fields(self.h, *[_p(a) for a in out])
+        return dict(zip(("phase", "rho", "ux", "uy"), out))
+
+    def pops(self):
+        f, g = np.empty(self.n * 9), np.empty(self.n * 9)
+        self.L.lbobs_get_pops(self.h, _p(f), _p(g))
+        return f.reshape(-1, 9), g.reshape(-1, 9)
+
+
+def shape_reference_setup(nx=301, ny=301, radius=50, radius_droplet=10):
+    """binary_shape.cpp:439-520 through the oracle: mask, rho, phi, ux, uy."""
+    n = nx * ny
+    mask = np.zeros(n, np.int32)
+    rho, phi, ux, uy = (np.empty(n) for _ in range(4))
+    oracle().lbobs_reference_setup(nx, ny, radius, radius_droplet, mask.ctypes.data, _p(rho), _p(phi), _p(ux), _p(uy))
+    return mask, rho, phi, ux, uy
+
+
+def shape_perturbed_fields(mask, rho, phi, amp=0.05, speed=0.02):
+    """Hashed perturbation of the reference initial state on the fluid nodes plus a hashed velocity everywhere."""
+    n = mask.size
+    fl = mask == 1
+    rho2 = np.where(fl, rho * (1.0 + amp * (hashed_uniform(n, 4) - 0.5)), rho)
+    phi2 = np.where(fl, phi * (1.0 - amp * hashed_uniform(n, 5)), phi)
+    ux = (hashed_uniform(n, 6) - 0.5) * (2 * speed)
+    uy = (hashed_uniform(n, 7) - 0.5) * (2 * speed)
+    return rho2, phi2, ux, uy
+
+
+def shape_random_case(nx, ny, seed):
+    """Several solid discs (one straddling the periodic seam in x is not allowed: bounce-back nodes must stay off
+    the array edge) with the reference's rule for bounce-back nodes, a perturbed two-phase state and a velocity field."""
+    rng = np.random.default_rng(seed)
+    iy, ix = np.meshgrid(np.arange(ny), np.arange(nx), indexing="ij")
+    solid = np.zeros((ny, nx), bool)
+    for _ in range(3):
+        r = int(rng.integers(4, max(5, min(nx, ny) // 6)))
+        cx, cy = int(rng.integers(r + 3, nx - r - 3)), int(rng.integers(r + 3, ny - r - 3))
+        solid |= (ix - cx) ** 2 + (iy - cy) ** 2 < r * r
+    mask = np.where(solid, -1, 1).astype(np.int32)
+    near = np.zeros(mask.shape, bool)
+    for dy in (-1, 0, 1):
+        for dx in (-1, 0, 1):
+            if dx or dy:
+                near |= np.roll(np.roll(mask, -dy, 0), -dx, 1) == 1
+    mask[(mask == -1) & near] = 0
+    fl = mask == 1
+    phi = np.where(fl, np.where(rng.uniform(size=(ny, nx)) < 0.4, 1.0, -1.0) * rng.uniform(0.8, 1.0, (ny, nx)), 1.5)
+    rho = np.where(fl, rng.uniform(0.95, 1.05, (ny, nx)), 0.5)
+    ux, uy = rng.uniform(-0.02, 0.02, (ny, nx)), rng.uniform(-0.02, 0.02, (ny, nx))
+    return mask.ravel(), rho.ravel(), phi.ravel(), ux.ravel(), uy.ravel()
+
+
+def ref_shape_run(steps, params=None, radius_droplet=0, phi=None, rho=None, ux=None, uy=None, outdir=None):
+    """The unmodified binary_shape.cpp (301x301, radius 50) for `steps` loop iterations."""
+    L = C.CDLL(os.path.join(REF_DIR, "libref_shape.so"))
+    L.refshape_run.argtypes = [C.c_int, C.c_char_p, dp, C.c_int] + [dp] * 4 + [dp] * 6 + [C.c_void_p]
+    n = 301 * 301
+    keep = [None if x is None else np.ascontiguousarray(x, dtype=np.float64).ravel() for x in (phi, rho, ux, uy)]
+    p = None if params is None else np.array(params[:7], dtype=np.float64)
+    o = [np.empty(n) for _ in range(4)] + [np.empty(n * 9), np.empty(n * 9)]
+    geom = np.zeros(n, np.int32)
+    cwd = os.getcwd()
+    try:
+        rc = L.refshape_run(steps, (outdir or _scratch()).encode(), None if p is None else _p(p), radius_droplet,
+                            *[None if x is None else _p(x) for x in keep], *[_p(x) for x in o], geom.ctypes.data)
+    finally:
+        os.chdir(cwd)
+    assert rc == 0, rc
+    return dict(nx=301, ny=301, phase=o[0], rho=o[1], ux=o[2], uy=o[3], f=o[4].reshape(-1, 9), g=o[5].reshape(-1, 9), geometry=geom)
 
 
 def _scratch():

@@ -102,3 +102,19 @@ def test_cylinder_program_files(tmp_path):
     assert _sha16(tmp_path / "antibb" / "density0000200.dat") == "3d0afc83ee2ff0a7"
     assert _sha16(tmp_path / "antibb" / "density0064000.dat") == "b719d0f7297f1ed1"
     assert len(os.listdir(tmp_path / "antibb")) == 321
+
+
+def test_binary_shape_program_files(tmp_path):
+    """hosts/binary_shape.cpp: the complete 20001-iteration run; fingerprints taken from the unmodified
+    CurvedSolid/binary_shape.cpp built with g++ -O2 -ffp-contract=off and run in an empty directory
+    (stdout with all 201 'Mass is' lines, geometry.dat, phase.dat, the single '.dat' the three field
+    writers share, 101 legacy .vtk files)."""
+    out = _run("binary_shape", [], str(tmp_path))
+    assert hashlib.sha256(out.encode()).hexdigest()[:16] == "2b98d4974a4ac78c"
+    assert _sha16(tmp_path / "geometry.dat") == "029458e9dfa10ff8"
+    assert _sha16(tmp_path / "phase.dat") == "0ba98c3844c89b3e"
+    assert _sha16(tmp_path / ".dat") == "d4cabfac3c757cf6"
+    assert _sha16(tmp_path / "vtk0000000.vtk") == "69194701a6e5292e"
+    assert _sha16(tmp_path / "vtk0000200.vtk") == "a6ec05415407c75b"
+    assert _sha16(tmp_path / "vtk0020000.vtk") == "50ccb783563608e9"
+    assert len(os.listdir(tmp_path)) == 104

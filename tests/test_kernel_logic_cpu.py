@@ -96,6 +96,11 @@ def _emu2(path):
     L.emutrt_init.argtypes = [C.c_void_p] + [dp] * 3
     L.emutrt_step.argtypes = [C.c_void_p, C.c_int]
     L.emutrt_get.argtypes = [C.c_void_p] + [dp] * 2
+    L.emubs_create.restype = C.c_void_p
+    L.emubs_create.argtypes = [C.c_int, C.c_int, dp, C.c_void_p]
+    L.emubs_init.argtypes = [C.c_void_p] + [dp] * 4
+    L.emubs_step.argtypes = [C.c_void_p, C.c_int]
+    L.emubs_get.argtypes = [C.c_void_p] + [dp] * 6
     L.emumrt_create.restype = C.c_void_p
     L.emumrt_create.argtypes = [C.c_int] * 3 + [C.c_double] * 3
     L.emumrt_init.argtypes = [C.c_void_p] + [dp] * 3
@@ -205,4 +210,45 @@ def test_trt_threads_match_oracle(emu_libs, case):
         assert ndiff(o.rho(), r) == 0, s
         assert ndiff(o.pops().ravel(), f) == 0, s
     L.emutrt_destroy(e)
+    o.close()
+
+
+@pytest.mark.parametrize("case", ["disc_301", "disc_perturbed_160x120", "discs_64x48", "discs_131x77"])
+def test_shape_threads_match_oracle(emu_libs, case):
+    """k_bs_init / k_bs_phase / k_bs_collide thread functions (periodic push with folded bounce-back, wall-normal
+    phase extrapolation recomputed in the phase pass) against the oracle."""
+    L = _emu2(emu_libs["d2q9"])
+    params = list(ol.PARAMS_SHAPE)
+    if case == "disc_301":
+        nx = ny = 301
+        mask, rho, phi, ux, uy = ol.shape_reference_setup()
+        steps = (0, 1, 2, 40)
+    elif case.startswith("disc_perturbed"):
+        nx, ny = 160, 120
+        mask, rho, phi, ux, uy = ol.shape_reference_setup(nx, ny, 30, 7)
+        rho, phi, ux, uy = ol.shape_perturbed_fields(mask, rho, phi)
+        params = [0.03, 0.05, 0.9, 0.1, 0.8, 1.4, 1.0 / 1.3, 1e-5, -2e-5]
+        steps = (0, 1, 2, 120)
+    else:
+        nx, ny = [int(v) for v in case.split("_")[1].split("x")]
+        mask, rho, phi, ux, uy = ol.shape_random_case(nx, ny, seed=nx)
+        params = [0.04, 0.04, 1.0, -0.15, 0.7, 2.5, 0.5, 0.0, 3e-5]
+        steps = (0, 1, 2, 150)
+    n = nx * ny
+    p = np.array(params)
+    o = ol.OracleShape(nx, ny, mask, params)
+    o.init(rho, phi, ux, uy)
+    e = L.emubs_create(nx, ny, _p(p), mask.ctypes.data)
+    L.emubs_init(e, _p(rho), _p(phi), _p(ux), _p(uy))
+    for s in steps:
+        o.step(s)
+        L.emubs_step(e, s)
+        out = [np.empty(n) for _ in range(4)] + [np.empty(9 * n), np.empty(9 * n)]
+        L.emubs_get(e, *[_p(x) for x in out])
+        a = o.fields()
+        for i, k in enumerate(("phase", "rho", "ux", "uy")):
+            assert ndiff(a[k], out[i]) == 0, (k, s)
+        fo, go = o.pops()
+        assert ndiff(fo.ravel(), out[4]) == 0 and ndiff(go.ravel(), out[5]) == 0, s
+    L.emubs_destroy(e)
     o.close()

@@ -131,3 +131,41 @@ def test_trt_cylinder_advected(steps):
     o.step(steps)
     _exact("trt_adv_t%d" % steps, dict(rho=o.rho(), f=o.pops()))
     o.close()
+
+
+@pytest.mark.parametrize("upto", [201, 2001])
+def test_shape_curved_solid(upto):
+    """CurvedSolid/binary_shape.cpp as shipped; every recorded snapshot up to `upto` iterations."""
+    mask, rho, phi, ux, uy = ol.shape_reference_setup()
+    assert ol.ndiff(mask.astype(np.float64), gl.samples("shape_geometry", "mask")[0]) == 0
+    o = ol.OracleShape(301, 301, mask)
+    o.init(rho, phi, ux, uy)
+    done = 0
+    for steps in (1, 2, 201, 2001):
+        if steps > upto or (upto == 2001 and steps < 2001):
+            continue
+        o.step(steps - done)
+        done = steps
+        fields = o.fields()
+        fields["f"], fields["g"] = o.pops()
+        _exact("shape_t%d" % steps, fields)
+        mass = 0.0
+        for v in fields["phase"][mask == 1]:
+            mass += v
+        assert mass == gl.meta("shape_t%d" % steps)["mass"]
+    o.close()
+
+
+@pytest.mark.parametrize("steps", [1, 300])
+def test_shape_curved_solid_perturbed(steps):
+    tag = "shape_pert_t%d" % steps
+    m = gl.meta(tag)
+    mask, rho, phi, _, _ = ol.shape_reference_setup()
+    rho2, phi2, ux2, uy2 = ol.shape_perturbed_fields(mask, rho, phi)
+    o = ol.OracleShape(301, 301, mask, m["params"])
+    o.init(rho2, phi2, ux2, uy2)
+    o.step(steps)
+    fields = o.fields()
+    fields["f"], fields["g"] = o.pops()
+    _exact(tag, fields)
+    o.close()

@@ -105,3 +105,22 @@ def test_trt_cylinder(omega, ce, cw):
         assert ol.ndiff(r["geometry"], mask) == 0
         assert ol.ndiff(r["rho"], o.rho()) == 0 and ol.ndiff(r["f"], o.pops()) == 0, steps
         o.close()
+
+
+@pytest.mark.skipif(not ol.ref_available("shape"), reason="oracle/_ref not built")
+@pytest.mark.parametrize("params,rd", [(None, 0), ([0.05, 0.03, 1.2, -0.2, 0.6, 2.0, 0.8, 0.0, 0.0], 14)])
+def test_shape_curved_solid(params, rd):
+    mask, rho, phi, ux, uy = ol.shape_reference_setup(radius_droplet=rd or 10)
+    rho, phi, ux, uy = ol.shape_perturbed_fields(mask, rho, phi, amp=0.08, speed=0.03)
+    for steps in (0, 1, 3, 80):
+        o = ol.OracleShape(301, 301, mask, params or ol.PARAMS_SHAPE)
+        o.init(rho, phi, ux, uy)
+        o.step(steps)
+        r = ol.ref_shape_run(steps, params, rd, phi, rho, ux, uy)
+        assert ol.ndiff(r["geometry"], mask) == 0
+        a = o.fields()
+        for k in a:
+            assert ol.ndiff(r[k], a[k]) == 0, (k, steps)
+        f, g = o.pops()
+        assert ol.ndiff(r["f"], f) == 0 and ol.ndiff(r["g"], g) == 0, steps
+        o.close()
