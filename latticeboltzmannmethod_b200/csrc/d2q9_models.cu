@@ -25,11 +25,69 @@ __global__ void __launch_bounds__(kThreads) k_sc_density(lbm2::ScParams P, const
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < (long long)P.nx * P.ny) lbm2::sc_density_thread(P, f, rho, psi, i);
 }
+// WRITE (all step kernels below): leave the macroscopic fields behind; only the last step of an lbm_step(n) batch does
+template <bool WRITE>
 __global__ void __launch_bounds__(kThreads) k_sc_collide(lbm2::ScParams P, const double *f, const double *rho, const double *psi,
                                                           double *f2, double *u1, double *u2)
 {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < (long long)P.nx * P.ny) lbm2::sc_collide_thread(P, f, rho, psi, f2, u1, u2, (int)(i % P.nx), (int)(i / P.nx));
+    if (i < (long long)P.nx * P.ny) lbm2::sc_collide_thread(P, f, rho, psi, f2, u1, u2, (int)(i % P.nx), (int)(i / P.nx), WRITE);
+}
+// One launch per Shan-Chen step: a TX x TY tile of nodes per block.  Every thread loads the nine populations of
+// its node, sums them and puts psi = 1 - exp(-rho) into shared memory; the first threads of the block do the
+// same for the ring of nodes around the tile (periodic), whose populations are re-read through L2; after one
+// barrier each thread has the nine psi values of its force stencil and collides out of registers.  The rho and
+// psi arrays of the two-kernel form and their 2 x 16 B per node of traffic disappear.
+template <int TX, int TY, int MINB, bool WRITE>
+__global__ void __launch_bounds__(TX *TY, MINB) k_sc_fused(lbm2::ScParams P, const double *__restrict__ f, double *__restrict__ f2,
+                                                     double *__restrict__ rho, double *__restrict__ u1, double *__restrict__ u2)
+{
+    __shared__ double psi_s[TY + 2][TX + 2];
+    const int nx = P.nx, ny = P.ny;
+    const long long n = (long long)nx * ny;
+    const int lx = threadIdx.x % TX, ly = threadIdx.x / TX;
+    const int x0 = blockIdx.x * TX, y0 = blockIdx.y * TY;
+    // the node of this thread; past the edge of the grid it wraps, which is exactly the periodic neighbour
+    // the last column (row) needs, and the thread then only contributes psi
+    const bool active = x0 + lx < nx && y0 + ly < ny;
+    const int gx = (x0 + lx) % nx, gy = (y0 + ly) % ny;
+    const long long i = (long long)gy * nx + gx;
+    double F[9], dense = 0;
+#pragma unroll
+    for (int k = 0; k < 9; k++) F[k] = f[k * n + i];
+#pragma unroll
+    for (int k = 0; k < 9; k++) dense += F[k];
+    psi_s[ly + 1][lx + 1] = 1.0 - lbm_exp(-dense);
+    constexpr int kRing = 2 * TX + 2 * TY + 4;
+    for (int r = threadIdx.x; r < kRing; r += TX * TY) {
+        int rx, ry;   // position in the (TX+2) x (TY+2) frame
+        if (r < TX + 2) { rx = r; ry = 0; }
+        else if (r < 2 * (TX + 2)) { rx = r - (TX + 2); ry = TY + 1; }
+        else if (r < 2 * (TX + 2) + TY) { rx = 0; ry = r - 2 * (TX + 2) + 1; }
+        else { rx = TX + 1; ry = r - 2 * (TX + 2) - TY + 1; }
+        const int hx = (x0 + rx - 1 + nx) % nx, hy = (y0 + ry - 1 + ny) % ny;
+        const long long h = (long long)hy * nx + hx;
+        double d = 0;
+#pragma unroll
+        for (int k = 0; k < 9; k++) d += f[k * n + h];
+        psi_s[ry][rx] = 1.0 - lbm_exp(-d);
+    }
+    __syncthreads();
+    if (!active) return;
+    const int CX[9] = LBM2_CX, CY[9] = LBM2_CY;
+    double ps[9];
+#pragma unroll
+    for (int k = 0; k < 9; k++) ps[k] = psi_s[ly + 1 + CY[k]][lx + 1 + CX[k]];
+    double v1, v2;
+    lbm2::sc_collide_core(P, F, dense, ps[0], ps, v1, v2);
+    if (WRITE) { rho[i] = dense; u1[i] = v1; u2[i] = v2; }
+    const int xm = gx == 0 ? nx - 1 : gx - 1, xp = gx == nx - 1 ? 0 : gx + 1;
+    const int ym = gy == 0 ? ny - 1 : gy - 1, yp = gy == ny - 1 ? 0 : gy + 1;
+#pragma unroll
+    for (int k = 0; k < 9; k++) {
+        const int x2 = CX[k] > 0 ? xp : (CX[k] < 0 ? xm : gx), y2 = CY[k] > 0 ? yp : (CY[k] < 0 ? ym : gy);
+        f2[k * n + (long long)y2 * nx + x2] = F[k];
+    }
 }
 // ---- binary kernels (node index i = iX*NY+iY, iY fastest) ----
 __global__ void __launch_bounds__(kThreads) k_b2_wallphase(lbm2::B2Params P, double *phase)
@@ -50,11 +108,12 @@ __global__ void __launch_bounds__(kThreads) k_b2_phase(lbm2::B2Params P, const d
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < (long long)P.nx * P.ny) lbm2::b2_phase_thread(P, g, phase, (int)(i / P.ny), (int)(i % P.ny));
 }
+template <bool WRITE>
 __global__ void __launch_bounds__(kThreads) k_b2_collide(lbm2::B2Params P, const double *f, const double *g, const double *phase,
                                                           double *f2, double *g2, double *rho, double *ux, double *uy)
 {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < (long long)P.nx * P.ny) lbm2::b2_collide_thread(P, f, g, phase, f2, g2, rho, ux, uy, (int)(i / P.ny), (int)(i % P.ny));
+    if (i < (long long)P.nx * P.ny) lbm2::b2_collide_thread(P, f, g, phase, f2, g2, rho, ux, uy, (int)(i / P.ny), (int)(i % P.ny), WRITE);
 }
 // ---- MRT kernels ----
 __global__ void __launch_bounds__(kThreads) k_mrt_init(lbm2::MrtParams P, const double *rho, const double *ux, const double *uy, double *f)
@@ -62,11 +121,12 @@ __global__ void __launch_bounds__(kThreads) k_mrt_init(lbm2::MrtParams P, const 
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < (long long)P.nx * P.ny) lbm2::mrt_init_thread(P, rho, ux, uy, f, i);
 }
+template <bool WRITE>
 __global__ void __launch_bounds__(kThreads) k_mrt_step(lbm2::MrtParams P, const double *f, const double *force, double *f2,
                                                         double *rho, double *ux, double *uy)
 {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < (long long)P.nx * P.ny) lbm2::mrt_thread(P, f, force, f2, rho, ux, uy, (int)(i / P.ny), (int)(i % P.ny));
+    if (i < (long long)P.nx * P.ny) lbm2::mrt_thread(P, f, force, f2, rho, ux, uy, (int)(i / P.ny), (int)(i % P.ny), WRITE);
 }
 // ---- TRT diffusion kernels (node index i = iY*nx+iX) ----
 __global__ void __launch_bounds__(kThreads) k_trt_init(lbm2::TrtParams P, const double *rho, const double *ux, const double *uy,
@@ -75,12 +135,13 @@ __global__ void __launch_bounds__(kThreads) k_trt_init(lbm2::TrtParams P, const 
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < (long long)P.nx * P.ny) lbm2::trt_init_thread(P, rho, ux, uy, fa, fb, i);
 }
+template <bool WRITE>
 __global__ void __launch_bounds__(kThreads) k_trt_step(lbm2::TrtParams P, const double *__restrict__ f,
                                                         const unsigned short *__restrict__ links, const double *__restrict__ ux,
                                                         const double *__restrict__ uy, double *__restrict__ f2, double *__restrict__ rho)
 {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < (long long)P.nx * P.ny) lbm2::trt_thread(P, f, links, ux, uy, f2, rho, i);
+    if (i < (long long)P.nx * P.ny) lbm2::trt_thread(P, f, links, ux, uy, f2, rho, i, WRITE);
 }
 // ---- binary liquid around a curved solid (node index i = iY*nx+iX) ----
 __global__ void __launch_bounds__(kThreads) k_bs_init(lbm2::BsParams P, const double *rho, const double *phi, const double *ux,
@@ -95,13 +156,14 @@ __global__ void __launch_bounds__(kThreads) k_bs_phase(lbm2::BsParams P, const d
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < (long long)P.nx * P.ny) lbm2::bs_phase_thread(P, g, links, phi, i);
 }
-__global__ void __launch_bounds__(kThreads) k_bs_collide(lbm2::BsParams P, const double *__restrict__ f, const double *__restrict__ g,
+template <bool WRITE>
+__global__ void __launch_bounds__(kThreads, 2) k_bs_collide(lbm2::BsParams P, const double *__restrict__ f, const double *__restrict__ g,
                                                           const double *__restrict__ phi, const unsigned short *__restrict__ links,
                                                           double *__restrict__ f2, double *__restrict__ g2, double *__restrict__ rho,
                                                           double *__restrict__ ux, double *__restrict__ uy)
 {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < (long long)P.nx * P.ny) lbm2::bs_collide_thread(P, f, g, phi, links, f2, g2, rho, ux, uy, i);
+    if (i < (long long)P.nx * P.ny) lbm2::bs_collide_thread(P, f, g, phi, links, f2, g2, rho, ux, uy, i, WRITE);
 }
 // ---- AoS <-> SoA at the boundary ----
 __global__ void __launch_bounds__(kThreads) k_aos_to_soa9(long long n, const double *aos, double *soa)
@@ -130,6 +192,7 @@ public:
     {
         if (cfg_.nx < 3 || cfg_.ny < 3 || cfg_.nz != 1) return rt_.fail(LBM_EINVAL, "2-D model: need nx,ny >= 3 and nz == 1");
         n_ = (long long)cfg_.nx * cfg_.ny;
+        if (n_ >= (1ll << 31)) return rt_.fail(LBM_EINVAL, "2-D model: nx*ny must stay below 2^31");
         for (int b = 0; b < 2; b++) {
             LBM_CUDA(rt_, cudaMalloc(&f_[b], 9 * n_ * sizeof(double)));
             LBM_CUDA(rt_, cudaMemsetAsync(f_[b], 0, 9 * n_ * sizeof(double), rt_.stream));
@@ -223,7 +286,7 @@ public:
     lbm_status setup()
     {
         LBM_TRY(alloc_common());
-        P_ = lbm2::ScParams{cfg_.nx, cfg_.ny, cfg_.tau, cfg_.g};
+        P_ = lbm2::sc_params(cfg_.nx, cfg_.ny, cfg_.tau, cfg_.g);
         LBM_CUDA(rt_, cudaMalloc(&aux_, n_ * sizeof(double)));   // psi
         return LBM_OK;
     }
@@ -235,13 +298,32 @@ public:
     }
     lbm_status step(int nsteps) override
     {
+        // kernel_variant 1: the two-kernel form (density pass + collide); otherwise the fused tile kernel:
+        // 0 = 32x4 tile capped at 64 registers, 8 blocks/SM (fastest measured: 2.12 ms at 8192^2); 2 = 32x16;
+        // 3 = 32x8 at 64 registers (2.27 ms); 5 = 32x8 uncapped, 3 blocks/SM (2.58 ms)
+        if (cfg_.kernel_variant != 1) {
+            for (int t = 0; t < nsteps; t++) {
+                const bool w = t == nsteps - 1;
+                rt_.about_to_launch();
+                switch (cfg_.kernel_variant) {
+                case 2: launch_fused<32, 16, 1>(w); break;
+                case 3: launch_fused<32, 8, 4>(w); break;
+                case 5: launch_fused<32, 8, 3>(w); break;
+                default: launch_fused<32, 4, 8>(w); break;
+                }
+                LBM_TRY(rt_.launched("k_sc_fused"));
+                cur_ = 1 - cur_;
+            }
+            return LBM_OK;
+        }
         for (int t = 0; t < nsteps; t++) {
             rt_.about_to_launch();
             k_sc_density<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, f_[cur_], fields_[LBM_RHO], aux_);
             LBM_TRY(rt_.launched("k_sc_density"));
             rt_.about_to_launch();
-            k_sc_collide<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, f_[cur_], fields_[LBM_RHO], aux_, f_[1 - cur_],
-                                                                      fields_[LBM_UX], fields_[LBM_UY]);
+            auto kern = t == nsteps - 1 ? k_sc_collide<true> : k_sc_collide<false>;
+            kern<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, f_[cur_], fields_[LBM_RHO], aux_, f_[1 - cur_], fields_[LBM_UX],
+                                                              fields_[LBM_UY]);
             LBM_TRY(rt_.launched("k_sc_collide"));
             cur_ = 1 - cur_;
         }
@@ -250,6 +332,13 @@ public:
     lbm_status diagnostics(double *m, double *mom, double *pm, int *nan) override { return diag_common(0, m, mom, pm, nan); }
 
 private:
+    template <int TX, int TY, int MINB>
+    void launch_fused(bool write)
+    {
+        const dim3 grid((cfg_.nx + TX - 1) / TX, (cfg_.ny + TY - 1) / TY);
+        auto kern = write ? k_sc_fused<TX, TY, MINB, true> : k_sc_fused<TX, TY, MINB, false>;
+        kern<<<grid, TX * TY, 0, rt_.stream>>>(P_, f_[cur_], f_[1 - cur_], fields_[LBM_RHO], fields_[LBM_UX], fields_[LBM_UY]);
+    }
     lbm2::ScParams P_{};
 };
 
@@ -280,8 +369,9 @@ public:
             k_b2_phase<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, g_[cur_], fields_[LBM_PHASE]);
             LBM_TRY(rt_.launched("k_b2_phase"));
             rt_.about_to_launch();
-            k_b2_collide<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, f_[cur_], g_[cur_], fields_[LBM_PHASE], f_[1 - cur_],
-                                                                      g_[1 - cur_], fields_[LBM_RHO], fields_[LBM_UX], fields_[LBM_UY]);
+            auto kern = t == nsteps - 1 ? k_b2_collide<true> : k_b2_collide<false>;
+            kern<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, f_[cur_], g_[cur_], fields_[LBM_PHASE], f_[1 - cur_], g_[1 - cur_],
+                                                              fields_[LBM_RHO], fields_[LBM_UX], fields_[LBM_UY]);
             LBM_TRY(rt_.launched("k_b2_collide"));
             cur_ = 1 - cur_;
         }
@@ -322,8 +412,9 @@ public:
     {
         for (int t = 0; t < nsteps; t++) {
             rt_.about_to_launch();
-            k_mrt_step<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, f_[cur_], aux_, f_[1 - cur_], fields_[LBM_RHO],
-                                                                    fields_[LBM_UX], fields_[LBM_UY]);
+            auto kern = t == nsteps - 1 ? k_mrt_step<true> : k_mrt_step<false>;
+            kern<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, f_[cur_], aux_, f_[1 - cur_], fields_[LBM_RHO], fields_[LBM_UX],
+                                                              fields_[LBM_UY]);
             LBM_TRY(rt_.launched("k_mrt_step"));
             cur_ = 1 - cur_;
         }
@@ -380,8 +471,9 @@ public:
     {
         for (int t = 0; t < nsteps; t++) {
             rt_.about_to_launch();
-            k_trt_step<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, f_[cur_], links_, fields_[LBM_UX], fields_[LBM_UY], f_[1 - cur_],
-                                                                    fields_[LBM_RHO]);
+            auto kern = t == nsteps - 1 ? k_trt_step<true> : k_trt_step<false>;
+            kern<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, f_[cur_], links_, fields_[LBM_UX], fields_[LBM_UY], f_[1 - cur_],
+                                                              fields_[LBM_RHO]);
             LBM_TRY(rt_.launched("k_trt_step"));
             cur_ = 1 - cur_;
         }
@@ -470,8 +562,9 @@ public:
             k_bs_phase<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, g_[cur_], links_, fields_[LBM_PHASE]);
             LBM_TRY(rt_.launched("k_bs_phase"));
             rt_.about_to_launch();
-            k_bs_collide<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, f_[cur_], g_[cur_], fields_[LBM_PHASE], links_, f_[1 - cur_],
-                                                                      g_[1 - cur_], fields_[LBM_RHO], fields_[LBM_UX], fields_[LBM_UY]);
+            auto kern = t == nsteps - 1 ? k_bs_collide<true> : k_bs_collide<false>;
+            kern<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, f_[cur_], g_[cur_], fields_[LBM_PHASE], links_, f_[1 - cur_], g_[1 - cur_],
+                                                              fields_[LBM_RHO], fields_[LBM_UX], fields_[LBM_UY]);
             LBM_TRY(rt_.launched("k_bs_collide"));
             cur_ = 1 - cur_;
         }

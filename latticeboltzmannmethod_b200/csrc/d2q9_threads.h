@@ -25,7 +25,11 @@ namespace lbm2 {
 struct ScParams {
     int nx, ny;
     double tau, g;
+    // the two per-run constants of the node update, divided once on the host (IEEE division: the same bits as
+    // dividing in every thread): -1.0/tau of shanchen.cpp:182 and (1 - 0.5/tau) of :163
+    double neg_inv_tau, force_factor;
 };
+inline ScParams sc_params(int nx, int ny, double tau, double g) { return ScParams{nx, ny, tau, g, -1.0 / tau, 1 - 0.5 / tau}; }
 
 // shanchen.cpp:124-132 plus psi = 1 - exp(-rho), which the reference re-evaluates
 // for every neighbour (:152-157); same function, same argument, computed once.
@@ -39,43 +43,28 @@ LBM_HD void sc_density_thread(const ScParams &P, const double *f, double *rho, d
     psi[i] = 1.0 - lbm_exp(-r);
 }
 
-// shanchen.cpp:136-186: force (float accumulators), shifted velocity, force
-// populations, closed-form equilibria, in-place BGK, periodic push
-LBM_HD void sc_collide_thread(const ScParams &P, const double *f, const double *rho, const double *psi, double *f2,
-                              double *u1, double *u2, int ix, int iy)
+// shanchen.cpp:136-186 for one node whose populations F, density and the pseudopotential psi of the node (ps_c)
+// and of its nine stencil nodes (ps[k], k = 0 is the node itself) are in registers: force (float accumulators),
+// shifted velocity, force populations, closed-form equilibria, in-place BGK.  F holds the post-collision values on return.
+LBM_HD void sc_collide_core(const ScParams &P, double (&F)[9], double dense, double ps_c, const double (&ps)[9], double &v1, double &v2)
 {
-    const int nx = P.nx, ny = P.ny;
-    const long long n = (long long)nx * ny, i = (long long)iy * nx + ix;
     const int CX[9] = LBM2_CX, CY[9] = LBM2_CY;
     const double W[9] = LBM2_W;
-    const double dense = rho[i];
-    long long nb[9];
-#pragma unroll
-    for (int k = 0; k < 9; k++) {
-        const int x2 = (ix + CX[k] + nx) % nx, y2 = (iy + CY[k] + ny) % ny;
-        nb[k] = (long long)nx * y2 + x2;
-    }
     float fx = 0.0, fy = 0.0;
 #pragma unroll
     for (int k = 0; k < 9; k++) {
-        const double ps = psi[nb[k]];
-        fx += W[k] * CX[k] * ps;
-        fy += W[k] * CY[k] * ps;
+        fx += W[k] * CX[k] * ps[k];
+        fy += W[k] * CY[k] * ps[k];
     }
-    fx = -P.g * psi[i] * fx;
-    fy = -P.g * psi[i] * fy;
-    double F[9];
-#pragma unroll
-    for (int k = 0; k < 9; k++) F[k] = f[k * n + i];
-    const double v1 = (F[1] - F[3] + F[5] - F[6] - F[7] + F[8]) / dense + fx / (2.0 * dense);
-    const double v2 = (F[2] - F[4] + F[5] + F[6] - F[7] - F[8]) / dense + fy / (2.0 * dense);
-    u1[i] = v1;
-    u2[i] = v2;
+    fx = -P.g * ps_c * fx;
+    fy = -P.g * ps_c * fy;
+    v1 = (F[1] - F[3] + F[5] - F[6] - F[7] + F[8]) / dense + fx / (2.0 * dense);
+    v2 = (F[2] - F[4] + F[5] + F[6] - F[7] - F[8]) / dense + fy / (2.0 * dense);
     double fpop[9];
 #pragma unroll
     for (int k = 0; k < 9; k++) {
         const int cx = CX[k], cy = CY[k];
-        fpop[k] = W[k] * (1 - 0.5 / P.tau) *
+        fpop[k] = W[k] * P.force_factor *
                   ((3 * (cx - v1) + 9 * cx * (cx * v1 + cy * v2)) * fx + (3 * (cy - v2) + 9 * cy * (cx * v1 + cy * v2)) * fy);
     }
     const float usq = v1 * v1 + v2 * v2;
@@ -90,11 +79,33 @@ LBM_HD void sc_collide_thread(const ScParams &P, const double *f, const double *
     feq[7] = 1.0 / 36.0 * dense * (1.0 + 3 * (-v1 - v2) + 4.5 * (v1 + v2) * (v1 + v2) - 1.5 * usq);
     feq[8] = 1.0 / 36.0 * dense * (1.0 + 3 * (v1 - v2) + 4.5 * (v1 - v2) * (v1 - v2) - 1.5 * usq);
 #pragma unroll
+    for (int k = 0; k < 9; k++) F[k] += P.neg_inv_tau * (F[k] - feq[k]) + fpop[k];
+}
+
+// the two-kernel form: rho and psi come from sc_density_thread's arrays; periodic push
+LBM_HD void sc_collide_thread(const ScParams &P, const double *f, const double *rho, const double *psi, double *f2,
+                              double *u1, double *u2, int ix, int iy, bool write_fields = true)
+{
+    const int nx = P.nx, ny = P.ny;
+    const long long n = (long long)nx * ny, i = (long long)iy * nx + ix;
+    const int CX[9] = LBM2_CX, CY[9] = LBM2_CY;
+    long long nb[9];
+    double ps[9], F[9];
+#pragma unroll
     for (int k = 0; k < 9; k++) {
-        double fk = F[k];
-        fk += -1.0 / P.tau * (fk - feq[k]) + fpop[k];
-        f2[k * n + nb[k]] = fk;
+        const int x2 = (ix + CX[k] + nx) % nx, y2 = (iy + CY[k] + ny) % ny;
+        nb[k] = (long long)nx * y2 + x2;
+        ps[k] = psi[nb[k]];
+        F[k] = f[k * n + i];
     }
+    double v1, v2;
+    sc_collide_core(P, F, rho[i], psi[i], ps, v1, v2);
+    if (write_fields) {      // only the last step of a batch has to leave the fields behind (shanchen.cpp:190-207 reads them)
+        u1[i] = v1;
+        u2[i] = v2;
+    }
+#pragma unroll
+    for (int k = 0; k < 9; k++) f2[k * n + nb[k]] = F[k];
 }
 
 // shanchen.cpp:95-113 generalised to a given (rho, u): f = feq(rho, u)
@@ -205,7 +216,7 @@ LBM_HD void b2_init_thread(const B2Params &P, const double *phase, double *fa, d
 // binary.cpp:252-327 (collide), :201-233 (bounce-back rows) and :341-350 (pull streaming) as one
 // push: a population that would enter a wall row comes back to its own node reversed
 LBM_HD void b2_collide_thread(const B2Params &P, const double *f, const double *g, const double *phase, double *f2,
-                              double *g2, double *rho, double *uxo, double *uyo, int ix, int iy)
+                              double *g2, double *rho, double *uxo, double *uyo, int ix, int iy, bool write_fields = true)
 {
     const int NX = P.nx, NY = P.ny;
     if (iy < 1 || iy > NY - 2) return;
@@ -222,7 +233,7 @@ LBM_HD void b2_collide_thread(const B2Params &P, const double *f, const double *
         jy += F[k] * CY[k];
     }
     const double ux = jx / d, uy = jy / d;
-    rho[i] = d; uxo[i] = ux; uyo[i] = uy;
+    if (write_fields) { rho[i] = d; uxo[i] = ux; uyo[i] = uy; }
     double gx, gy, lap, feq[9], geq[9];
     b2_stencils(P, phase, ix, iy, gx, gy, lap);
     const double ph = phase[i];
@@ -259,7 +270,7 @@ struct MrtParams {
 // forcex_of_ix: the per-column force mrt.cpp:165 evaluates with cos(); built on the host with the
 // same expression so the device needs no cos().
 LBM_HD void mrt_thread(const MrtParams &P, const double *f, const double *forcex_of_ix, double *f2, double *rho_o,
-                       double *ux_o, double *uy_o, int ix, int iy)
+                       double *ux_o, double *uy_o, int ix, int iy, bool write_fields = true)
 {
     const int NX = P.nx, NY = P.ny;
     const long long n = (long long)NX * NY, i = (long long)ix * NY + iy;
@@ -347,7 +358,7 @@ LBM_HD void mrt_thread(const MrtParams &P, const double *f, const double *forcex
             fl[k] = fl[k] + W[k] * addit;
         }
     }
-    rho_o[i] = rho; ux_o[i] = ux; uy_o[i] = uy;
+    if (write_fields) { rho_o[i] = rho; ux_o[i] = ux; uy_o[i] = uy; }
 #pragma unroll
     for (int k = 0; k < 9; k++) {
         const long long t = (long long)((ix + CX[k] + NX) % NX) * NY + (iy + CY[k] + NY) % NY;
@@ -427,7 +438,7 @@ LBM_HD TrtPair trt_pair(double fk, double fo, double wt, double dense, double cu
 }
 
 LBM_HD void trt_thread(const TrtParams &P, const double *f, const unsigned short *links, const double *ux_i, const double *uy_i,
-                       double *f2, double *rho_o, long long i)
+                       double *f2, double *rho_o, long long i, bool write_fields = true)
 {
     const unsigned link = links[i];
     if (!(link & 1u)) return;
@@ -440,7 +451,7 @@ LBM_HD void trt_thread(const TrtParams &P, const double *f, const unsigned short
     double sum = 0;
 #pragma unroll
     for (int k = 0; k < 9; k++) sum += fl[k];
-    rho_o[i] = sum;
+    if (write_fields) rho_o[i] = sum;
     const double dense_temp = sum, ux_temp = ux_i[i], uy_temp = uy_i[i];
     const double u_sq = ux_temp * ux_temp + uy_temp * uy_temp;
     // pairs (1,3), (2,4), (5,7), (6,8); weights_trt = 1/3 on the axes, 1/12 on the diagonals (cylinder.cpp:50)
@@ -549,8 +560,9 @@ LBM_HD void bs_phase_thread(const BsParams &P, const double *g, const unsigned s
     const int dir = (int)(link >> 9);
     if (!(link & 1u) && dir == 0) return;
     const long long n = (long long)P.nx * P.ny;
-    const int CX[9] = LBM2_CX, CY[9] = LBM2_CY;
-    const long long src = dir ? i + CY[dir] * P.nx + CX[dir] : i;
+    // c_x+1 and c_y+1 of the nine directions as 2-bit fields (a table indexed by `dir` would live in local memory)
+    const int cxd = (int)((0x20919u >> (2 * dir)) & 3u) - 1, cyd = (int)((0x2865u >> (2 * dir)) & 3u) - 1;
+    const long long src = i + cyd * P.nx + cxd;
     double phase_temp = 0.0;
 #pragma unroll
     for (int k = 0; k < 9; k++) phase_temp += g[k * n + src];
@@ -559,7 +571,8 @@ LBM_HD void bs_phase_thread(const BsParams &P, const double *g, const unsigned s
 
 // collide_bulk (:260-356) of one fluid node, then update_bounce_back + stream folded into the push
 LBM_HD void bs_collide_thread(const BsParams &P, const double *f, const double *g, const double *phi, const unsigned short *links,
-                              double *f2, double *g2, double *rho_o, double *ux_o, double *uy_o, long long i)
+                              double *f2, double *g2, double *rho_o, double *ux_o, double *uy_o, long long i,
+                              bool write_fields = true)
 {
     const unsigned link = links[i];
     if (!(link & 1u)) return;
@@ -572,9 +585,9 @@ LBM_HD void bs_collide_thread(const BsParams &P, const double *f, const double *
     // periodic neighbours: (iX+cx+NX)%NX, (iY+cy+NY)%NY
     const int xs[3] = {ix == 0 ? P.nx - 1 : ix - 1, ix, ix == P.nx - 1 ? 0 : ix + 1};
     const int ys[3] = {iy == 0 ? P.ny - 1 : iy - 1, iy, iy == P.ny - 1 ? 0 : iy + 1};
-    long long nb[9];
+    int nb[9];      // nx*ny < 2^31 (checked at create)
 #pragma unroll
-    for (int k = 0; k < 9; k++) nb[k] = (long long)ys[CY[k] + 1] * P.nx + xs[CX[k] + 1];
+    for (int k = 0; k < 9; k++) nb[k] = ys[CY[k] + 1] * P.nx + xs[CX[k] + 1];
 
     double fl[9], gl[9];
     double dense_temp = 0.0, ux_temp = 0.0, uy_temp = 0.0;
@@ -589,7 +602,7 @@ LBM_HD void bs_collide_thread(const BsParams &P, const double *f, const double *
     }
     ux_temp = (ux_temp + 0.5 * P.force_x) / dense_temp;
     uy_temp = (uy_temp + 0.5 * P.force_y) / dense_temp;
-    rho_o[i] = dense_temp; ux_o[i] = ux_temp; uy_o[i] = uy_temp;
+    if (write_fields) { rho_o[i] = dense_temp; ux_o[i] = ux_temp; uy_o[i] = uy_temp; }
 
     double laplace_temp = 0.0, gradx_temp = 0.0, grady_temp = 0.0;
 #pragma unroll

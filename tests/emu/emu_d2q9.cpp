@@ -17,7 +17,7 @@ extern "C" {
 // ---- Shan-Chen ----
 EmuSc *emusc_create(int nx, int ny, double tau, double g)
 {
-    EmuSc *e = new EmuSc; e->P = ScParams{nx, ny, tau, g};
+    EmuSc *e = new EmuSc; e->P = sc_params(nx, ny, tau, g);
     size_t n = (size_t)nx * ny;
     for (int i = 0; i < 2; i++) e->f[i].assign(9 * n, 0.0);
     e->rho.assign(n, 0.0); e->psi.assign(n, 0.0); e->u1.assign(n, 0.0); e->u2.assign(n, 0.0);

@@ -141,9 +141,13 @@ def test_d3q19_population_roundtrip_and_diagnostics():
 
 
 # ---------------- 2-D programs ----------------
-def test_shanchen_vs_oracle_and_golden():
+@pytest.mark.parametrize("variant", [0, 1, 2, 3, 5])
+def test_shanchen_vs_oracle_and_golden(variant):
+    """variant 0/2/3/5: the fused tile kernel (32x4, 32x16, 32x8 at 64 registers, 32x8); 1: density pass + collide."""
     api = _api()
-    ctx = api.Context(api.shanchen_config())
+    cfg = api.shanchen_config()
+    cfg.kernel_variant = variant
+    ctx = api.Context(cfg)
     ctx.set_field("rho", api.shanchen_initial_rho())
     ctx.init()
     o = ol.OracleShanChen(128, 128)
@@ -169,6 +173,30 @@ def test_shanchen_vs_oracle_and_golden():
     spread = gl.rel_inf("shanchen_libm_t30000", "rho", ctx.get_field("rho"))
     assert spread < 1e-3
     ctx.close()
+
+
+@pytest.mark.parametrize("variant", [0, 1, 2, 3, 5])
+@pytest.mark.parametrize("nx,ny", [(45, 37), (64, 8), (33, 100)])
+def test_shanchen_odd_sizes_vs_oracle(nx, ny, variant):
+    """Grids that are no multiple of the tile: partial tiles wrap onto the periodic neighbours."""
+    api = _api()
+    cfg = api.shanchen_config(nx, ny)
+    cfg.kernel_variant = variant
+    ctx = api.Context(cfg)
+    rng = np.random.default_rng(nx * 1000 + ny)
+    f0 = np.array([4 / 9] + [1 / 9] * 4 + [1 / 36] * 4) * rng.uniform(0.2, 1.8, (nx * ny, 1)) * (1 + 0.01 * rng.uniform(-1, 1, (nx * ny, 9)))
+    ctx.set_populations(0, f0)
+    o = ol.OracleShanChen(nx, ny)
+    o.set_pops(f0)
+    for s in (1, 2, 40):
+        ctx.step(s)
+        o.step(s)
+        a = o.fields()
+        for k, name in (("rho", "rho"), ("u1", "ux"), ("u2", "uy")):
+            assert ndiff(a[k], ctx.get_field(name)) == 0, (k, s)
+        assert ndiff(o.pops(), ctx.get_populations(0)) == 0, s
+    ctx.close()
+    o.close()
 
 
 def test_binary2d_vs_oracle_and_golden():

@@ -33,13 +33,17 @@ def main():
     peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"] if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6650.0
     out = []
     # Shan-Chen: the reference droplet tiled with period 128
-    ctx = api.Context(api.shanchen_config(n, n))
     rho = np.tile(api.shanchen_initial_rho().reshape(128, 128), (n // 128, n // 128)).ravel()
-    ctx.set_field("rho", rho)
-    ctx.init()
-    ms = timed(ctx, 20)
-    out.append(("shanchen_d2q9", ms, 144))
-    ctx.close()
+    for variant, label in ((0, "shanchen_d2q9"), (3, "shanchen_d2q9 (tile 32x8, 64 regs)"), (5, "shanchen_d2q9 (tile 32x8)"),
+                           (1, "shanchen_d2q9 (two kernels)")):
+        cfg = api.shanchen_config(n, n)
+        cfg.kernel_variant = variant
+        ctx = api.Context(cfg)
+        ctx.set_field("rho", rho)
+        ctx.init()
+        ms = timed(ctx, 20)
+        out.append((label, ms, 144))
+        ctx.close()
     ctx = api.Context(api.binary2d_config(n, n))
     ph = np.tile(api.binary2d_initial_phase().reshape(128, 128), (n // 128, n // 128)).ravel()
     ctx.set_field("phase", ph)
