@@ -20,6 +20,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <unistd.h>
 #include <iostream>
 #include <sstream>
 #include <string>
@@ -157,6 +158,20 @@ void ref3d_set_pops(void *h, const double *f, const double *g)
     size_t n = (size_t)r->nx * r->ny * r->nz * 19;
     memcpy(l->f, f, n * sizeof(double));
     memcpy(l->g, g, n * sizeof(double));
+}
+
+// every text writer of the reference Solver (solver.hpp:578-787), into `dir`, under the names hosts/solver_selftest.cpp uses
+int ref3d_write_text(void *h, const char *dir)
+{
+    Ref3D *r = static_cast<Ref3D *>(h);
+    if (chdir(dir) != 0) return 1;
+    Solver<Descriptor> &s = *r->solver;
+    s.writeTextXZVelocity("vel_xz"); s.writeTextXYVelocity("vel_xy"); s.writeTextYZVelocity("vel_yz");
+    s.writeTextWholeVelocity("vel_whole"); s.writeTextWholePhase("phase_whole"); s.writeTextWholeDensity("density_whole");
+    s.writeTextXYPhase("phase_xy"); s.writeTextXZPhase("phase_xz"); s.writeTextYZPhase("phase_yz");
+    s.writeTextXYDensity("density_xy"); s.writeTextXZDensity("density_xz"); s.writeTextYZDensity("density_yz");
+    s.writeVTKWholePhase("phase_legacy");
+    return 0;
 }
 
 void ref3d_destroy(void *h)

@@ -118,3 +118,59 @@ def test_binary_shape_program_files(tmp_path):
     assert _sha16(tmp_path / "vtk0000200.vtk") == "a6ec05415407c75b"
     assert _sha16(tmp_path / "vtk0020000.vtk") == "50ccb783563608e9"
     assert len(os.listdir(tmp_path)) == 104
+
+
+# SHA-256 prefixes of the files the REFERENCE Solver's own text writers (solver.hpp:578-787, compiled into
+# oracle/_ref/libref_quarter.so, ref3d_write_text) produce for the run hosts/solver_selftest.cpp makes:
+# 14x11x16, phase_gradient 0.02, bubble width 4, 7 steps.
+REFERENCE_TEXT_FILES = {
+    "density_whole.dat": "fdc70e5cc6234728", "density_xy.dat": "00cf984c11a94a5e", "density_xz.dat": "b269441ccf0353a7",
+    "density_yz.dat": "f525e1b38910c6c4", "phase_legacy.vtk": "dc4becf80d4993dc", "phase_whole.dat": "ad3ea1c91c740252",
+    "phase_xy.dat": "777ce63a15d1b91d", "phase_xz.dat": "ec99e2896df95d9a", "phase_yz.dat": "8aecd41105084859",
+    "vel_whole.dat": "73ee85e965e22489", "vel_xy.dat": "dec06696d2736f8c", "vel_xz.dat": "33e2cda5e1da1793",
+    "vel_yz.dat": "d25ce8767bb049aa",
+}
+
+
+def test_solver_interface_writers_and_restarts(tmp_path):
+    """hosts/solver_b200.h (the reference Solver<D>'s method names on the C ABI): every text writer byte-identical
+    to the reference's, the .vts family readable, macroscopic restart (load_file) and exact restart
+    (savePopulations/loadPopulations) verified inside the program."""
+    out = _run("solver_selftest", [], str(tmp_path))
+    assert "solver_selftest OK" in out
+    for name, sha in REFERENCE_TEXT_FILES.items():
+        assert _sha16(tmp_path / name) == sha, name
+    a = _read_vts(tmp_path / "all.vts")
+    assert list(a) == ["Velocity", "Phase", "Density", "Points"]
+    assert list(_read_vts(tmp_path / "density.vts")) == ["Density", "Points"]
+    assert list(_read_vts(tmp_path / "velocity.vts")) == ["Velocity", "Points"]
+    assert np.array_equal(_read_vts(tmp_path / "phase.vts")["Phase"], a["Phase"])
+    assert np.array_equal(_read_vts(tmp_path / "local_phase_process0.vts")["Phase"], a["Phase"])
+    assert open(tmp_path / "local_phase_text_process0.dat").read() == open(tmp_path / "phase_whole.dat").read()
+    # the same run through the ctypes binding
+    from latticeboltzmannmethod_b200 import api
+    import oracle_lib as ol
+    cfg = api.microchannel_config("quarter", 14, 11, 16)
+    cfg.wall_gradient = 0.02
+    ctx = api.Context(cfg)
+    for name, f in zip(("rho", "phase", "ux", "uy", "uz"), ol.bubble_fields(14, 11, 16, 4)):
+        ctx.set_field(name, f)
+    ctx.init()
+    ctx.step(7)
+    assert np.array_equal(ctx.get_field("phase"), a["Phase"]) and np.array_equal(ctx.get_field("rho"), a["Density"])
+    assert np.array_equal(ctx.get_field("uz"), a["Velocity"].reshape(-1, 3)[:, 2])
+    ctx.close()
+
+
+def test_microchannel_checkpoint_restart(tmp_path):
+    """LBM_CHECKPOINT / LBM_RESTART of the drop-in QuarterChannel program: 201 steps in one go equal 141 + 60 bit for bit."""
+    one, two = tmp_path / "one", tmp_path / "two"
+    os.mkdir(one)
+    os.mkdir(two)
+    _run("microchannel_quarter", [], str(one), env={"LBM_NUMTIME": "201"})
+    _run("microchannel_quarter", [], str(two), env={"LBM_NUMTIME": "141", "LBM_CHECKPOINT": "ck"})
+    out = _run("microchannel_quarter", [], str(two), env={"LBM_NUMTIME": "201", "LBM_RESTART": "ck"})
+    assert "Time is 160" in out and "Time is 140" not in out
+    a, b = _read_vts(one / "phase00200.vts"), _read_vts(two / "phase00200.vts")
+    for k in ("Velocity", "Phase", "Density"):
+        assert np.array_equal(a[k], b[k]), k
