@@ -250,11 +250,15 @@ def ours(args, rank, world, local_rank):
     barrier()
 
     # ---- device-resident timing: K steps, CUDA events on the stream the kernels run on ----
+    # the sampler thread (NVML start-up takes tens of ms, different on every rank) is running before the barrier, so
+    # that all ranks record their first event and queue their first step together: a slab cannot run ahead of its
+    # neighbours, and any start skew would be billed to the early ranks as waiting time
     clocks = ClockSampler(local_rank)
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     launches0 = ctx.launch_count
     ctx.profile(True)
     clocks.start()
+    barrier()
     ev0.record(stream)
     ctx.step(args.steps)
     ev1.record(stream)
