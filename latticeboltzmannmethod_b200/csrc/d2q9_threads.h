@@ -155,20 +155,29 @@ LBM_HD void b2_phase_thread(const B2Params &P, const double *g, double *phase, i
     if (iy == NY - 2) phase[i + 1] = ph - P.wall_gradient;
 }
 
-LBM_HD void b2_stencils(const B2Params &P, const double *phase, int ix, int iy, double &gx, double &gy, double &lap)
+// binary.cpp:265-278: the three stencil sums over the nine phase values ph[k] (k = 0 the node itself), ascending k
+LBM_HD void b2_stencil_sums(const double (&ph)[9], double &gx, double &gy, double &lap)
 {
-    const int CX[9] = LBM2_CX, CY[9] = LBM2_CY;
     const float GX[9] = LBM2_B_GX, GY[9] = LBM2_B_GY, LAP[9] = LBM2_B_LAP;
     double al = 0.0, ax = 0.0, ay = 0.0;
 #pragma unroll
     for (int k = 0; k < 9; k++) {
-        const int x2 = (ix + CX[k] + P.nx) % P.nx, y2 = (iy + CY[k] + P.ny) % P.ny;
-        const double ph = phase[(long long)x2 * P.ny + y2];
-        al += LAP[k] * ph;
-        ax += GX[k] * ph;
-        ay += GY[k] * ph;
+        al += LAP[k] * ph[k];
+        ax += GX[k] * ph[k];
+        ay += GY[k] * ph[k];
     }
     gx = ax; gy = ay; lap = al;
+}
+LBM_HD void b2_stencils(const B2Params &P, const double *phase, int ix, int iy, double &gx, double &gy, double &lap)
+{
+    const int CX[9] = LBM2_CX, CY[9] = LBM2_CY;
+    double ph[9];
+#pragma unroll
+    for (int k = 0; k < 9; k++) {
+        const int x2 = (ix + CX[k] + P.nx) % P.nx, y2 = (iy + CY[k] + P.ny) % P.ny;
+        ph[k] = phase[(long long)x2 * P.ny + y2];
+    }
+    b2_stencil_sums(ph, gx, gy, lap);
 }
 
 // binary.cpp:291-313 (and :169-195)
@@ -213,47 +222,75 @@ LBM_HD void b2_init_thread(const B2Params &P, const double *phase, double *fa, d
     }
 }
 
-// binary.cpp:252-327 (collide), :201-233 (bounce-back rows) and :341-350 (pull streaming) as one
-// push: a population that would enter a wall row comes back to its own node reversed
+// binary.cpp:252-327 for one node whose populations F, G and the nine phase values of its stencil are in
+// registers; F and G hold the post-collision values on return
+LBM_HD void b2_collide_core(const B2Params &P, double (&F)[9], double (&G)[9], const double (&ph9)[9], double &d, double &ux, double &uy)
+{
+    const int CX[9] = LBM2_CX, CY[9] = LBM2_CY;
+    double jx = 0.0, jy = 0.0;
+    d = 0.0;
+#pragma unroll
+    for (int k = 0; k < 9; k++) {
+        d += F[k];
+        jx += F[k] * CX[k];
+        jy += F[k] * CY[k];
+    }
+    ux = jx / d;
+    uy = jy / d;
+    double gx, gy, lap, feq[9], geq[9];
+    b2_stencil_sums(ph9, gx, gy, lap);
+    const double ph = ph9[0];
+    b2_equilibria(P, d, ph, ux, uy, gx, gy, lap, feq, geq);
+    const double tau_rho = P.tau_gas + (ph + 1.0) / 2.0 * P.dtau;
+    const double omega_rho = 1.0 / tau_rho;
+#pragma unroll
+    for (int k = 0; k < 9; k++) {
+        F[k] = F[k] * (1.0 - omega_rho) + omega_rho * feq[k];
+        G[k] = G[k] * (1.0 - P.omega_phi) + P.omega_phi * geq[k];
+    }
+}
+
+// :201-233 (bounce-back rows) and :341-350 (pull streaming) as one push: a population that would enter a
+// wall row comes back to its own node reversed
+LBM_HD void b2_push(const B2Params &P, const double (&F)[9], const double (&G)[9], double *f2, double *g2, int ix, int iy)
+{
+    const int NX = P.nx, NY = P.ny;
+    const long long n = (long long)NX * NY, i = (long long)ix * NY + iy;
+    const int CX[9] = LBM2_CX, CY[9] = LBM2_CY, OPP[9] = LBM2_OPP;
+#pragma unroll
+    for (int k = 0; k < 9; k++) {
+        const int ty = iy + CY[k];
+        if (ty == 0 || ty == NY - 1) {
+            f2[OPP[k] * n + i] = F[k];
+            g2[OPP[k] * n + i] = G[k];
+        } else {
+            const long long t = (long long)((ix + CX[k] + NX) % NX) * NY + ty;
+            f2[k * n + t] = F[k];
+            g2[k * n + t] = G[k];
+        }
+    }
+}
+
+// the two-kernel form: the phase field comes from b2_phase_thread's array
 LBM_HD void b2_collide_thread(const B2Params &P, const double *f, const double *g, const double *phase, double *f2,
                               double *g2, double *rho, double *uxo, double *uyo, int ix, int iy, bool write_fields = true)
 {
     const int NX = P.nx, NY = P.ny;
     if (iy < 1 || iy > NY - 2) return;
     const long long n = (long long)NX * NY, i = (long long)ix * NY + iy;
-    const int CX[9] = LBM2_CX, CY[9] = LBM2_CY, OPP[9] = LBM2_OPP;
-    double F[9], G[9];
-    double d = 0.0, jx = 0.0, jy = 0.0;
+    const int CX[9] = LBM2_CX, CY[9] = LBM2_CY;
+    double F[9], G[9], ph9[9];
 #pragma unroll
     for (int k = 0; k < 9; k++) {
         F[k] = f[k * n + i];
         G[k] = g[k * n + i];
-        d += F[k];
-        jx += F[k] * CX[k];
-        jy += F[k] * CY[k];
+        const int x2 = (ix + CX[k] + NX) % NX, y2 = (iy + CY[k] + NY) % NY;
+        ph9[k] = phase[(long long)x2 * NY + y2];
     }
-    const double ux = jx / d, uy = jy / d;
+    double d, ux, uy;
+    b2_collide_core(P, F, G, ph9, d, ux, uy);
     if (write_fields) { rho[i] = d; uxo[i] = ux; uyo[i] = uy; }
-    double gx, gy, lap, feq[9], geq[9];
-    b2_stencils(P, phase, ix, iy, gx, gy, lap);
-    const double ph = phase[i];
-    b2_equilibria(P, d, ph, ux, uy, gx, gy, lap, feq, geq);
-    const double tau_rho = P.tau_gas + (ph + 1.0) / 2.0 * P.dtau;
-    const double omega_rho = 1.0 / tau_rho;
-#pragma unroll
-    for (int k = 0; k < 9; k++) {
-        const double fo = F[k] * (1.0 - omega_rho) + omega_rho * feq[k];
-        const double go = G[k] * (1.0 - P.omega_phi) + P.omega_phi * geq[k];
-        const int ty = iy + CY[k];
-        if (ty == 0 || ty == NY - 1) {
-            f2[OPP[k] * n + i] = fo;
-            g2[OPP[k] * n + i] = go;
-        } else {
-            const long long t = (long long)((ix + CX[k] + NX) % NX) * NY + ty;
-            f2[k * n + t] = fo;
-            g2[k * n + t] = go;
-        }
-    }
+    b2_push(P, F, G, f2, g2, ix, iy);
 }
 
 // ======================= MRT (MRT/mrt.cpp, MRT/another_mrt.cpp) =======================

@@ -199,9 +199,13 @@ def test_shanchen_odd_sizes_vs_oracle(nx, ny, variant):
     o.close()
 
 
-def test_binary2d_vs_oracle_and_golden():
+@pytest.mark.parametrize("variant", [0, 2, 3, 4])
+def test_binary2d_vs_oracle_and_golden(variant):
+    """variant 0: phase pass + collide (default); 2/3/4: the fused tile kernel (8x32, 4x32 at 96 registers, 4x32)."""
     api = _api()
-    ctx = api.Context(api.binary2d_config())
+    cfg = api.binary2d_config()
+    cfg.kernel_variant = variant
+    ctx = api.Context(cfg)
     ctx.set_field("phase", api.binary2d_initial_phase())
     ctx.init()
     o = ol.OracleBinary2D(128, 128)
@@ -229,11 +233,14 @@ def test_binary2d_vs_oracle_and_golden():
     ctx.close()
 
 
-def test_binary2d_random_odd_size():
+@pytest.mark.parametrize("variant", [0, 2, 3, 4])
+@pytest.mark.parametrize("nx,ny", [(37, 23), (4, 70), (65, 34), (9, 33)])
+def test_binary2d_random_odd_size(nx, ny, variant):
     api = _api()
-    nx, ny = 37, 23
     ph0 = np.random.default_rng(1).uniform(-1, 1, nx * ny)
-    ctx = api.Context(api.binary2d_config(nx, ny))
+    cfg = api.binary2d_config(nx, ny)
+    cfg.kernel_variant = variant
+    ctx = api.Context(cfg)
     ctx.set_field("phase", ph0)
     ctx.init()
     o = ol.OracleBinary2D(nx, ny)
@@ -244,6 +251,8 @@ def test_binary2d_random_odd_size():
         a = o.fields()
         for k in ("phase", "rho", "ux", "uy"):
             assert ndiff(a[k], ctx.get_field(k)) == 0, (k, s)
+        fo, go = o.pops()
+        assert ndiff(fo, ctx.get_populations(0)) == 0 and ndiff(go, ctx.get_populations(1)) == 0, s
     ctx.close()
     o.close()
 
