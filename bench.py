@@ -107,8 +107,18 @@ def reference_arm(args, rank):
         return
     ranks = host_ranks()
     nx, ny, nz = cpu_sample_grid(ranks)
-    cfg = {"workload": "QuarterChannel D3Q19 binary liquid, bounded sample %dx%dx%d of the %dx%dx%d-per-GPU job" % (nx, ny, nz, args.nx, args.ny, args.nz_per_gpu),
-           "precision": "fp64", "host_ranks": ranks}
+    # the same config block as our arm prints for this --gpus (the job the numbers are about); the reference's CPU
+    # code runs a bounded sample of it, named in `sample`
+    world = max(1, args.gpus)
+    if args.workload == "full":
+        wl = "Microchannel3D/FullChannel 92x52x1500 (BASELINE.json configs[3]), z-slabs over %d GPU(s)" % world
+        jx, jy, jz = 92, 52, 1500
+    else:
+        jx, jy, jz = args.nx, args.ny, args.nz_per_gpu * world
+        wl = "Microchannel3D/QuarterChannel scaled to %dx%dx%d (%d planes per GPU; BASELINE.json configs[4])" % (jx, jy, jz, args.nz_per_gpu)
+    cfg = {"workload": wl, "nx": jx, "ny": jy, "nz": jz, "nodes": jx * jy * jz, "precision": "fp64",
+           "sample": "the unmodified reference Lattice/Solver on a %dx%dx%d sample of that job, %d host ranks (mini-MPI z-slabs)" % (nx, ny, nz, ranks),
+           "host_ranks": ranks}
     if ref_binary():
         r = run_reference_cpu(nx, ny, nz, args.warmup, args.steps, ranks)
         kind, val, sec = "reference", r["mlups"], r["seconds"]
