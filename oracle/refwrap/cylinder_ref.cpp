@@ -12,6 +12,7 @@
 #include <cmath>
 #include <vector>
 #include <cstring>
+#include <unistd.h>
 
 #define main ref_main
 #include "DiffusionCylinder/cylinder.cpp"
@@ -25,9 +26,12 @@ void refcyl_shape(int *nx, int *ny, int *npop) { *nx = 129; *ny = 129; *npop = N
 // The constants and the velocity field are the program's own globals (cylinder.cpp:27-28,33,38-43): a
 // non-positive omega_in keeps the compiled-in constants; ux_in/uy_in/rho_in (may be NULL) overwrite the
 // fields initialize_geometry() filled, before init() builds the populations from them.
-int refcyl_run(int steps, double omega_in, double ce_in, double conc_wall_in, const double *rho_in, const double *ux_in,
-               const double *uy_in, double *rho_out, double *f_out, int *geom_out)
+// workdir: initialize_geometry() writes antibbgeometry_before.dat / antibbgeometry_after.dat into the current
+// directory (cylinder.cpp:243,284).
+int refcyl_run(int steps, const char *workdir, double omega_in, double ce_in, double conc_wall_in, const double *rho_in,
+               const double *ux_in, const double *uy_in, double *rho_out, double *f_out, int *geom_out)
 {
+    if (workdir && chdir(workdir) != 0) return 2;
     if (omega_in > 0.0) {
         omega = omega_in; omega_plus = 2.0 - omega; omega_minus = omega;
         ce = ce_in; conc_wall = conc_wall_in;

@@ -412,11 +412,16 @@ def trt_advected_fields(mask, conc_wall, speed=0.05):
 def ref_cylinder_run(steps, omega=0.0, ce=0.0, conc_wall=0.0, rho=None, ux=None, uy=None):
     """The unmodified cylinder.cpp (129x129, radius 40) for `steps` loop iterations; omega <= 0 keeps its constants."""
     L = C.CDLL(os.path.join(REF_DIR, "libref_cylinder.so"))
-    L.refcyl_run.argtypes = [C.c_int, C.c_double, C.c_double, C.c_double, dp, dp, dp, dp, dp, C.c_void_p]
+    L.refcyl_run.argtypes = [C.c_int, C.c_char_p, C.c_double, C.c_double, C.c_double, dp, dp, dp, dp, dp, C.c_void_p]
     n = 129 * 129
     keep = [None if x is None else np.ascontiguousarray(x, dtype=np.float64).ravel() for x in (rho, ux, uy)]
     r, f, g = np.empty(n), np.empty(n * 9), np.zeros(n, np.int32)
-    rc = L.refcyl_run(steps, omega, ce, conc_wall, *[None if x is None else _p(x) for x in keep], _p(r), _p(f), g.ctypes.data)
+    cwd = os.getcwd()
+    try:
+        rc = L.refcyl_run(steps, _scratch().encode(), omega, ce, conc_wall, *[None if x is None else _p(x) for x in keep],
+                          _p(r), _p(f), g.ctypes.data)
+    finally:
+        os.chdir(cwd)
     assert rc == 0, rc
     return dict(nx=129, ny=129, rho=r, f=f.reshape(-1, 9), geometry=g)
 
