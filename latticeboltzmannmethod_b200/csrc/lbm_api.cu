@@ -14,9 +14,15 @@ thread_local std::string g_create_error;
 
 bool have_ctx(lbm_ctx *ctx) { return ctx && ctx->model; }
 
+// Every entry point binds the context's device and drops a stale *non-sticky* error another call left behind
+// in this thread (ours are read right after each launch; a faulted kernel's error is sticky and survives this),
+// so that the next launch check reports its own launch and nothing else.
 lbm_status bind_device(lbm_ctx *ctx)
 {
-    return ctx->rt.cuda(cudaSetDevice(ctx->rt.device), "cudaSetDevice");
+    LBM_TRY(ctx->rt.cuda(cudaSetDevice(ctx->rt.device), "cudaSetDevice"));
+    ctx->bound = true;
+    (void)cudaGetLastError();
+    return LBM_OK;
 }
 }  // namespace
 
@@ -109,7 +115,7 @@ lbm_status lbm_create(const lbm_config *cfg, lbm_ctx **out)
 void lbm_destroy(lbm_ctx *ctx)
 {
     if (!ctx) return;
-    cudaSetDevice(ctx->rt.device);
+    if (ctx->bound) cudaSetDevice(ctx->rt.device);     // a context whose device never existed owns nothing on it
     if (ctx->rt.stream) cudaStreamSynchronize(ctx->rt.stream);
     delete ctx->model;
     if (ctx->rt.own_stream && ctx->rt.stream) cudaStreamDestroy(ctx->rt.stream);

@@ -140,6 +140,7 @@ struct lbm_ctx {
     lbm::Runtime rt;
     lbm::Model *model = nullptr;
     bool initialised = false;
+    bool bound = false;   // cudaSetDevice(rt.device) has succeeded at least once
 };
 
 #endif

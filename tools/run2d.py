@@ -11,10 +11,14 @@ from latticeboltzmannmethod_b200 import api  # noqa: E402
 
 
 def main():
-    model = sys.argv[1]
-    n = int(sys.argv[2]) if len(sys.argv) > 2 else 8192
-    steps = int(sys.argv[3]) if len(sys.argv) > 3 else 4
-    variant = int(sys.argv[4]) if len(sys.argv) > 4 else 0
+    if sys.argv[1] == "all":
+        for m in ("shanchen", "binary", "mrt_gs", "mrt_hermite", "trt", "shape"):
+            run(m, *[int(a) for a in sys.argv[2:]])
+        return
+    run(sys.argv[1], *[int(a) for a in sys.argv[2:]])
+
+
+def run(model, n=8192, steps=4, variant=0):
     if model == "shanchen":
         cfg = api.shanchen_config(n, n)
         fields = dict(rho=np.tile(api.shanchen_initial_rho().reshape(128, 128), (n // 128, n // 128)).ravel())
