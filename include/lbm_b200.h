@@ -116,7 +116,8 @@ lbm_status lbm_set_field(lbm_ctx *ctx, int field, const double *host, size_t n);
 lbm_status lbm_set_geometry(lbm_ctx *ctx, const int *mask, size_t n);
 
 /* Replaces: init() of binary.cpp:122-198; the init loops of shanchen.cpp:87-114
- * (from the rho field), mrt.cpp:97-120 / another_mrt.cpp:89-110 and cylinder.cpp:97-124 (from rho,ux,uy),
+ * (from the rho field and the velocity fields, which are zero in a new context as the program's globals are;
+ * after lbm_step they hold the last output, so set them again before re-initialising), mrt.cpp:97-120 / another_mrt.cpp:89-110 and cylinder.cpp:97-124 (from rho,ux,uy),
  * binary_shape.cpp:222-258 (from rho,phase,ux,uy);
  * Solver::init (solver.hpp:871-879) incl. its phase halo exchange. */
 lbm_status lbm_init(lbm_ctx *ctx);
