@@ -179,12 +179,14 @@ __global__ void __launch_bounds__(kThreads) k_mrt_init(lbm2::MrtParams P, const 
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < (long long)P.nx * P.ny) lbm2::mrt_init_thread(P, rho, ux, uy, f, i);
 }
-template <bool WRITE>
-__global__ void __launch_bounds__(kThreads) k_mrt_step(lbm2::MrtParams P, const double *f, const double *force, double *f2,
-                                                        double *rho, double *ux, double *uy)
+template <int VARIANT, bool WRITE>
+__global__ void __launch_bounds__(kThreads) k_mrt_step(lbm2::MrtParams P, const double *__restrict__ f, const double *__restrict__ force,
+                                                        double *__restrict__ f2, double *__restrict__ rho, double *__restrict__ ux,
+                                                        double *__restrict__ uy)
 {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < (long long)P.nx * P.ny) lbm2::mrt_thread(P, f, force, f2, rho, ux, uy, (int)(i / P.ny), (int)(i % P.ny), WRITE);
+    if (i < (long long)P.nx * P.ny)
+        lbm2::mrt_thread_v<VARIANT>(P, f, force, f2, rho, ux, uy, (int)(i / P.ny), (int)(i % P.ny), WRITE);
 }
 // ---- TRT diffusion kernels (node index i = iY*nx+iX) ----
 __global__ void __launch_bounds__(kThreads) k_trt_init(lbm2::TrtParams P, const double *rho, const double *ux, const double *uy,
@@ -496,7 +498,8 @@ public:
     {
         for (int t = 0; t < nsteps; t++) {
             rt_.about_to_launch();
-            auto kern = t == nsteps - 1 ? k_mrt_step<true> : k_mrt_step<false>;
+            const bool w = t == nsteps - 1;
+            auto kern = P_.variant == 0 ? (w ? k_mrt_step<0, true> : k_mrt_step<0, false>) : (w ? k_mrt_step<1, true> : k_mrt_step<1, false>);
             kern<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, f_[cur_], aux_, f_[1 - cur_], fields_[LBM_RHO], fields_[LBM_UX],
                                                               fields_[LBM_UY]);
             LBM_TRY(rt_.launched("k_mrt_step"));

@@ -306,8 +306,41 @@ struct MrtParams {
 // back-transform, periodic push.  mrt.cpp:146-251 / another_mrt.cpp:114-214.
 // forcex_of_ix: the per-column force mrt.cpp:165 evaluates with cos(); built on the host with the
 // same expression so the device needs no cos().
-LBM_HD void mrt_thread(const MrtParams &P, const double *f, const double *forcex_of_ix, double *f2, double *rho_o,
-                       double *ux_o, double *uy_o, int ix, int iy, bool write_fields = true)
+//
+// The transforms are written against the sparsity of M, which is a property of the lattice, not of the run:
+// M[m][k] is structurally zero where the row's polynomial in (cx, cy) vanishes (GS: 22 of 81 entries, Hermite 17),
+// and the Gram-Schmidt rows are small integers.  Skipping a structurally zero term and replacing a product with
+// +-1 by the operand are exact: the accumulators start at +0.0 and can never become -0.0, and x*1.0 == x.
+// (What is NOT done: no re-association, no contraction, every remaining product and sum in the reference order.)
+LBM_HD bool mrt_structural_nonzero(int variant, int m, int k)
+{
+    const int CX[9] = LBM2_CX, CY[9] = LBM2_CY;
+    const bool x = CX[k] != 0, y = CY[k] != 0;
+    if (variant == 0) {   // mrt.cpp:71-80
+        switch (m) {
+        case 3: case 4: return x;
+        case 5: case 6: return y;
+        case 7: return x != y;      // cx^2 - cy^2
+        case 8: return x && y;      // cx cy
+        default: return true;
+        }
+    }
+    switch (m) {          // another_mrt.cpp:75-84
+    case 1: case 7: return x;
+    case 2: case 8: return y;
+    case 4: return x && y;
+    default: return true;
+    }
+}
+// mrt.cpp:71-80 evaluated: the Gram-Schmidt matrix (exact small integers; the unit test pins it to mrt_build_tables)
+#define LBM2_MRT_GS_M                                                                                                       \
+    {{1, 1, 1, 1, 1, 1, 1, 1, 1}, {-4, -1, -1, -1, -1, 2, 2, 2, 2}, {4, -2, -2, -2, -2, 1, 1, 1, 1},                         \
+     {0, 1, 0, -1, 0, 1, -1, -1, 1}, {0, -2, 0, 2, 0, 1, -1, -1, 1}, {0, 0, 1, 0, -1, 1, 1, -1, -1},                          \
+     {0, 0, -2, 0, 2, 1, 1, -1, -1}, {0, 1, -1, 1, -1, 0, 0, 0, 0}, {0, 0, 0, 0, 0, 1, -1, 1, -1}}
+
+template <int VARIANT>
+LBM_HD void mrt_thread_v(const MrtParams &P, const double *f, const double *forcex_of_ix, double *f2, double *rho_o,
+                         double *ux_o, double *uy_o, int ix, int iy, bool write_fields)
 {
     const int NX = P.nx, NY = P.ny;
     const long long n = (long long)NX * NY, i = (long long)ix * NY + iy;
@@ -325,7 +358,9 @@ LBM_HD void mrt_thread(const MrtParams &P, const double *f, const double *forcex
     const double dense = rho;
     ux /= dense;
     uy /= dense;
-    if (P.variant == 0) {
+    const double *om = P.omegamat;
+    double momforce[9];
+    if (VARIANT == 0) {
         const double forcex = forcex_of_ix[ix];
         const double forcey = 0;
         ux += forcex / (2.0 * dense);
@@ -340,8 +375,6 @@ LBM_HD void mrt_thread(const MrtParams &P, const double *f, const double *forcex
         eq[6] = -dense * uyeq;
         eq[7] = dense * (uxeq * uxeq - uyeq * uyeq);
         eq[8] = dense * uxeq * uyeq;
-        const double *om = P.omegamat;
-        double momforce[9];
         momforce[0] = 0.0;
         momforce[1] = (1.0 - om[1] / 2.0) * 6.0 * (uxeq * forcex + uyeq * forcey);
         momforce[2] = 0.0;
@@ -351,23 +384,6 @@ LBM_HD void mrt_thread(const MrtParams &P, const double *f, const double *forcex
         momforce[6] = 0.0;
         momforce[7] = (1.0 - om[7] / 2.0) * 2.0 * (uxeq * forcex - uyeq * forcey);
         momforce[8] = (1.0 - om[8] / 2.0) * (uxeq * forcey + uyeq * forcex);
-#pragma unroll
-        for (int m = 0; m < 9; m++) {
-            double a = 0.0;
-#pragma unroll
-            for (int k = 0; k < 9; k++) a = a + P.M[m][k] * (-fl[k]);
-            a += eq[m];
-            a *= om[m];
-            a += momforce[m];
-            add[m] = a;
-        }
-#pragma unroll
-        for (int k = 0; k < 9; k++) {
-            double addit = 0.0;
-#pragma unroll
-            for (int m = 0; m < 9; m++) addit = addit + P.B[k][m] * add[m];
-            fl[k] = fl[k] + addit;
-        }
     } else {
         const double uxeq = ux, uyeq = uy;
         eq[0] = dense;
@@ -379,21 +395,39 @@ LBM_HD void mrt_thread(const MrtParams &P, const double *f, const double *forcex
         eq[6] = 4.5 * dense * uxeq * uxeq * uyeq * uyeq;
         eq[7] = P.c3s15 * dense * uxeq * uyeq * uyeq;
         eq[8] = P.c3s15 * dense * uxeq * uxeq * uyeq;
+    }
+    // forward transform of -f, plus equilibrium moments (and, GS, relaxation and forcing in moment space)
+    const int MGS[9][9] = LBM2_MRT_GS_M;
 #pragma unroll
-        for (int m = 0; m < 9; m++) {
-            double a = 0.0;
-#pragma unroll
-            for (int k = 0; k < 9; k++) a = a + P.M[m][k] * (-fl[k]);
-            a += eq[m];
-            add[m] = a;
-        }
+    for (int m = 0; m < 9; m++) {
+        double a = 0.0;
 #pragma unroll
         for (int k = 0; k < 9; k++) {
-            double addit = 0.0;
-#pragma unroll
-            for (int m = 0; m < 9; m++) addit = addit + P.B[k][m] * add[m];
-            fl[k] = fl[k] + W[k] * addit;
+            if (!mrt_structural_nonzero(VARIANT, m, k)) continue;
+            if (VARIANT == 0) {
+                const int c = MGS[m][k];
+                if (c == 1) a = a + (-fl[k]);
+                else if (c == -1) a = a + fl[k];
+                else a = a + (double)c * (-fl[k]);
+            } else {
+                a = a + P.M[m][k] * (-fl[k]);
+            }
         }
+        a += eq[m];
+        if (VARIANT == 0) {
+            a *= om[m];
+            a += momforce[m];
+        }
+        add[m] = a;
+    }
+    // back transform
+#pragma unroll
+    for (int k = 0; k < 9; k++) {
+        double addit = 0.0;
+#pragma unroll
+        for (int m = 0; m < 9; m++)
+            if (mrt_structural_nonzero(VARIANT, m, k)) addit = addit + P.B[k][m] * add[m];
+        fl[k] = VARIANT == 0 ? fl[k] + addit : fl[k] + W[k] * addit;
     }
     if (write_fields) { rho_o[i] = rho; ux_o[i] = ux; uy_o[i] = uy; }
 #pragma unroll
@@ -401,6 +435,12 @@ LBM_HD void mrt_thread(const MrtParams &P, const double *f, const double *forcex
         const long long t = (long long)((ix + CX[k] + NX) % NX) * NY + (iy + CY[k] + NY) % NY;
         f2[k * n + t] = fl[k];
     }
+}
+LBM_HD void mrt_thread(const MrtParams &P, const double *f, const double *forcex_of_ix, double *f2, double *rho_o,
+                       double *ux_o, double *uy_o, int ix, int iy, bool write_fields = true)
+{
+    if (P.variant == 0) mrt_thread_v<0>(P, f, forcex_of_ix, f2, rho_o, ux_o, uy_o, ix, iy, write_fields);
+    else mrt_thread_v<1>(P, f, forcex_of_ix, f2, rho_o, ux_o, uy_o, ix, iy, write_fields);
 }
 
 // mrt.cpp:107-119 / another_mrt.cpp:97-109: second-order equilibrium from given rho, ux, uy
