@@ -108,8 +108,8 @@ __global__ void __launch_bounds__(kThreads) k_b2_phase(lbm2::B2Params P, const d
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < (long long)P.nx * P.ny) lbm2::b2_phase_thread(P, g, phase, (int)(i / P.ny), (int)(i % P.ny));
 }
-template <bool WRITE>
-__global__ void __launch_bounds__(kThreads) k_b2_collide(lbm2::B2Params P, const double *f, const double *g, const double *phase,
+template <bool WRITE, int NT = kThreads>
+__global__ void __launch_bounds__(NT) k_b2_collide(lbm2::B2Params P, const double *f, const double *g, const double *phase,
                                                           double *f2, double *g2, double *rho, double *ux, double *uy)
 {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -216,8 +216,8 @@ __global__ void __launch_bounds__(kThreads) k_bs_phase(lbm2::BsParams P, const d
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < (long long)P.nx * P.ny) lbm2::bs_phase_thread(P, g, links, phi, i);
 }
-template <bool WRITE>
-__global__ void __launch_bounds__(kThreads, 2) k_bs_collide(lbm2::BsParams P, const double *__restrict__ f, const double *__restrict__ g,
+template <bool WRITE, int NT = kThreads, int MINB = 2>
+__global__ void __launch_bounds__(NT, MINB) k_bs_collide(lbm2::BsParams P, const double *__restrict__ f, const double *__restrict__ g,
                                                           const double *__restrict__ phi, const unsigned short *__restrict__ links,
                                                           double *__restrict__ f2, double *__restrict__ g2, double *__restrict__ rho,
                                                           double *__restrict__ ux, double *__restrict__ uy)
@@ -432,7 +432,7 @@ public:
     }
     lbm_status step(int nsteps) override
     {
-        // kernel_variant 0 (default) and 1: phase pass + collide, the fastest measured (4.26 ms at 8192^2).  The fused
+        // kernel_variant 0 (default) and 1: phase pass + collide, the fastest measured (4.11 ms at 8192^2).  The fused
         // tile kernel is kept as variants 2 (8 columns x 32 rows, 5.37 ms), 3 (4 x 32 capped at 96 registers, 4.52 ms)
         // and 4 (4 x 32, 5.08 ms): unlike Shan-Chen's, this collision needs ~125 registers, so the fused form gains
         // no occupancy and pays for the ring and the barrier.
@@ -455,9 +455,16 @@ public:
             k_b2_phase<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, g_[cur_], fields_[LBM_PHASE]);
             LBM_TRY(rt_.launched("k_b2_phase"));
             rt_.about_to_launch();
-            auto kern = t == nsteps - 1 ? k_b2_collide<true> : k_b2_collide<false>;
-            kern<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, f_[cur_], g_[cur_], fields_[LBM_PHASE], f_[1 - cur_], g_[1 - cur_],
-                                                              fields_[LBM_RHO], fields_[LBM_UX], fields_[LBM_UY]);
+            const bool w = t == nsteps - 1;
+            if (cfg_.kernel_variant != 1) {     // default: 128-thread blocks (4.11 ms at 8192^2; variant 1, 256 threads: 4.23 ms)
+                auto kern = w ? k_b2_collide<true, 128> : k_b2_collide<false, 128>;
+                kern<<<(unsigned)((n_ + 127) / 128), 128, 0, rt_.stream>>>(P_, f_[cur_], g_[cur_], fields_[LBM_PHASE], f_[1 - cur_], g_[1 - cur_],
+                                                                          fields_[LBM_RHO], fields_[LBM_UX], fields_[LBM_UY]);
+            } else {
+                auto kern = w ? k_b2_collide<true> : k_b2_collide<false>;
+                kern<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, f_[cur_], g_[cur_], fields_[LBM_PHASE], f_[1 - cur_], g_[1 - cur_],
+                                                                  fields_[LBM_RHO], fields_[LBM_UX], fields_[LBM_UY]);
+            }
             LBM_TRY(rt_.launched("k_b2_collide"));
             cur_ = 1 - cur_;
         }
@@ -649,9 +656,22 @@ public:
             k_bs_phase<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, g_[cur_], links_, fields_[LBM_PHASE]);
             LBM_TRY(rt_.launched("k_bs_phase"));
             rt_.about_to_launch();
-            auto kern = t == nsteps - 1 ? k_bs_collide<true> : k_bs_collide<false>;
-            kern<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, f_[cur_], g_[cur_], fields_[LBM_PHASE], links_, f_[1 - cur_], g_[1 - cur_],
-                                                              fields_[LBM_RHO], fields_[LBM_UX], fields_[LBM_UY]);
+            // kernel_variant 0 (default): 128 threads x 4 blocks/SM (128 registers), 4.27 ms at 8192^2; 1: 128 threads x 3
+            // (168 registers, no spills), 4.75 ms; 2: 256 threads x 2 (128 registers), 4.45 ms
+            const bool w = t == nsteps - 1;
+            if (cfg_.kernel_variant == 1) {
+                auto kern = w ? k_bs_collide<true, 128, 3> : k_bs_collide<false, 128, 3>;
+                kern<<<(unsigned)((n_ + 127) / 128), 128, 0, rt_.stream>>>(P_, f_[cur_], g_[cur_], fields_[LBM_PHASE], links_, f_[1 - cur_],
+                                                                          g_[1 - cur_], fields_[LBM_RHO], fields_[LBM_UX], fields_[LBM_UY]);
+            } else if (cfg_.kernel_variant != 2) {
+                auto kern = w ? k_bs_collide<true, 128, 4> : k_bs_collide<false, 128, 4>;
+                kern<<<(unsigned)((n_ + 127) / 128), 128, 0, rt_.stream>>>(P_, f_[cur_], g_[cur_], fields_[LBM_PHASE], links_, f_[1 - cur_],
+                                                                          g_[1 - cur_], fields_[LBM_RHO], fields_[LBM_UX], fields_[LBM_UY]);
+            } else {
+                auto kern = w ? k_bs_collide<true> : k_bs_collide<false>;
+                kern<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, f_[cur_], g_[cur_], fields_[LBM_PHASE], links_, f_[1 - cur_],
+                                                                  g_[1 - cur_], fields_[LBM_RHO], fields_[LBM_UX], fields_[LBM_UY]);
+            }
             LBM_TRY(rt_.launched("k_bs_collide"));
             cur_ = 1 - cur_;
         }

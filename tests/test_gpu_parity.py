@@ -199,9 +199,9 @@ def test_shanchen_odd_sizes_vs_oracle(nx, ny, variant):
     o.close()
 
 
-@pytest.mark.parametrize("variant", [0, 2, 3, 4])
+@pytest.mark.parametrize("variant", [0, 1, 2, 3, 4])
 def test_binary2d_vs_oracle_and_golden(variant):
-    """variant 0: phase pass + collide (default); 2/3/4: the fused tile kernel (8x32, 4x32 at 96 registers, 4x32)."""
+    """variant 0/1: phase pass + collide (128- / 256-thread blocks); 2/3/4: the fused tile kernel (8x32, 4x32 at 96 registers, 4x32)."""
     api = _api()
     cfg = api.binary2d_config()
     cfg.kernel_variant = variant

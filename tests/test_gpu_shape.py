@@ -17,10 +17,11 @@ def _api():
     return api
 
 
-def _ctx(api, nx, ny, mask, rho, phi, ux, uy, params=ol.PARAMS_SHAPE):
+def _ctx(api, nx, ny, mask, rho, phi, ux, uy, params=ol.PARAMS_SHAPE, variant=0):
     cfg = api.shape_config(nx, ny, wall_gradient=params[3], aconst=params[0], kconst=params[1], gammaconst=params[2],
                            tau_gas=params[4], tau_liq=params[5], tau_phi=1.0 / params[6])
     cfg.force[0], cfg.force[1] = params[7], params[8]
+    cfg.kernel_variant = variant
     ctx = api.Context(cfg)
     ctx.set_geometry(mask)
     for name, a in (("rho", rho), ("phase", phi), ("ux", ux), ("uy", uy)):
@@ -68,12 +69,13 @@ def test_shape_perturbed_golden(steps):
     ctx.close()
 
 
+@pytest.mark.parametrize("variant", [0, 1, 2])
 @pytest.mark.parametrize("nx,ny", [(64, 48), (131, 77), (517, 263)])
-def test_shape_random_geometry_vs_oracle(nx, ny):
+def test_shape_random_geometry_vs_oracle(nx, ny, variant):
     api = _api()
     mask, rho, phi, ux, uy = ol.shape_random_case(nx, ny, seed=nx)
     params = [0.04, 0.04, 1.0, -0.15, 0.7, 2.5, 0.5, 0.0, 3e-5]
-    ctx = _ctx(api, nx, ny, mask, rho, phi, ux, uy, params)
+    ctx = _ctx(api, nx, ny, mask, rho, phi, ux, uy, params, variant)
     o = ol.OracleShape(nx, ny, mask, params)
     o.init(rho, phi, ux, uy)
     for s in (0, 1, 2, 60):

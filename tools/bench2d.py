@@ -83,17 +83,20 @@ def main():
                       "frac_of_measured_hbm": (fluid * 168 + n * n * 2) / ms / 1e6 / peak}))
     # curved solid: the reference disc and droplets scaled to the grid
     mask, rho, phi, ux, uy = api.shape_setup(n, n, radius=int(n * 50 / 301), radius_droplet=int(n * 10 / 301))
-    ctx = api.Context(api.shape_config(n, n))
-    ctx.set_geometry(mask)
-    for name, a in (("rho", rho), ("phase", phi), ("ux", ux), ("uy", uy)):
-        ctx.set_field(name, a)
-    ctx.init()
-    ms = timed(ctx, 20)
     fluid = int((mask == 1).sum())
-    ctx.close()
-    print(json.dumps({"model": "binary_shape_d2q9", "grid": [n, n], "fluid_nodes": fluid, "ms_per_step": ms,
-                      "mlups": fluid / ms / 1e3, "bytes_per_update": 288, "achieved_gbs": fluid * 288 / ms / 1e6,
-                      "frac_of_measured_hbm": fluid * 288 / ms / 1e6 / peak}))
+    for variant in (0,):
+        cfg = api.shape_config(n, n)
+        cfg.kernel_variant = variant
+        ctx = api.Context(cfg)
+        ctx.set_geometry(mask)
+        for name, a in (("rho", rho), ("phase", phi), ("ux", ux), ("uy", uy)):
+            ctx.set_field(name, a)
+        ctx.init()
+        ms = timed(ctx, 20)
+        ctx.close()
+        print(json.dumps({"model": "binary_shape_d2q9" if variant == 0 else "binary_shape_d2q9 (variant %d)" % variant, "grid": [n, n], "fluid_nodes": fluid, "ms_per_step": ms,
+                          "mlups": fluid / ms / 1e3, "bytes_per_update": 288, "achieved_gbs": fluid * 288 / ms / 1e6,
+                          "frac_of_measured_hbm": fluid * 288 / ms / 1e6 / peak}))
     for name, ms, b in out:
         mlups = n * n / ms / 1e3
         print(json.dumps({"model": name, "grid": [n, n], "ms_per_step": ms, "mlups": mlups, "bytes_per_update": b,
