@@ -54,8 +54,8 @@ __global__ void __launch_bounds__(128, MINB) k_collide_push_occ(Geom g, Params P
 // (nodes 2..NX-3 x 2..NY-3: every push is a plain shifted store), which removes the control-flow merges
 // and register moves the folded boundary path costs every thread; the rim kernel runs the one-node rim
 // (and, on output steps, the wall-node fields) -- 2(NX+NY) nodes per plane.
-template <bool FXY, bool WRITE, int MINB, bool XRIM = false, bool TILE2D = false>
-__global__ void __launch_bounds__(128, MINB) k_collide_interior(Geom g, Params P, const double *__restrict__ fin,
+template <bool FXY, bool WRITE, int MINB, bool XRIM = false, bool TILE2D = false, int NT = 128>
+__global__ void __launch_bounds__(NT, MINB) k_collide_interior(Geom g, Params P, const double *__restrict__ fin,
                                                                 const double *__restrict__ gin, const double *__restrict__ phi,
                                                                 double *__restrict__ fout, double *__restrict__ gout, FieldsOut o,
                                                                 int zs0)
@@ -72,7 +72,7 @@ __global__ void __launch_bounds__(128, MINB) k_collide_interior(Geom g, Params P
         if (ix >= NX || iy >= NY) return;
         idx = (long long)iy * NX + ix;
     } else {
-        idx = (long long)blockIdx.x * 128 + threadIdx.x;
+        idx = (long long)blockIdx.x * NT + threadIdx.x;
         if (idx >= (long long)NX * NY) return;
         ix = (int)(idx % NX);
         iy = (int)(idx / NX);
@@ -566,6 +566,7 @@ public:
         const FieldsOut o = fields_out();
         const dim3 gi((unsigned)(((long long)g_.nx * g_.ny + 127) / 128), count);
         const dim3 gt((unsigned)(((g_.nx + 31) / 32) * ((g_.ny + 3) / 4)), count);
+        const dim3 g64((unsigned)(((long long)g_.nx * g_.ny + 63) / 64), count);
         const int rim = 2 * (g_.nx - 2) + g_.nx + g_.ny - 1;
         const dim3 gr((rim + 127) / 128, count);
 #define LBM_LAUNCH_DEFAULT(FXY, WR)                                                                                            \
@@ -573,6 +574,8 @@ public:
         rt_.about_to_launch();                                                                                                 \
         if (cfg_.kernel_variant == 65)                                                                                         \
             k_collide_interior<FXY, WR, 2, true><<<gi, 128, 0, rt_.stream>>>(g_, P_, f_[a], gq_[a], phi_, f_[b], gq_[b], o, zs0); \
+        else if (cfg_.kernel_variant == 67)                                                                                    \
+            k_collide_interior<FXY, WR, 6, true, false, 64><<<g64, 64, 0, rt_.stream>>>(g_, P_, f_[a], gq_[a], phi_, f_[b], gq_[b], o, zs0); \
         else if (cfg_.kernel_variant == 66)                                                                                    \
             k_collide_interior<FXY, WR, 3, true, true><<<gt, 128, 0, rt_.stream>>>(g_, P_, f_[a], gq_[a], phi_, f_[b], gq_[b], o, zs0); \
         else                                                                                                                   \
@@ -692,7 +695,7 @@ public:
             LBM_CUDA(rt_, cudaStreamWaitEvent(rt_.stream, ev_join_, 0));
             return LBM_OK;
         }
-        if (cfg_.kernel_variant == 0 || cfg_.kernel_variant == 65 || cfg_.kernel_variant == 66) return collide_default(1, g_.nz + 2, write_fields);
+        if (cfg_.kernel_variant == 0 || cfg_.kernel_variant == 65 || cfg_.kernel_variant == 66 || cfg_.kernel_variant == 67) return collide_default(1, g_.nz + 2, write_fields);
         if (cfg_.kernel_variant >= 60 && cfg_.kernel_variant <= 62) {
             const dim3 gi((unsigned)(((long long)g_.nx * g_.ny + 127) / 128), g_.nz + 2);
             const int rim = 2 * (g_.nx - 2) + 2 * std::max(0, g_.ny - 4) + g_.nx + g_.ny - 1;
@@ -931,7 +934,7 @@ public:
 
     lbm_status step(int nsteps) override
     {
-        const bool overlap = comm_ && cfg_.slab_count > 1 && (cfg_.kernel_variant == 0 || cfg_.kernel_variant == 65 || cfg_.kernel_variant == 66) && g_.nz >= 8;
+        const bool overlap = comm_ && cfg_.slab_count > 1 && (cfg_.kernel_variant == 0 || cfg_.kernel_variant == 65 || cfg_.kernel_variant == 66 || cfg_.kernel_variant == 67) && g_.nz >= 8;
         for (int t = 0; t < nsteps; t++) {
             if (overlap) {
                 LBM_TRY(step_overlapped(t == nsteps - 1));
