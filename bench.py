@@ -35,6 +35,7 @@ def parse():
     ap.add_argument("--nz-per-gpu", type=int, default=512)
     ap.add_argument("--variant", type=int, default=0, help="kernel_variant (0 default, 1 plain two-kernel path)")
     ap.add_argument("--e2e-steps", type=int, default=100, help="lattice steps per end-to-end segment (QuarterChannel NUMOUTPUT)")
+    ap.add_argument("--precision", default="f64", choices=["f64", "f32"], help="f32: liblbm_b200_f32.so, populations stored as float (not the parity build; the headline is f64)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
@@ -220,7 +221,8 @@ def ours(args, rank, world, local_rank):
         scaling = "weak"
     cfg = api.microchannel_config(which, nx, ny, nz, device=local_rank, slab_rank=rank, slab_count=world)
     cfg.kernel_variant = args.variant
-    ctx = api.Context(cfg)
+    ctx = api.Context(cfg, args.precision)
+    b_alg = B_ALG if args.precision == "f64" else B_ALG // 2     # populations stored as float: half the bytes per update
     z_begin, nz_local = ctx.slab_extent()
     nloc = ctx.local_nodes
     if world > 1:
@@ -229,7 +231,7 @@ def ours(args, rank, world, local_rank):
         ctx.comm_attach(uid[0])
 
     # pinned host buffers: initial fields in, result fields out (the e2e leg copies through them every segment)
-    L = api.load_library()
+    L = api.load_library(args.precision)
     import ctypes as C
     host = {}
     for name in ("rho", "phase", "ux", "uy", "uz"):
@@ -295,15 +297,15 @@ def ours(args, rank, world, local_rank):
         launches_per_step = prof[name]["launches"] / args.steps
         per_launch_ms = prof[name]["ms"] / prof[name]["launches"]
         peak, which_peak = peaks()
-        achieved = B_ALG * nloc / launches_per_step / (per_launch_ms * 1e-3) / 1e9
+        achieved = b_alg * nloc / launches_per_step / (per_launch_ms * 1e-3) / 1e9
         traffic = None
         tp = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tp):
             traffic = json.load(open(tp)).get(name, {}).get("dram_bytes_per_lattice_update")
             if traffic is not None:
-                traffic = traffic * nloc / launches_per_step
+                traffic = traffic * nloc / launches_per_step if args.precision == "f64" else None   # the ncu capture is of the fp64 build
         roof = {"bound": "hbm", "kernel": name, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": traffic, "peak_source": which_peak, "algorithmic_bytes_per_launch": B_ALG * nloc / launches_per_step,
+                "traffic": traffic, "peak_source": which_peak, "algorithmic_bytes_per_launch": b_alg * nloc / launches_per_step,
                 "launches_per_step": launches_per_step, "avg_launch_ms": per_launch_ms, "share_of_step": prof[name]["ms"] / sum(v["ms"] for v in prof.values()),
                 "kernels": prof}
 
@@ -348,8 +350,9 @@ def ours(args, rank, world, local_rank):
         line = {"metric": "MLUPS (aggregate), D3Q19 binary-liquid collide-stream, fp64", "value": value, "unit": "MLUPS",
                 "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_max / args.steps,
                 "higher_is_better": True, "scaling": scaling, "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-                "config": {"workload": wl, "nx": nx, "ny": ny, "nz": nz, "nodes": total_nodes, "precision": "fp64",
-                           "kernel_variant": args.variant, "l2": "inputs (%.1f GB of populations per GPU) exceed the 126 MB L2" % (nloc * 304 / 1e9),
+                "config": {"workload": wl, "nx": nx, "ny": ny, "nz": nz, "nodes": total_nodes,
+                           "precision": "fp64" if args.precision == "f64" else "fp32 storage of the populations, fp64 arithmetic and fields (not the parity build)",
+                           "kernel_variant": args.variant, "l2": "inputs (%.1f GB of populations per GPU) exceed the 126 MB L2" % (nloc * b_alg / 2 / 1e9),
                            "parallelism": "z-slab x%d" % world},
                 "mlups_per_gpu": value / world, "roofline": roof, "cpu_baseline": cb, "e2e": e2e, "clocks": clk,
                 "gpu_launches": launches}

@@ -53,6 +53,10 @@ typedef enum {
     LBM_ESTATE = 6   /* call made in the wrong order (e.g. step before init) */
 } lbm_status;
 
+/* Two builds export this ABI.  liblbm_b200.so is the fp64 library every parity statement refers to.
+ * liblbm_b200_f32.so holds LBM_BINARY_D3Q19 only and stores its populations as float in device memory
+ * (arithmetic and all fields stay double; host buffers stay double at every call): half the memory and
+ * traffic, results within the tolerance DESIGN.md section 3 states.  No reference counterpart. */
 typedef enum {
     LBM_SHANCHEN_D2Q9 = 0,     /* ShanChen/shanchen.cpp */
     LBM_BINARY_D2Q9 = 1,       /* FreeEnergy/binary.cpp */

@@ -39,23 +39,25 @@ class Config(C.Structure):
                 ("device", C.c_int), ("slab_rank", C.c_int), ("slab_count", C.c_int), ("kernel_variant", C.c_int)]
 
 
-_lib = None
+_LIB_F32 = os.path.join(_PKG, "liblbm_b200_f32.so")
+_libs = {}
 dp = C.POINTER(C.c_double)
 
 
-def library_path():
-    return _LIB
+def library_path(precision="f64"):
+    return _LIB_F32 if precision == "f32" else _LIB
 
 
-def load_library():
-    """Loads liblbm_b200.so; raises (never falls back) when it has not been built."""
-    global _lib
-    if _lib is not None:
-        return _lib
-    if not os.path.exists(_LIB):
-        raise ImportError("liblbm_b200.so is missing: build it with `python -m latticeboltzmannmethod_b200.build` "
-                          "(or __graft_entry__.build()); there is no CPU fallback")
-    L = C.CDLL(_LIB)
+def load_library(precision="f64"):
+    """Loads liblbm_b200.so (precision "f64", the parity build) or liblbm_b200_f32.so ("f32": same ABI, D3Q19 model
+    only, populations stored as float); raises (never falls back) when it has not been built."""
+    if precision in _libs:
+        return _libs[precision]
+    path = library_path(precision)
+    if not os.path.exists(path):
+        raise ImportError("%s is missing: build it with `python -m latticeboltzmannmethod_b200.build` "
+                          "(or __graft_entry__.build()); there is no CPU fallback" % os.path.basename(path))
+    L = C.CDLL(path)
     vp, sz, ci = C.c_void_p, C.c_size_t, C.c_int
     sig = {
         "lbm_config_default": (ci, [C.POINTER(Config), ci]),
@@ -94,7 +96,7 @@ def load_library():
     for name, (res, args) in sig.items():
         fn = getattr(L, name)          # AttributeError if the library does not export it
         fn.restype, fn.argtypes = res, args
-    _lib = L
+    _libs[precision] = L
     return L
 
 
@@ -123,8 +125,8 @@ def _ptr(a):
 class Context:
     """One lbm_ctx: one lattice model on one GPU (for the 3-D model: one z-slab)."""
 
-    def __init__(self, cfg):
-        self.L = load_library()
+    def __init__(self, cfg, precision="f64"):
+        self.L = load_library(precision)
         self.cfg = cfg
         h = C.c_void_p()
         st = self.L.lbm_create(C.byref(cfg), C.byref(h))

@@ -8,7 +8,9 @@
 #include <cstring>
 #include <vector>
 
-#include "d3q19_fused.cuh"
+#ifndef LBM_POP_FLOAT
+#include "d3q19_fused.cuh"   // the alternative kernels exist in the fp64 build only
+#endif
 #include "d3q19_threads.h"
 #include "lbm_internal.h"
 
@@ -21,16 +23,17 @@ using lbm3::Params;
 
 constexpr int kThreads = 256;
 
-__global__ void __launch_bounds__(kThreads) k_phase(Geom g, Params P, const double *gpop, double *phi, int zs0)
+__global__ void __launch_bounds__(kThreads) k_phase(Geom g, Params P, const pop_t *gpop, double *phi, int zs0)
 {
     const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= (long long)g.nx * g.ny) return;
     lbm3::phase_thread(g, P, gpop, phi, zs0 + blockIdx.y, (int)(idx % g.nx), (int)(idx / g.nx));
 }
 
+#ifndef LBM_POP_FLOAT   // alternative kernels: fp64 build only
 template <bool FXY, bool WRITE>
-__global__ void __launch_bounds__(kThreads) k_collide_push(Geom g, Params P, const double *fin, const double *gin,
-                                                            const double *phi, double *fout, double *gout, FieldsOut o,
+__global__ void __launch_bounds__(kThreads) k_collide_push(Geom g, Params P, const pop_t *fin, const pop_t *gin,
+                                                            const double *phi, pop_t *fout, pop_t *gout, FieldsOut o,
                                                             int zs0)
 {
     const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -40,8 +43,8 @@ __global__ void __launch_bounds__(kThreads) k_collide_push(Geom g, Params P, con
 }
 
 template <bool FXY, bool WRITE, int MINB>
-__global__ void __launch_bounds__(128, MINB) k_collide_push_occ(Geom g, Params P, const double *fin, const double *gin,
-                                                                const double *phi, double *fout, double *gout, FieldsOut o,
+__global__ void __launch_bounds__(128, MINB) k_collide_push_occ(Geom g, Params P, const pop_t *fin, const pop_t *gin,
+                                                                const double *phi, pop_t *fout, pop_t *gout, FieldsOut o,
                                                                 int zs0)
 {
     const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -50,14 +53,15 @@ __global__ void __launch_bounds__(128, MINB) k_collide_push_occ(Geom g, Params P
                                           (int)(idx / g.nx));
 }
 
+#endif  // LBM_POP_FLOAT
 // Interior / rim split of the plain collide-push.  The interior kernel contains no boundary code at all
 // (nodes 2..NX-3 x 2..NY-3: every push is a plain shifted store), which removes the control-flow merges
 // and register moves the folded boundary path costs every thread; the rim kernel runs the one-node rim
 // (and, on output steps, the wall-node fields) -- 2(NX+NY) nodes per plane.
 template <bool FXY, bool WRITE, int MINB, bool XRIM = false, bool TILE2D = false, int NT = 128>
-__global__ void __launch_bounds__(NT, MINB) k_collide_interior(Geom g, Params P, const double *__restrict__ fin,
-                                                                const double *__restrict__ gin, const double *__restrict__ phi,
-                                                                double *__restrict__ fout, double *__restrict__ gout, FieldsOut o,
+__global__ void __launch_bounds__(NT, MINB) k_collide_interior(Geom g, Params P, const pop_t *__restrict__ fin,
+                                                                const pop_t *__restrict__ gin, const double *__restrict__ phi,
+                                                                pop_t *__restrict__ fout, pop_t *__restrict__ gout, FieldsOut o,
                                                                 int zs0)
 {
     const int NX = g.nx, NY = g.ny;
@@ -83,7 +87,7 @@ __global__ void __launch_bounds__(NT, MINB) k_collide_interior(Geom g, Params P,
     if (iy < 2 || iy > NY - 3 || ix < (XRIM ? 1 : 2) || ix > NX - (XRIM ? 2 : 3)) return;
     const long long pl = g.pl;
     double F[19], G[19], PH[19];
-    const double *pf = fin + lbm3::pop_index(g, zs, 0, idx), *pg = gin + lbm3::pop_index(g, zs, 0, idx);
+    const pop_t *pf = fin + lbm3::pop_index(g, zs, 0, idx), *pg = gin + lbm3::pop_index(g, zs, 0, idx);
     constexpr int CX[19] = LBM3_CX, CY[19] = LBM3_CY, CZ[19] = LBM3_CZ;
 #pragma unroll
     for (int k = 0; k < 19; k++) {
@@ -95,9 +99,9 @@ __global__ void __launch_bounds__(NT, MINB) k_collide_interior(Geom g, Params P,
 }
 
 template <bool FXY, bool WRITE, bool ROWS_ONLY = false>
-__global__ void __launch_bounds__(128) k_collide_rim(Geom g, Params P, const double *__restrict__ fin,
-                                                     const double *__restrict__ gin, const double *__restrict__ phi,
-                                                     double *__restrict__ fout, double *__restrict__ gout, FieldsOut o, int zs0)
+__global__ void __launch_bounds__(128) k_collide_rim(Geom g, Params P, const pop_t *__restrict__ fin,
+                                                     const pop_t *__restrict__ gin, const double *__restrict__ phi,
+                                                     pop_t *__restrict__ fout, pop_t *__restrict__ gout, FieldsOut o, int zs0)
 {
     const int NX = g.nx, NY = g.ny, zs = zs0 + blockIdx.y;
     const int rows = 2 * (NX - 2), cols = ROWS_ONLY ? 0 : 2 * (NY - 4 > 0 ? NY - 4 : 0);
@@ -139,6 +143,7 @@ __global__ void __launch_bounds__(128) k_collide_rim(Geom g, Params P, const dou
     lbm3::collide_push_node_streamed<FXY, WRITE>(g, P, F, [Gp](int k) { return Gp[k]; }, PH, fout, gout, o, zs, ix, iy);
 }
 
+#ifndef LBM_POP_FLOAT   // alternative kernels: fp64 build only
 // Collide-push with every global load asynchronous and no block-wide barrier.
 //
 // ncu on k_collide_push (profiles/r01_collide_plain.*): 8 resident warps per SM (238 registers), top stall
@@ -150,9 +155,9 @@ __global__ void __launch_bounds__(128) k_collide_rim(Geom g, Params P, const dou
 // whole collision of the current one without holding registers; every thread only ever touches its own
 // slots, so there is no __syncthreads and warps drift freely.
 template <bool FXY, bool WRITE, int MINB>
-__global__ void __launch_bounds__(128, MINB) k_collide_async(Geom g, Params P, const double *__restrict__ fin,
-                                                             const double *__restrict__ gin, const double *__restrict__ phi,
-                                                             double *__restrict__ fout, double *__restrict__ gout, FieldsOut o,
+__global__ void __launch_bounds__(128, MINB) k_collide_async(Geom g, Params P, const pop_t *__restrict__ fin,
+                                                             const pop_t *__restrict__ gin, const double *__restrict__ phi,
+                                                             pop_t *__restrict__ fout, pop_t *__restrict__ gout, FieldsOut o,
                                                              int zs_begin, int zs_end, int chunk)
 {
     extern __shared__ __align__(16) double slots[];   // [57][128]
@@ -201,9 +206,9 @@ __global__ void __launch_bounds__(128, MINB) k_collide_async(Geom g, Params P, c
 
 // Plain collide-push through collide_streamed(): fewer live registers, more resident warps.
 template <bool FXY, bool WRITE, int MINB>
-__global__ void __launch_bounds__(128, MINB) k_collide_streamed(Geom g, Params P, const double *__restrict__ fin,
-                                                                const double *__restrict__ gin, const double *__restrict__ phi,
-                                                                double *__restrict__ fout, double *__restrict__ gout, FieldsOut o,
+__global__ void __launch_bounds__(128, MINB) k_collide_streamed(Geom g, Params P, const pop_t *__restrict__ fin,
+                                                                const pop_t *__restrict__ gin, const double *__restrict__ phi,
+                                                                pop_t *__restrict__ fout, pop_t *__restrict__ gout, FieldsOut o,
                                                                 int zs0)
 {
     const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -215,9 +220,9 @@ __global__ void __launch_bounds__(128, MINB) k_collide_streamed(Geom g, Params P
 // Plain collide-push with the f and the g populations of a node on two different threads: a block
 // of 256 threads updates 128 nodes, warps 0-3 hold f, warps 4-7 hold g (d3q19_threads.h, "split").
 template <bool FXY, bool WRITE, int MINB>
-__global__ void __launch_bounds__(256, MINB) k_collide_split(Geom g, Params P, const double *__restrict__ fin,
-                                                             const double *__restrict__ gin, const double *__restrict__ phi,
-                                                             double *__restrict__ fout, double *__restrict__ gout, FieldsOut o,
+__global__ void __launch_bounds__(256, MINB) k_collide_split(Geom g, Params P, const pop_t *__restrict__ fin,
+                                                             const pop_t *__restrict__ gin, const double *__restrict__ phi,
+                                                             pop_t *__restrict__ fout, pop_t *__restrict__ gout, FieldsOut o,
                                                              int zs0)
 {
     __shared__ double xch[8][128];
@@ -265,6 +270,7 @@ __global__ void __launch_bounds__(256, MINB) k_collide_split(Geom g, Params P, c
     }
 }
 
+#endif  // LBM_POP_FLOAT
 __global__ void k_init_fields(Geom g, Params P, double *phi, double *rho)
 {
     const int z = blockIdx.x * blockDim.x + threadIdx.x;
@@ -273,28 +279,28 @@ __global__ void k_init_fields(Geom g, Params P, double *phi, double *rho)
 
 __global__ void __launch_bounds__(kThreads) k_init_pops(Geom g, Params P, const double *phi, const double *rho,
                                                          const double *ux, const double *uy, const double *uz,
-                                                         double *fout, double *gout)
+                                                         pop_t *fout, pop_t *gout)
 {
     const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= (long long)g.nx * g.ny) return;
     lbm3::init_pops_thread(g, P, phi, rho, ux, uy, uz, fout, gout, blockIdx.y, (int)(idx % g.nx), (int)(idx / g.nx));
 }
 
-__global__ void __launch_bounds__(kThreads) k_after_init(Geom g, Params P, const double *fin, FieldsOut o)
+__global__ void __launch_bounds__(kThreads) k_after_init(Geom g, Params P, const pop_t *fin, FieldsOut o)
 {
     const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= (long long)g.nx * g.ny) return;
     lbm3::after_init_thread(g, P, fin, o, blockIdx.y, (int)(idx % g.nx), (int)(idx / g.nx));
 }
 
-__global__ void __launch_bounds__(kThreads) k_gather_aos(Geom g, const double *pop, double *aos)
+__global__ void __launch_bounds__(kThreads) k_gather_aos(Geom g, const pop_t *pop, double *aos)
 {
     const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= (long long)g.nx * g.ny) return;
     lbm3::gather_aos_thread(g, pop, aos, blockIdx.y, (int)(idx % g.nx), (int)(idx / g.nx));
 }
 
-__global__ void __launch_bounds__(kThreads) k_scatter_aos(Geom g, const double *aos, double *pop)
+__global__ void __launch_bounds__(kThreads) k_scatter_aos(Geom g, const double *aos, pop_t *pop)
 {
     const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= (long long)g.nx * g.ny) return;
@@ -316,6 +322,7 @@ struct NcclApi {
     const char *(*GetErrorString)(int) = nullptr;
 };
 constexpr int kNcclFloat64 = 8;  // ncclDouble
+constexpr int kNcclFloat32 = 7;  // ncclFloat
 
 NcclApi *nccl_api(std::string *why)
 {
@@ -370,7 +377,7 @@ public:
         P_.phase_gradient = cfg_.wall_gradient; P_.rho_wall = cfg_.rho_wall;
         fxy_ = P_.fx != 0.0 || P_.fy != 0.0;
 
-        const size_t pop_bytes = (size_t)(g_.nz + 4) * 19 * g_.pl * sizeof(double);
+        const size_t pop_bytes = (size_t)(g_.nz + 4) * 19 * g_.pl * sizeof(pop_t);
         for (int b = 0; b < 2; b++) {
             LBM_CUDA(rt_, cudaMalloc(&f_[b], pop_bytes));
             LBM_CUDA(rt_, cudaMalloc(&gq_[b], pop_bytes));
@@ -460,6 +467,7 @@ public:
         k_after_init<<<plane_grid(g_.nz), kThreads, 0, rt_.stream>>>(g_, P_, f_[cur_], fields_out());
         return rt_.launched("k_after_init");
     }
+#ifndef LBM_POP_FLOAT   // alternative kernels: fp64 build only
     // kernel_variant 0: the whole step as one kernel (d3q19_fused.cuh)
     template <int TY>
     lbm_status launch_fused(int write_fields)
@@ -557,6 +565,7 @@ public:
         return rt_.launched("k_collide_rim");
     }
 
+#endif  // LBM_POP_FLOAT
     // default collide: interior incl. the x columns (168 registers, 12 warps/SM) + rim rows, for `count`
     // storage planes starting at zs0; the phase field of planes zs0-1 .. zs0+count must be up to date
     lbm_status collide_default(int zs0, int count, int write_fields)
@@ -593,6 +602,7 @@ public:
         return rt_.launched("k_collide_rim");
     }
 
+#ifndef LBM_POP_FLOAT   // alternative kernels: fp64 build only
     // fused interior (phase pulled in, x columns folded) + rim rows
     template <int TY, int MINB>
     lbm_status launch_fused6(int write_fields)
@@ -628,8 +638,18 @@ public:
         return rt_.launched("k_collide_rim");
     }
 
+#endif  // LBM_POP_FLOAT
     lbm_status slab_collide(int write_fields) override
     {
+#ifdef LBM_POP_FLOAT
+        // fp32-storage build: the default path and its block-shape variants only
+        if (cfg_.kernel_variant != 0 && cfg_.kernel_variant != 65 && cfg_.kernel_variant != 66 && cfg_.kernel_variant != 67)
+            return rt_.fail(LBM_EINVAL, "this kernel_variant exists in the fp64 build only");
+        rt_.about_to_launch();
+        k_phase<<<plane_grid(g_.nz + 4), kThreads, 0, rt_.stream>>>(g_, P_, gq_[cur_], phi_, 0);
+        LBM_TRY(rt_.launched("k_phase"));
+        return collide_default(1, g_.nz + 2, write_fields);
+#else
         switch (cfg_.kernel_variant) {
         case 70: return launch_fused3<4, 3, 3>(write_fields);
         case 71: return launch_fused3<4, 2, 3>(write_fields);
@@ -805,6 +825,7 @@ public:
         }
 #undef LBM_LAUNCH_COLLIDE
         return rt_.launched("k_collide_push");
+#endif
     }
     lbm_status slab_finish() override
     {
@@ -816,9 +837,9 @@ public:
     {
         const int b = 1 - cur_;
         const size_t pp = 19 * (size_t)g_.pl;
-        auto at = [&](double *arr, int z) { return arr + (size_t)(z + 2) * pp; };
+        auto at = [&](pop_t *arr, int z) { return arr + (size_t)(z + 2) * pp; };
         const int nz = g_.nz;
-        double *p = nullptr;
+        void *p = nullptr;   // population messages are pop_t (double; float in the fp32-storage build), phase messages double
         size_t n = 0;
         switch (id) {
         case LBM_HALO_S_F_UP: p = at(f_[b], nz - 1); n = pp; break;
@@ -855,7 +876,7 @@ public:
                 size_t ns, nr;
                 LBM_TRY(slab_halo(pairs[i][0], &s, &ns));
                 LBM_TRY(slab_halo(pairs[i][1], &r, &nr));
-                LBM_CUDA(rt_, cudaMemcpyAsync(r, s, ns * sizeof(double), cudaMemcpyDeviceToDevice, st));
+                LBM_CUDA(rt_, cudaMemcpyAsync(r, s, ns * (phi_only ? sizeof(double) : sizeof(pop_t)), cudaMemcpyDeviceToDevice, st));
             }
             return LBM_OK;
         }
@@ -863,6 +884,7 @@ public:
         NcclApi *api = nccl_api(&rt_.err);
         if (!api) return LBM_ENCCL;
         const int up = (cfg_.slab_rank + 1) % cfg_.slab_count, down = (cfg_.slab_rank - 1 + cfg_.slab_count) % cfg_.slab_count;
+        const int dtype = (phi_only || sizeof(pop_t) == sizeof(double)) ? kNcclFloat64 : kNcclFloat32;
         int rc = api->GroupStart();
         // sends in the order [up..., down...], receives [from below..., from above...]: with two
         // slabs both neighbours are the same peer and NCCL matches a pair's messages in order
@@ -871,14 +893,14 @@ public:
             size_t ns;
             LBM_TRY(slab_halo(pairs[i][0], &s, &ns));
             const bool to_up = i < npairs / 2;
-            rc = api->Send(s, ns, kNcclFloat64, to_up ? up : down, comm_, st);
+            rc = api->Send(s, ns, dtype, to_up ? up : down, comm_, st);
         }
         for (int i = 0; i < npairs && rc == 0; i++) {
             void *r;
             size_t nr;
             LBM_TRY(slab_halo(pairs[i][1], &r, &nr));
             const bool from_below = i < npairs / 2;
-            rc = api->Recv(r, nr, kNcclFloat64, from_below ? down : up, comm_, st);
+            rc = api->Recv(r, nr, dtype, from_below ? down : up, comm_, st);
         }
         const int rc2 = api->GroupEnd();
         if (rc == 0) rc = rc2;
@@ -954,7 +976,7 @@ public:
         LBM_CUDA(rt_, cudaMalloc(&stage, n * sizeof(double)));
         lbm_status st = rt_.cuda(cudaMemcpyAsync(stage, host, n * sizeof(double), cudaMemcpyHostToDevice, rt_.stream), "H2D populations");
         if (st == LBM_OK) {
-            double *dst = set == 0 ? f_[cur_] : gq_[cur_];
+            pop_t *dst = set == 0 ? f_[cur_] : gq_[cur_];
             k_scatter_aos<<<plane_grid(g_.nz), kThreads, 0, rt_.stream>>>(g_, stage, dst);
             st = rt_.launched("k_scatter_aos");
         }
@@ -1006,7 +1028,7 @@ private:
     Params P_{};
     bool fxy_ = false;
     int z_begin_ = 0, cur_ = 0;
-    double *f_[2] = {nullptr, nullptr}, *gq_[2] = {nullptr, nullptr};
+    pop_t *f_[2] = {nullptr, nullptr}, *gq_[2] = {nullptr, nullptr};
     double *phi_ = nullptr, *rho_ = nullptr, *ux_ = nullptr, *uy_ = nullptr, *uz_ = nullptr, *diag_ = nullptr;
     void *comm_ = nullptr;
     cudaStream_t side_ = nullptr;

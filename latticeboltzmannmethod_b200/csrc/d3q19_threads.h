@@ -20,6 +20,7 @@
 #define LBM_D3Q19_THREADS_H
 
 #include "d3q19_node.h"
+#include "lbm_pop.h"
 
 namespace lbm3 {
 
@@ -35,7 +36,7 @@ LBM_HD long long pop_index(const Geom &g, int zs, int k, long long idx) { return
 // the permuted copy), :75-106 (wall nodes: inner neighbour - phase_gradient).
 // The thread of bulk node (ix,iy) also writes the mirror/wall nodes whose inner
 // neighbour it is, so no second pass is needed.
-LBM_HD void phase_thread(const Geom &g, const Params &P, const double *gpop, double *phi, int zs, int ix, int iy)
+LBM_HD void phase_thread(const Geom &g, const Params &P, const pop_t *gpop, double *phi, int zs, int ix, int iy)
 {
     const int NX = g.nx, NY = g.ny;
     if (ix < 1 || ix > NX - 2 || iy < 1 || iy > NY - 2) return;
@@ -71,7 +72,7 @@ LBM_HD void phase_thread(const Geom &g, const Params &P, const double *gpop, dou
 // velocity component flips, the node coordinate stays on the inner line).
 // (Inlined on purpose: as a __noinline__ call it forces the population arrays of every thread into
 // local memory -- measured 2x slower.)
-LBM_HD void push_border(const Geom &g, double *fout, double *gout, int zs, int ix, int iy, int k, double fv, double gv)
+LBM_HD void push_border(const Geom &g, pop_t *fout, pop_t *gout, int zs, int ix, int iy, int k, double fv, double gv)
 {
     const int CX[19] = LBM3_CX, CY[19] = LBM3_CY, CZ[19] = LBM3_CZ;
     const int OPP[19] = {0, 2, 1, 4, 3, 6, 5, 10, 9, 8, 7, 14, 13, 12, 11, 18, 17, 16, 15};
@@ -119,8 +120,8 @@ LBM_HD void mirror_fields(const double *F, const Params &P, const FieldsOut &o, 
 // the x wall (iX = NX-2) are folded in as an address select on the ten directions with cx != 0, so that
 // these two columns are stored by the same coalesced warps as their row neighbours.
 template <bool FXY, bool WRITE, int PART = 0>
-LBM_HD void collide_push_node(const Geom &g, const Params &P, double *F, double *G, const double *PH, double *fout,
-                              double *gout, const FieldsOut &o, int zs, int ix, int iy)
+LBM_HD void collide_push_node(const Geom &g, const Params &P, double *F, double *G, const double *PH, pop_t *fout,
+                              pop_t *gout, const FieldsOut &o, int zs, int ix, int iy)
 {
     const int NX = g.nx, NY = g.ny;
     const long long idx = (long long)iy * NX + ix;
@@ -168,8 +169,8 @@ LBM_HD void collide_push_node(const Geom &g, const Params &P, double *F, double 
 // 377-688) for this node.  `phi` must already hold the extended phase field of
 // planes zs-1..zs+1.
 template <bool FXY, bool WRITE>
-LBM_HD void collide_push_thread(const Geom &g, const Params &P, const double *fin, const double *gin,
-                                const double *phi, double *fout, double *gout, const FieldsOut &o, int zs, int ix, int iy)
+LBM_HD void collide_push_thread(const Geom &g, const Params &P, const pop_t *fin, const pop_t *gin,
+                                const double *phi, pop_t *fout, pop_t *gout, const FieldsOut &o, int zs, int ix, int iy)
 {
     const int NX = g.nx, NY = g.ny;
     if (ix < 1 || ix > NX - 2 || iy < 1 || iy > NY - 2) {
@@ -198,8 +199,8 @@ LBM_HD void collide_push_thread(const Geom &g, const Params &P, const double *fi
 // the default kernel pair as one per-node function (CPU unit test): rows iY = 1 and NY-2 take the rim
 // path, every other bulk node the PART 3 path of k_collide_interior
 template <bool FXY, bool WRITE>
-LBM_HD void collide_push_thread_rows(const Geom &g, const Params &P, const double *fin, const double *gin,
-                                     const double *phi, double *fout, double *gout, const FieldsOut &o, int zs, int ix, int iy)
+LBM_HD void collide_push_thread_rows(const Geom &g, const Params &P, const pop_t *fin, const pop_t *gin,
+                                     const double *phi, pop_t *fout, pop_t *gout, const FieldsOut &o, int zs, int ix, int iy)
 {
     const int NX = g.nx, NY = g.ny;
     if (ix < 1 || ix > NX - 2 || iy < 1 || iy > NY - 2) {
@@ -225,7 +226,7 @@ LBM_HD void collide_push_thread_rows(const Geom &g, const Params &P, const doubl
 // Push functor: stores one post-collision pair as soon as it exists.
 struct PushInterior {
     const Geom &g;
-    double *fo, *go;     // fout/gout + pop_index(zs, 0, idx)
+    pop_t *fo, *go;     // fout/gout + pop_index(zs, 0, idx)
     template <int K>
     LBM_HD void operator()(double fv, double gv) const
     {
@@ -242,7 +243,7 @@ struct PushInterior {
 };
 struct PushBorder {
     const Geom &g;
-    double *fout, *gout;
+    pop_t *fout, *gout;
     int zs, ix, iy;
     template <int K>
     LBM_HD void operator()(double fv, double gv) const { push_border(g, fout, gout, zs, ix, iy, K, fv, gv); }
@@ -251,8 +252,8 @@ struct PushBorder {
 // One bulk node whose f populations are in registers (F), whose g populations come from `getG`
 // and whose 19 neighbour phase values are in PH.  Same reference lines as collide_push_thread.
 template <bool FXY, bool WRITE, int PART = 0, class GetG>
-LBM_HD void collide_push_node_streamed(const Geom &g, const Params &P, double *F, GetG getG, const double *PH, double *fout,
-                                       double *gout, const FieldsOut &o, int zs, int ix, int iy)
+LBM_HD void collide_push_node_streamed(const Geom &g, const Params &P, double *F, GetG getG, const double *PH, pop_t *fout,
+                                       pop_t *gout, const FieldsOut &o, int zs, int ix, int iy)
 {
     const int NX = g.nx, NY = g.ny;
     const long long idx = (long long)iy * NX + ix;
@@ -280,8 +281,8 @@ LBM_HD void collide_push_node_streamed(const Geom &g, const Params &P, double *F
 
 // plain-kernel flavour of the above (used by the CPU unit test to pin collide_streamed against collide)
 template <bool FXY, bool WRITE>
-LBM_HD void collide_push_thread_streamed(const Geom &g, const Params &P, const double *fin, const double *gin,
-                                         const double *phi, double *fout, double *gout, const FieldsOut &o, int zs, int ix, int iy)
+LBM_HD void collide_push_thread_streamed(const Geom &g, const Params &P, const pop_t *fin, const pop_t *gin,
+                                         const double *phi, pop_t *fout, pop_t *gout, const FieldsOut &o, int zs, int ix, int iy)
 {
     const int NX = g.nx, NY = g.ny;
     if (ix < 1 || ix > NX - 2 || iy < 1 || iy > NY - 2) {
@@ -298,7 +299,7 @@ LBM_HD void collide_push_thread_streamed(const Geom &g, const Params &P, const d
         F[k] = fin[pop_index(g, zs, k, idx)];
         PH[k] = phi[(long long)(zs + CZ[k]) * g.pl + idx + CY[k] * NX + CX[k]];
     }
-    const double *gp = gin + pop_index(g, zs, 0, idx);
+    const pop_t *gp = gin + pop_index(g, zs, 0, idx);
     const long long pl = g.pl;
     collide_push_node_streamed<FXY, WRITE>(g, P, F, [gp, pl](int k) { return gp[(long long)k * pl]; }, PH, fout, gout, o, zs, ix, iy);
 }
@@ -307,7 +308,7 @@ LBM_HD void collide_push_thread_streamed(const Geom &g, const Params &P, const d
 // Single-set push functors (same folding of mirror / bounce-back as push_border).
 struct PushOneInterior {
     const Geom &g;
-    double *po;          // out array + pop_index(zs, 0, idx)
+    pop_t *po;          // out array + pop_index(zs, 0, idx)
     template <int K>
     LBM_HD void operator()(double v) const
     {
@@ -315,7 +316,7 @@ struct PushOneInterior {
         po[(long long)(CZ[K] * 19 + K) * g.pl + (CY[K] * g.nx + CX[K])] = v;
     }
 };
-LBM_HD void push_border_one(const Geom &g, double *out, int zs, int ix, int iy, int k, double v)
+LBM_HD void push_border_one(const Geom &g, pop_t *out, int zs, int ix, int iy, int k, double v)
 {
     const int CX[19] = LBM3_CX, CY[19] = LBM3_CY, CZ[19] = LBM3_CZ;
     const int OPP[19] = {0, 2, 1, 4, 3, 6, 5, 10, 9, 8, 7, 14, 13, 12, 11, 18, 17, 16, 15};
@@ -332,7 +333,7 @@ LBM_HD void push_border_one(const Geom &g, double *out, int zs, int ix, int iy, 
 }
 struct PushOneBorder {
     const Geom &g;
-    double *out;
+    pop_t *out;
     int zs, ix, iy;
     template <int K>
     LBM_HD void operator()(double v) const { push_border_one(g, out, zs, ix, iy, K, v); }
@@ -341,7 +342,7 @@ struct PushOneBorder {
 // f thread of a bulk node, after the exchange: F in registers, phase data received from the g thread
 template <bool FXY, bool WRITE>
 LBM_HD void f_thread_finish(const Geom &g, const Params &P, const double *F, double ph, double gx, double gy, double gz,
-                            double lap, double rho, double ux, double uy, double uz, double *fout, const FieldsOut &o, int zs,
+                            double lap, double rho, double ux, double uy, double uz, pop_t *fout, const FieldsOut &o, int zs,
                             int ix, int iy)
 {
     const int NX = g.nx, NY = g.ny;
@@ -363,7 +364,7 @@ LBM_HD void f_thread_finish(const Geom &g, const Params &P, const double *F, dou
 
 // g thread of a bulk node, after the exchange: G in registers, velocity received from the f thread
 LBM_HD void g_thread_finish(const Geom &g, const Params &P, const double *G, double ph, double lap, double ux, double uy,
-                            double uz, double *gout, int zs, int ix, int iy)
+                            double uz, pop_t *gout, int zs, int ix, int iy)
 {
     const int NX = g.nx, NY = g.ny;
     const long long idx = (long long)iy * NX + ix;
@@ -376,8 +377,8 @@ LBM_HD void g_thread_finish(const Geom &g, const Params &P, const double *G, dou
 
 // both halves on one thread (CPU unit test: pins the split against collide())
 template <bool FXY, bool WRITE>
-LBM_HD void collide_push_thread_split(const Geom &g, const Params &P, const double *fin, const double *gin, const double *phi,
-                                      double *fout, double *gout, const FieldsOut &o, int zs, int ix, int iy)
+LBM_HD void collide_push_thread_split(const Geom &g, const Params &P, const pop_t *fin, const pop_t *gin, const double *phi,
+                                      pop_t *fout, pop_t *gout, const FieldsOut &o, int zs, int ix, int iy)
 {
     const int NX = g.nx, NY = g.ny;
     if (ix < 1 || ix > NX - 2 || iy < 1 || iy > NY - 2) {
@@ -425,7 +426,7 @@ LBM_HD void init_fields_plane(const Geom &g, const Params &P, double *phi, doubl
 
 // Lattice::init for one bulk node (lattice.hpp:216-276); fields [z][in-plane]
 LBM_HD void init_pops_thread(const Geom &g, const Params &P, const double *phi, const double *rho, const double *ux,
-                             const double *uy, const double *uz, double *fout, double *gout, int z, int ix, int iy)
+                             const double *uy, const double *uz, pop_t *fout, pop_t *gout, int z, int ix, int iy)
 {
     const int NX = g.nx, NY = g.ny;
     if (ix < 1 || ix > NX - 2 || iy < 1 || iy > NY - 2) return;
@@ -444,7 +445,7 @@ LBM_HD void init_pops_thread(const Geom &g, const Params &P, const double *phi, 
 }
 
 // updateMacro right after init (solver.hpp:877): moments without the force shift
-LBM_HD void after_init_thread(const Geom &g, const Params &P, const double *fin, const FieldsOut &o, int z, int ix, int iy)
+LBM_HD void after_init_thread(const Geom &g, const Params &P, const pop_t *fin, const FieldsOut &o, int z, int ix, int iy)
 {
     const int NX = g.nx, NY = g.ny;
     if (ix >= NX || iy >= NY) return;
@@ -478,7 +479,7 @@ LBM_HD void after_init_thread(const Geom &g, const Params &P, const double *fin,
 
 // populations in the reference's AoS order for one node of plane z (any node):
 // mirror nodes get the permuted copy, wall nodes zero
-LBM_HD void gather_aos_thread(const Geom &g, const double *pop, double *aos, int z, int ix, int iy)
+LBM_HD void gather_aos_thread(const Geom &g, const pop_t *pop, double *aos, int z, int ix, int iy)
 {
     const int NX = g.nx, NY = g.ny;
     if (ix >= NX || iy >= NY) return;
@@ -497,7 +498,7 @@ LBM_HD void gather_aos_thread(const Geom &g, const double *pop, double *aos, int
     for (int k = 0; k < 19; k++) out[k] = pop[pop_index(g, z + 2, SYM[m][k], idx)];
 }
 
-LBM_HD void scatter_aos_thread(const Geom &g, const double *aos, double *pop, int z, int ix, int iy)
+LBM_HD void scatter_aos_thread(const Geom &g, const double *aos, pop_t *pop, int z, int ix, int iy)
 {
     const int NX = g.nx, NY = g.ny;
     if (ix < 1 || ix > NX - 2 || iy < 1 || iy > NY - 2) return;

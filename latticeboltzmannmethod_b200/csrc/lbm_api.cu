@@ -93,13 +93,20 @@ lbm_status lbm_create(const lbm_config *cfg, lbm_ctx **out)
     }
     if (st == LBM_OK) {
         switch (cfg->model) {
+#ifndef LBM_POP_FLOAT
         case LBM_SHANCHEN_D2Q9: ctx->model = lbm::make_d2q9_shanchen(ctx->rt, ctx->cfg, &st); break;
         case LBM_BINARY_D2Q9: ctx->model = lbm::make_d2q9_binary(ctx->rt, ctx->cfg, &st); break;
         case LBM_MRT_GS_D2Q9:
         case LBM_MRT_HERMITE_D2Q9: ctx->model = lbm::make_d2q9_mrt(ctx->rt, ctx->cfg, &st); break;
-        case LBM_BINARY_D3Q19: ctx->model = lbm::make_d3q19_binary(ctx->rt, ctx->cfg, &st); break;
         case LBM_TRT_DIFFUSION_D2Q9: ctx->model = lbm::make_d2q9_trt(ctx->rt, ctx->cfg, &st); break;
         case LBM_BINARY_SHAPE_D2Q9: ctx->model = lbm::make_d2q9_binary_shape(ctx->rt, ctx->cfg, &st); break;
+#else
+        case LBM_SHANCHEN_D2Q9: case LBM_BINARY_D2Q9: case LBM_MRT_GS_D2Q9: case LBM_MRT_HERMITE_D2Q9:
+        case LBM_TRT_DIFFUSION_D2Q9: case LBM_BINARY_SHAPE_D2Q9:
+            st = ctx->rt.fail(LBM_EINVAL, "liblbm_b200_f32.so holds the D3Q19 model only; the D2Q9 models are in liblbm_b200.so");
+            break;
+#endif
+        case LBM_BINARY_D3Q19: ctx->model = lbm::make_d3q19_binary(ctx->rt, ctx->cfg, &st); break;
         default: st = ctx->rt.fail(LBM_EINVAL, "unknown model");
         }
     }

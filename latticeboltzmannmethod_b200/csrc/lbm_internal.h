@@ -9,6 +9,7 @@
 #include <vector>
 
 #include "lbm_b200.h"
+#include "lbm_pop.h"
 
 namespace lbm {
 
@@ -122,7 +123,7 @@ Model *make_d2q9_binary_shape(Runtime &rt, const lbm_config &cfg, lbm_status *st
 // planes `plane_stride` apart (2-D models: planes = 1); `nx,ny` + `skip_border`
 // exclude mirror/wall nodes of the 3-D model.
 struct DiagLayout {
-    const double *f, *g;      // g may be null
+    const pop_t *f, *g;       // g may be null (pop_t: double; float only for D3Q19 in the fp32-storage build)
     long long stride_k;       // doubles between consecutive directions
     long long plane_stride;   // doubles between consecutive planes (of direction 0)
     int planes, nx, ny, q;
