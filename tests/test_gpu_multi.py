@@ -38,7 +38,7 @@ def _cfg(api, rank, world):
     return cfg
 
 
-def _worker(rank, world, port, out_dir, transport):
+def _worker(rank, world, port, out_dir, transport, precision="f64"):
     import torch
     import torch.distributed as dist
     from latticeboltzmannmethod_b200 import api
@@ -47,7 +47,7 @@ def _worker(rank, world, port, out_dir, transport):
     os.environ["MASTER_PORT"] = str(port)
     torch.cuda.set_device(rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
-    ctx = api.Context(_cfg(api, rank, world))
+    ctx = api.Context(_cfg(api, rank, world), precision)
     z0, nzl = ctx.slab_extent()
     pl = NX * NY
     for name, a in zip(F3, _fields()):
@@ -83,14 +83,15 @@ def _free_port():
 
 
 @pytest.mark.skipif(_ngpu() < 2, reason="needs at least 2 GPUs")
-@pytest.mark.parametrize("transport", ["nccl", "torch"])
-def test_slab_ring_on_gpus_equals_one_gpu(transport, tmp_path):
+@pytest.mark.parametrize("transport,precision", [("nccl", "f64"), ("torch", "f64"), ("nccl", "f32")])
+def test_slab_ring_on_gpus_equals_one_gpu(transport, precision, tmp_path):
+    """f32: the fp32-storage build sends float halo messages; its slab ring must equal its own one-GPU run."""
     import torch.multiprocessing as mp
     import oracle_lib as ol
     from latticeboltzmannmethod_b200 import api
     world = min(_ngpu(), 4)
-    mp.spawn(_worker, args=(world, _free_port(), str(tmp_path), transport), nprocs=world, join=True)
-    ctx = api.Context(_cfg(api, 0, 1))
+    mp.spawn(_worker, args=(world, _free_port(), str(tmp_path), transport, precision), nprocs=world, join=True)
+    ctx = api.Context(_cfg(api, 0, 1), precision)
     for name, a in zip(F3, _fields()):
         ctx.set_field(name, a)
     ctx.init()
