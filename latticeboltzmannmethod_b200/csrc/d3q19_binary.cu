@@ -144,6 +144,32 @@ __global__ void __launch_bounds__(128) k_collide_rim(Geom g, Params P, const pop
 }
 
 #ifndef LBM_POP_FLOAT   // alternative kernels: fp64 build only
+// The interior kernel with g fetched where the collision consumes it (collide_streamed): f and the phase stencil
+// are loaded up front, each g_k only when its post-collision value is formed and stored, so the 19 g registers
+// are never live together.  Nodes 2..NX-3 x 2..NY-3 (PART 1); the one-node rim incl. the columns goes to k_collide_rim.
+template <bool FXY, bool WRITE, int MINB>
+__global__ void __launch_bounds__(128, MINB) k_collide_interior_sg(Geom g, Params P, const pop_t *__restrict__ fin,
+                                                                   const pop_t *__restrict__ gin, const double *__restrict__ phi,
+                                                                   pop_t *__restrict__ fout, pop_t *__restrict__ gout, FieldsOut o,
+                                                                   int zs0)
+{
+    const long long idx = (long long)blockIdx.x * 128 + threadIdx.x;
+    const int NX = g.nx, NY = g.ny;
+    if (idx >= (long long)NX * NY) return;
+    const int ix = (int)(idx % NX), iy = (int)(idx / NX), zs = zs0 + blockIdx.y;
+    if (iy < 2 || iy > NY - 3 || ix < 2 || ix > NX - 3) return;
+    const long long pl = g.pl;
+    double F[19], PH[19];
+    const pop_t *pf = fin + lbm3::pop_index(g, zs, 0, idx), *pg = gin + lbm3::pop_index(g, zs, 0, idx);
+    constexpr int CX[19] = LBM3_CX, CY[19] = LBM3_CY, CZ[19] = LBM3_CZ;
+#pragma unroll
+    for (int k = 0; k < 19; k++) {
+        F[k] = __ldg(pf + k * pl);
+        PH[k] = __ldg(phi + (long long)(zs + CZ[k]) * pl + idx + CY[k] * NX + CX[k]);
+    }
+    lbm3::collide_push_node_streamed<FXY, WRITE, 1>(g, P, F, [pg, pl](int k) { return __ldg(pg + k * pl); }, PH, fout, gout, o, zs, ix, iy);
+}
+
 // Collide-push with every global load asynchronous and no block-wide barrier.
 //
 // ncu on k_collide_push (profiles/r01_collide_plain.*): 8 resident warps per SM (238 registers), top stall
@@ -716,6 +742,28 @@ public:
             return LBM_OK;
         }
         if (cfg_.kernel_variant == 0 || cfg_.kernel_variant == 65 || cfg_.kernel_variant == 66 || cfg_.kernel_variant == 67) return collide_default(1, g_.nz + 2, write_fields);
+        if (cfg_.kernel_variant == 68 || cfg_.kernel_variant == 69) {
+            const dim3 gi((unsigned)(((long long)g_.nx * g_.ny + 127) / 128), g_.nz + 2);
+            const int rim = 2 * (g_.nx - 2) + 2 * std::max(0, g_.ny - 4) + g_.nx + g_.ny - 1;
+            const dim3 gr((rim + 127) / 128, g_.nz + 2);
+#define LBM_LAUNCH_SG(FXY, WR)                                                                                                  \
+    do {                                                                                                                        \
+        if (cfg_.kernel_variant == 68)                                                                                          \
+            k_collide_interior_sg<FXY, WR, 4><<<gi, 128, 0, rt_.stream>>>(g_, P_, f_[a], gq_[a], phi_, f_[b], gq_[b], o, 1);     \
+        else                                                                                                                    \
+            k_collide_interior_sg<FXY, WR, 3><<<gi, 128, 0, rt_.stream>>>(g_, P_, f_[a], gq_[a], phi_, f_[b], gq_[b], o, 1);     \
+        LBM_TRY(rt_.launched("k_collide_interior_sg"));                                                                         \
+        rt_.about_to_launch();                                                                                                  \
+        k_collide_rim<FXY, WR><<<gr, 128, 0, rt_.stream>>>(g_, P_, f_[a], gq_[a], phi_, f_[b], gq_[b], o, 1);                    \
+    } while (0)
+            if (fxy_) {
+                if (write_fields) LBM_LAUNCH_SG(true, true); else LBM_LAUNCH_SG(true, false);
+            } else {
+                if (write_fields) LBM_LAUNCH_SG(false, true); else LBM_LAUNCH_SG(false, false);
+            }
+#undef LBM_LAUNCH_SG
+            return rt_.launched("k_collide_rim");
+        }
         if (cfg_.kernel_variant >= 60 && cfg_.kernel_variant <= 62) {
             const dim3 gi((unsigned)(((long long)g_.nx * g_.ny + 127) / 128), g_.nz + 2);
             const int rim = 2 * (g_.nx - 2) + 2 * std::max(0, g_.ny - 4) + g_.nx + g_.ny - 1;
