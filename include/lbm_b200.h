@@ -84,8 +84,11 @@ typedef struct {
     double ce, conc_wall;      /* cylinder.cpp:43,33; the TRT rates are omega_minus = omega, omega_plus = 2 - omega (:38-40) */
     int device;                /* CUDA device ordinal */
     int slab_rank, slab_count; /* z-slab decomposition (3-D only): this context owns slab `rank` of `count` */
-    int kernel_variant;        /* 0 = default (fastest measured); other values select the alternative D3Q19 kernels
-                                  kept for cross-checks and measurements, see DESIGN.md section 6 */
+    int kernel_variant;        /* 0 = default (fastest measured).  Other values select alternative kernels of the same
+                                  model, kept for cross-checks and measurements and held to the same parity tests:
+                                  D3Q19 see DESIGN.md section 6; Shan-Chen 1 = density pass + collide, 2/3/5 = other
+                                  tiles of the fused kernel; binary D2Q9 1 = 256-thread blocks, 2-4 = fused tile
+                                  kernel; curved solid 1/2 = other block shapes.  Results never depend on it. */
 } lbm_config;
 
 /* Fills *cfg with the constants of the reference program for `model`
