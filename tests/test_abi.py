@@ -17,13 +17,15 @@ def _declared():
     return sorted(set(re.findall(r"\b(lbm_[a-z0-9_]+)\s*\(", txt)))
 
 
-def test_library_exports_every_declared_symbol():
+@pytest.mark.parametrize("precision", ["f64", "f32"])
+def test_library_exports_every_declared_symbol(precision):
+    """Both builds (fp64, and the fp32-storage D3Q19 build) export the whole ABI."""
     from latticeboltzmannmethod_b200 import api
-    L = C.CDLL(api.library_path())
+    L = C.CDLL(api.library_path(precision))
     names = _declared()
     assert len(names) >= 25
     for n in names:
-        assert hasattr(L, n), "liblbm_b200.so does not export %s" % n
+        assert hasattr(L, n), "%s does not export %s" % (os.path.basename(api.library_path(precision)), n)
     assert set(api.EXPORTS) <= set(names)
 
 
