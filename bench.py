@@ -83,9 +83,17 @@ def cpu_baseline(seconds):
         probe = run_reference_cpu(nx, ny, nz, 0, 2, ranks)
         steps = max(3, int(seconds / max(probe["seconds"] / 2, 1e-3)))
         r = run_reference_cpu(nx, ny, nz, 1, steps, ranks)
+        # the serial build as well (one rank, a few seconds): the north star asks for both
+        serial = None
+        try:
+            p1 = run_reference_cpu(nx, ny, 32, 0, 1, 1)
+            s1 = run_reference_cpu(nx, ny, 32, 1, max(2, int(4.0 / max(p1["seconds"], 1e-3))), 1)
+            serial = {"value": s1["mlups"], "cores": 1, "sample": "%dx%dx32, %.1f s" % (nx, ny, s1["seconds"])}
+        except Exception:
+            pass
         return {"value": r["mlups"], "unit": "MLUPS", "cores": ranks, "kind": "reference",
                 "sample": "unmodified Microchannel3D/QuarterChannel Lattice/Solver on %d mini-MPI z-slab ranks, %dx%dx%d, %d steps, %.1f s"
-                          % (ranks, nx, ny, nz, steps, r["seconds"])}
+                          % (ranks, nx, ny, nz, steps, r["seconds"]), "serial": serial}
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import oracle_lib as ol
     nx, ny, nz = 64, 64, 64
