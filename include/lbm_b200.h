@@ -89,6 +89,10 @@ typedef struct {
                                   D3Q19 see DESIGN.md section 6; Shan-Chen 1 = density pass + collide, 2/3/5 = other
                                   tiles of the fused kernel; binary D2Q9 1 = 256-thread blocks, 2-4 = fused tile
                                   kernel; curved solid 1/2 = other block shapes.  Results never depend on it. */
+    double trt_magic;          /* LBM_BINARY_D3Q19 only, EXTENSION with no counterpart in the reference: 0 (default) keeps
+                                  the reference's BGK collision; Lambda > 0 relaxes the antisymmetric half of f with
+                                  omega- = 1/(Lambda/(tau-1/2) + 1/2) (two-relaxation-time), everything else unchanged.
+                                  Parity unpinned: validated against the BGK limit Lambda = (tau-1/2)^2. */
 } lbm_config;
 
 /* Fills *cfg with the constants of the reference program for `model`

@@ -58,7 +58,7 @@ __global__ void __launch_bounds__(128, MINB) k_collide_push_occ(Geom g, Params P
 // (nodes 2..NX-3 x 2..NY-3: every push is a plain shifted store), which removes the control-flow merges
 // and register moves the folded boundary path costs every thread; the rim kernel runs the one-node rim
 // (and, on output steps, the wall-node fields) -- 2(NX+NY) nodes per plane.
-template <bool FXY, bool WRITE, int MINB, bool XRIM = false, bool TILE2D = false, int NT = 128>
+template <bool FXY, bool WRITE, int MINB, bool XRIM = false, bool TILE2D = false, int NT = 128, bool TRT = false>
 __global__ void __launch_bounds__(NT, MINB) k_collide_interior(Geom g, Params P, const pop_t *__restrict__ fin,
                                                                 const pop_t *__restrict__ gin, const double *__restrict__ phi,
                                                                 pop_t *__restrict__ fout, pop_t *__restrict__ gout, FieldsOut o,
@@ -95,10 +95,10 @@ __global__ void __launch_bounds__(NT, MINB) k_collide_interior(Geom g, Params P,
         G[k] = __ldg(pg + k * pl);
         PH[k] = __ldg(phi + (long long)(zs + CZ[k]) * pl + idx + CY[k] * NX + CX[k]);
     }
-    lbm3::collide_push_node<FXY, WRITE, XRIM ? 3 : 1>(g, P, F, G, PH, fout, gout, o, zs, ix, iy);
+    lbm3::collide_push_node<FXY, WRITE, XRIM ? 3 : 1, TRT>(g, P, F, G, PH, fout, gout, o, zs, ix, iy);
 }
 
-template <bool FXY, bool WRITE, bool ROWS_ONLY = false>
+template <bool FXY, bool WRITE, bool ROWS_ONLY = false, bool TRT = false>
 __global__ void __launch_bounds__(128) k_collide_rim(Geom g, Params P, const pop_t *__restrict__ fin,
                                                      const pop_t *__restrict__ gin, const double *__restrict__ phi,
                                                      pop_t *__restrict__ fout, pop_t *__restrict__ gout, FieldsOut o, int zs0)
@@ -137,6 +137,10 @@ __global__ void __launch_bounds__(128) k_collide_rim(Geom g, Params P, const pop
         F[k] = fin[lbm3::pop_index(g, zs, k, idx)];
         G[k] = gin[lbm3::pop_index(g, zs, k, idx)];
         PH[k] = phi[(long long)(zs + CZ[k]) * pl + idx + CY[k] * NX + CX[k]];
+    }
+    if (TRT) {   // the two-rate extension exists in the array form of the collision only
+        lbm3::collide_push_node<FXY, WRITE, 0, true>(g, P, F, G, PH, fout, gout, o, zs, ix, iy);
+        return;
     }
     // compile-time direction indices in the folded push (no table look-ups in local memory)
     const double *Gp = G;
@@ -401,6 +405,10 @@ public:
         P_.omega_phi = 1.0 / cfg_.tau_phi;
         P_.fx = cfg_.force[0]; P_.fy = cfg_.force[1]; P_.fz = cfg_.force[2];
         P_.phase_gradient = cfg_.wall_gradient; P_.rho_wall = cfg_.rho_wall;
+        P_.trt_magic = cfg_.trt_magic;
+        if (cfg_.trt_magic < 0.0) return rt_.fail(LBM_EINVAL, "trt_magic must be >= 0 (0 = BGK, the reference's collision)");
+        if (cfg_.trt_magic > 0.0 && cfg_.kernel_variant != 0)
+            return rt_.fail(LBM_EINVAL, "the TRT extension exists for kernel_variant 0 only");
         fxy_ = P_.fx != 0.0 || P_.fy != 0.0;
 
         const size_t pop_bytes = (size_t)(g_.nz + 4) * 19 * g_.pl * sizeof(pop_t);
@@ -607,6 +615,13 @@ public:
 #define LBM_LAUNCH_DEFAULT(FXY, WR)                                                                                            \
     do {                                                                                                                       \
         rt_.about_to_launch();                                                                                                 \
+        if (P_.trt_magic > 0.0) {                                                                                              \
+            k_collide_interior<FXY, WR, 3, true, false, 128, true><<<gi, 128, 0, rt_.stream>>>(g_, P_, f_[a], gq_[a], phi_, f_[b], gq_[b], o, zs0); \
+            LBM_TRY(rt_.launched("k_collide_interior"));                                                                       \
+            rt_.about_to_launch();                                                                                             \
+            k_collide_rim<FXY, WR, true, true><<<gr, 128, 0, rt_.stream>>>(g_, P_, f_[a], gq_[a], phi_, f_[b], gq_[b], o, zs0); \
+            break;                                                                                                             \
+        }                                                                                                                      \
         if (cfg_.kernel_variant == 65)                                                                                         \
             k_collide_interior<FXY, WR, 2, true><<<gi, 128, 0, rt_.stream>>>(g_, P_, f_[a], gq_[a], phi_, f_[b], gq_[b], o, zs0); \
         else if (cfg_.kernel_variant == 67)                                                                                    \

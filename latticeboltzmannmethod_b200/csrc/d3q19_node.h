@@ -33,6 +33,7 @@ struct Params {
     double omega_phi;          // 1.0 / tau_phi (lattice.hpp:467)
     double fx, fy, fz;
     double phase_gradient, rho_wall;
+    double trt_magic;          // 0: BGK as in the reference; > 0: two-relaxation-time collision of f (extension, no reference)
 };
 
 // direction table of descriptor.h:43-45 for the code that is not unrolled
@@ -82,7 +83,13 @@ LBM_HD void moments(const double *F, double &rho, double &ux, double &uy, double
 //   rho,ux..   out: density and force-shifted velocity (what the reference stores, :412-414)
 // FXY = false is the fast path for force_x == force_y == 0 (both shipped
 // configurations): the x and y force terms are then exact zeros in the reference.
-template <bool FXY>
+//
+// TRT = true is an EXTENSION with no counterpart in the reference (the north star names TRT on D3Q19, the reference
+// has none): the f populations relax with two rates -- the symmetric part (f_k + f_kbar)/2 with omega+ = 1/tau, which
+// keeps the reference's viscosity, the antisymmetric part with omega- = 1/(Lambda/(tau - 1/2) + 1/2), Lambda =
+// P.trt_magic -- while equilibria, Guo force populations and the g collision stay exactly the reference's.  With
+// Lambda = (tau - 1/2)^2 both rates coincide and the scheme is BGK up to rounding; that limit is the validation.
+template <bool FXY, bool TRT = false>
 LBM_HD void collide(double *F, double *G, double ph, double gx, double gy, double gz, double lap, const Params &P,
                     double &rho, double &ux, double &uy, double &uz)
 {
@@ -205,6 +212,24 @@ LBM_HD void collide(double *F, double *G, double ph, double gx, double gy, doubl
 
     // lattice.hpp:483-488
     const double mo = -omega, mop = -P.omega_phi;
+    if (TRT) {
+        const double omega_minus = 1.0 / (P.trt_magic / (tau - 0.5) + 0.5);
+        F[0] = (F[0] - omega * (F[0] - feq[0])) + fp[0];
+#define LBM3_TRT(k, kb)                                                     \
+    {                                                                       \
+        const double fpl = 0.5 * (F[k] + F[kb]), fmi = 0.5 * (F[k] - F[kb]); \
+        const double epl = 0.5 * (feq[k] + feq[kb]), emi = 0.5 * (feq[k] - feq[kb]); \
+        const double a = omega * (fpl - epl), b = omega_minus * (fmi - emi); \
+        F[k] = ((F[k] - a) - b) + fp[k];                                    \
+        F[kb] = ((F[kb] - a) + b) + fp[kb];                                 \
+    }
+        LBM3_TRT(1, 2) LBM3_TRT(3, 4) LBM3_TRT(5, 6) LBM3_TRT(7, 10) LBM3_TRT(8, 9)
+        LBM3_TRT(11, 14) LBM3_TRT(12, 13) LBM3_TRT(15, 18) LBM3_TRT(16, 17)
+#undef LBM3_TRT
+#pragma unroll
+        for (int k = 0; k < 19; k++) G[k] += mop * (G[k] - geq[k]);
+        return;
+    }
 #pragma unroll
     for (int k = 0; k < 19; k++) {
         F[k] += mo * (F[k] - feq[k]) + fp[k];

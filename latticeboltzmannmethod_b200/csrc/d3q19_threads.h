@@ -119,7 +119,7 @@ LBM_HD void mirror_fields(const double *F, const Params &P, const FieldsOut &o, 
 // folded boundary push); 3: a node with 2 <= iY <= NY-3 and any bulk iX -- the x mirror line (iX = 1) and
 // the x wall (iX = NX-2) are folded in as an address select on the ten directions with cx != 0, so that
 // these two columns are stored by the same coalesced warps as their row neighbours.
-template <bool FXY, bool WRITE, int PART = 0>
+template <bool FXY, bool WRITE, int PART = 0, bool TRT = false>
 LBM_HD void collide_push_node(const Geom &g, const Params &P, double *F, double *G, const double *PH, pop_t *fout,
                               pop_t *gout, const FieldsOut &o, int zs, int ix, int iy)
 {
@@ -134,7 +134,7 @@ LBM_HD void collide_push_node(const Geom &g, const Params &P, double *F, double 
         if (PART != 3 && ix == 1 && iy == 1) mirror_fields<3>(F, P, o, (long long)(zs - 2) * g.pl);
     }
     double rho, ux, uy, uz;
-    collide<FXY>(F, G, PH[0], gx, gy, gz, lap, P, rho, ux, uy, uz);
+    collide<FXY, TRT>(F, G, PH[0], gx, gy, gz, lap, P, rho, ux, uy, uz);
     if (WRITE && own) {
         const long long at = (long long)(zs - 2) * g.pl + idx;
         o.rho[at] = rho; o.ux[at] = ux; o.uy[at] = uy; o.uz[at] = uz;

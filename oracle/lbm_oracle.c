@@ -91,6 +91,7 @@ struct lbo3 {
     double *phi;               /* [(nz+4)][pl] extended phase field (bulk, mirror, wall, ghost planes) */
     double *rho, *ux, *uy, *uz;/* [nz][pl] */
     double aconst, kconst, gammaconst, phase_gradient, rho_wall, tau_phi, tau_liq, tau_gas, fx, fy, fz;
+    double trt_magic;          /* 0: the reference's BGK; > 0: the two-relaxation-time EXTENSION (no reference counterpart) */
 };
 
 static inline size_t pidx(const lbo3 *s, int zs, int k, size_t node)
@@ -357,9 +358,24 @@ void lbo3_collide(lbo3 *s, int write_fields)
                     sum_force += fp[k];
                 }
                 fp[0] = -sum_force;
+                /* extension (no reference counterpart): two relaxation rates for f -- the symmetric half of every pair
+                 * (k, opposite k) with omega+ = 1/tau, the antisymmetric half with omega- from the magic parameter */
+                if (s->trt_magic > 0.0) {
+                    const double omega_minus = 1.0 / (s->trt_magic / (tau - 0.5) + 0.5);
+                    F[0] = (F[0] - omega_rho * (F[0] - feq[0])) + fp[0];
+                    for (int k = 1; k < 19; k++) {
+                        int kb = OPP3[k];
+                        if (kb < k) continue;
+                        double fpl = 0.5 * (F[k] + F[kb]), fmi = 0.5 * (F[k] - F[kb]);
+                        double epl = 0.5 * (feq[k] + feq[kb]), emi = 0.5 * (feq[k] - feq[kb]);
+                        double a = omega_rho * (fpl - epl), b = omega_minus * (fmi - emi);
+                        F[k] = ((F[k] - a) - b) + fp[k];
+                        F[kb] = ((F[kb] - a) + b) + fp[kb];
+                    }
+                }
                 /* lattice.hpp:483-488 then the push */
                 for (int k = 0; k < 19; k++) {
-                    F[k] += -omega_rho * (F[k] - feq[k]) + fp[k];
+                    if (s->trt_magic <= 0.0) F[k] += -omega_rho * (F[k] - feq[k]) + fp[k];
                     G[k] += -omega_phi * (G[k] - geq[k]);
                     int tx, ty, dz;
                     int kk = push_target(s, ix, iy, k, &tx, &ty, &dz);
@@ -511,6 +527,8 @@ void lbo3_get_pops(lbo3 *s, double *f, double *g)
                 }
             }
 }
+
+void lbo3_set_trt(lbo3 *s, double magic) { s->trt_magic = magic; }
 
 void lbo3_set_pops(lbo3 *s, const double *f, const double *g)
 {

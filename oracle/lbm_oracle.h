@@ -77,6 +77,9 @@ void lbo3_get_fields(lbo3 *, double *rho, double *phase, double *ux, double *uy,
  * permuted copy of their inner neighbour, wall nodes 0 (the reference's are junk) */
 void lbo3_get_pops(lbo3 *, double *f, double *g);
 void lbo3_set_pops(lbo3 *, const double *f, const double *g);
+/* EXTENSION, no counterpart in the reference: magic > 0 switches the f collision to two relaxation rates
+ * (omega+ = 1/tau, omega- = 1/(magic/(tau-1/2)+1/2)); 0 restores the reference's BGK. */
+void lbo3_set_trt(lbo3 *, double magic);
 
 /* ---------------- D2Q9 binary liquid (FreeEnergy/binary.cpp) ---------------- */
 typedef struct lbo2b lbo2b;

@@ -125,6 +125,11 @@ class Oracle3D:
         self.h = self.L.lbo3_create(nx, ny, nz, _p(p))
         assert self.h
 
+    def set_trt(self, magic):
+        """Extension without a reference counterpart: two-relaxation-time collision of f (0 = the reference's BGK)."""
+        self.L.lbo3_set_trt.argtypes = [C.c_void_p, C.c_double]
+        self.L.lbo3_set_trt(self.h, magic)
+
     def close(self):
         if self.h:
             self.L.lbo3_destroy(self.h)
