@@ -375,6 +375,9 @@ def ours(args, rank, world, local_rank):
 
 
 def main():
+    # NCCL_DEBUG=VERSION makes NCCL print its banner on stdout ahead of the JSON line; keep stdout to that one line
+    if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+        os.environ["NCCL_DEBUG"] = "WARN"
     args = parse()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
