@@ -207,6 +207,21 @@ def slab_initial_fields(api, nx, ny, nz_global, z_begin, nz_local, width, np):
     return phase.reshape(-1)
 
 
+class quiet_stdout:
+    """Sends file descriptor 1 to stderr while communicators come up: NCCL prints its version banner on stdout at the
+    first communicator, and stdout has to stay the one JSON line."""
+
+    def __enter__(self):
+        sys.stdout.flush()
+        self.saved = os.dup(1)
+        os.dup2(2, 1)
+
+    def __exit__(self, *a):
+        sys.stdout.flush()
+        os.dup2(self.saved, 1)
+        os.close(self.saved)
+
+
 def ours(args, rank, world, local_rank):
     import numpy as np
     import torch
@@ -216,7 +231,9 @@ def ours(args, rank, world, local_rank):
     dist = None
     if world > 1:
         import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        with quiet_stdout():
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+            dist.barrier()
 
     if args.workload == "full":
         nx, ny, nz, width, which = 92, 52, 1500, 8, "full"
@@ -234,9 +251,10 @@ def ours(args, rank, world, local_rank):
     z_begin, nz_local = ctx.slab_extent()
     nloc = ctx.local_nodes
     if world > 1:
-        uid = [api.comm_unique_id() if rank == 0 else None]
-        dist.broadcast_object_list(uid, src=0)
-        ctx.comm_attach(uid[0])
+        with quiet_stdout():
+            uid = [api.comm_unique_id() if rank == 0 else None]
+            dist.broadcast_object_list(uid, src=0)
+            ctx.comm_attach(uid[0])
 
     # pinned host buffers: initial fields in, result fields out (the e2e leg copies through them every segment)
     L = api.load_library(args.precision)
@@ -375,9 +393,6 @@ def ours(args, rank, world, local_rank):
 
 
 def main():
-    # NCCL_DEBUG=VERSION makes NCCL print its banner on stdout ahead of the JSON line; keep stdout to that one line
-    if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
-        os.environ["NCCL_DEBUG"] = "WARN"
     args = parse()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
