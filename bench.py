@@ -207,6 +207,23 @@ def slab_initial_fields(api, nx, ny, nz_global, z_begin, nz_local, width, np):
     return phase.reshape(-1)
 
 
+def bind_to_gpu_numa_node(device_index):
+    """Pins this process to the CPU cores NVML reports as local to its GPU, so that the pinned host buffers of the
+    end-to-end leg are first-touched on the GPU's own socket (torchrun does not bind ranks)."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(device_index)
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        cpus = {64 * w + b for w, m in enumerate(mask) for b in range(64) if (m >> b) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+    except Exception:
+        pass      # placement is an optimisation of the e2e figure only
+
+
 class quiet_stdout:
     """Sends file descriptor 1 to stderr while communicators come up: NCCL prints its version banner on stdout at the
     first communicator, and stdout has to stay the one JSON line."""
@@ -228,6 +245,8 @@ def ours(args, rank, world, local_rank):
     from latticeboltzmannmethod_b200 import api
 
     torch.cuda.set_device(local_rank)
+    if world > 1:      # at N=1 the whole host stays available to the CPU baseline timed in the same run
+        bind_to_gpu_numa_node(local_rank)
     dist = None
     if world > 1:
         import torch.distributed as dist
