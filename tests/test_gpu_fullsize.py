@@ -55,3 +55,71 @@ def test_z_translation_invariance_and_conservation_at_bench_size():
     for k in keep:
         for z in zs:
             assert np.array_equal(keep[k][z], b[k][(z + SHIFT) % N]), (k, z)
+
+
+@pytest.mark.parametrize("variant,omega,omega_bulk", [("gs", 1.2, 0.8), ("hermite", 0.9, 0.1)])
+def test_mrt_8192_squared_equals_the_y_independent_oracle_run(variant, omega, omega_bulk):
+    """BASELINE.json configs[2]: the shear wave of mrt.cpp on 8192 x 8192.  The problem does not depend on y, so every
+    column of the big run must equal the oracle's 8192 x 3 run -- bit for bit."""
+    import oracle_lib as ol
+    from latticeboltzmannmethod_b200 import api
+    n, steps = 8192, 25
+    v = 0 if variant == "gs" else 1
+    o = ol.OracleMRT(v, n, 3, omega, omega_bulk, 0.002 if v == 0 else 0.0)
+    o.init_wave(0.001)
+    o.step(steps)
+    want = {k: a.reshape(n, 3)[:, 1] for k, a in o.fields().items()}
+    o.close()
+    ctx = api.Context(api.mrt_config(variant, n, n, omega, omega_bulk))
+    rho, ux, uy = api.mrt_initial_fields(variant, n, 1)
+    for name, a in (("rho", rho), ("ux", ux), ("uy", uy)):
+        ctx.set_field(name, np.repeat(a, n))
+    ctx.init()
+    ctx.step(steps)
+    for k in ("rho", "ux", "uy"):
+        got = ctx.get_field(k).reshape(n, n)
+        assert np.array_equal(got, np.broadcast_to(got[:, :1], got.shape)), k      # every row of y equal
+        assert np.array_equal(got[:, 0], want[k]), k
+    ctx.close()
+
+
+def test_shanchen_8192_squared_equals_the_tiled_128_squared_oracle_run():
+    """The droplet of shanchen.cpp tiled with its own period: each 128 x 128 tile of the big periodic run must equal
+    the oracle's 128 x 128 run -- bit for bit."""
+    import oracle_lib as ol
+    from latticeboltzmannmethod_b200 import api
+    n, t, steps = 8192, 128, 40
+    o = ol.OracleShanChen(t, t)
+    o.init_droplet()
+    rho0 = o.fields()["rho"].copy()
+    o.step(steps)
+    want = o.fields()["rho"].reshape(t, t)
+    o.close()
+    ctx = api.Context(api.shanchen_config(n, n))
+    ctx.set_field("rho", np.tile(rho0.reshape(t, t), (n // t, n // t)).ravel())
+    ctx.init()
+    ctx.step(steps)
+    got = ctx.get_field("rho").reshape(n // t, t, n // t, t)
+    assert np.array_equal(got, np.broadcast_to(want[None, :, None, :], got.shape))
+    ctx.close()
+
+
+def test_binary2d_tiled_in_x_equals_the_128_squared_oracle_run():
+    """binary.cpp's box on a wetting wall, repeated 256 times along the periodic x direction (32768 x 128): each
+    128-column tile must equal the oracle's 128 x 128 run -- bit for bit."""
+    import oracle_lib as ol
+    from latticeboltzmannmethod_b200 import api
+    t, reps, steps = 128, 256, 60
+    o = ol.OracleBinary2D(t, t)
+    o.init_reference()
+    o.step(steps)
+    want = {k: a.reshape(t, t) for k, a in o.fields().items()}        # [iX][iY]
+    o.close()
+    ctx = api.Context(api.binary2d_config(t * reps, t))
+    ctx.set_field("phase", np.tile(api.binary2d_initial_phase().reshape(t, t), (reps, 1)).ravel())
+    ctx.init()
+    ctx.step(steps)
+    for k in ("phase", "rho", "ux", "uy"):
+        got = ctx.get_field(k).reshape(reps, t, t)
+        assert np.array_equal(got, np.broadcast_to(want[k][None], got.shape)), k
+    ctx.close()
