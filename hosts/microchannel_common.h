@@ -17,23 +17,13 @@ static int run_channel(const ChannelSetup &S, int argc, char **argv)
     if (std::getenv("LBM_NUMTIME")) NUMTIME = std::atoi(std::getenv("LBM_NUMTIME"));
     const double rhol = 1.0, rhog = 1.0;
 
+    // the parameter list of main.cpp:48-63, same names and values
     ParamsList params;
-    params.add("omega", 1.0);
-    params.add("aconst", 0.04);
-    params.add("kconst", 0.04);
-    params.add("gammaconst", 1.0);
-    params.add("phase_gradient", 0.0);
-    params.add("phase_wall", 0.0);
-    params.add("rho_wall", 0.5);
-    params.add("tau_phi", S.tau_phi);
-    params.add("tau_liq", 2.5);
-    params.add("tau_gas", 0.7);
-    params.add("force_x", 0.0);
-    params.add("force_y", 0.0);
-    params.add("force_z", S.force_z);
-    params.add("NX", NX);
-    params.add("NY", NY);
-    params.add("NZ", NZ);
+    const struct { const char *name; double value; } table[] = {
+        {"omega", 1.0}, {"aconst", 0.04}, {"kconst", 0.04}, {"gammaconst", 1.0}, {"phase_gradient", 0.0}, {"phase_wall", 0.0},
+        {"rho_wall", 0.5}, {"tau_phi", S.tau_phi}, {"tau_liq", 2.5}, {"tau_gas", 0.7}, {"force_x", 0.0}, {"force_y", 0.0},
+        {"force_z", S.force_z}, {"NX", (double)NX}, {"NY", (double)NY}, {"NZ", (double)NZ}};
+    for (size_t i = 0; i < sizeof table / sizeof table[0]; i++) params.add(table[i].name, table[i].value);
 
     Solver solver(params);
 
