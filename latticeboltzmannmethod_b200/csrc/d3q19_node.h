@@ -214,14 +214,19 @@ LBM_HD void collide(double *F, double *G, double ph, double gx, double gy, doubl
     const double mo = -omega, mop = -P.omega_phi;
     if (TRT) {
         const double omega_minus = 1.0 / (P.trt_magic / (tau - 0.5) + 0.5);
+        // the force populations split like the populations themselves: the symmetric half keeps Guo's prefactor
+        // (1 - omega/2) that fp[] already carries, the antisymmetric half -- the one that injects momentum -- takes
+        // (1 - omega_minus/2), so that a step adds exactly F to the momentum whatever Lambda is
+        const double fr = (1.0 - 0.5 * omega_minus) / pref;
         F[0] = (F[0] - omega * (F[0] - feq[0])) + fp[0];
 #define LBM3_TRT(k, kb)                                                     \
     {                                                                       \
         const double fpl = 0.5 * (F[k] + F[kb]), fmi = 0.5 * (F[k] - F[kb]); \
         const double epl = 0.5 * (feq[k] + feq[kb]), emi = 0.5 * (feq[k] - feq[kb]); \
         const double a = omega * (fpl - epl), b = omega_minus * (fmi - emi); \
-        F[k] = ((F[k] - a) - b) + fp[k];                                    \
-        F[kb] = ((F[kb] - a) + b) + fp[kb];                                 \
+        const double fsy = 0.5 * (fp[k] + fp[kb]), fan = fr * (0.5 * (fp[k] - fp[kb])); \
+        F[k] = ((F[k] - a) - b) + (fsy + fan);                              \
+        F[kb] = ((F[kb] - a) + b) + (fsy - fan);                            \
     }
         LBM3_TRT(1, 2) LBM3_TRT(3, 4) LBM3_TRT(5, 6) LBM3_TRT(7, 10) LBM3_TRT(8, 9)
         LBM3_TRT(11, 14) LBM3_TRT(12, 13) LBM3_TRT(15, 18) LBM3_TRT(16, 17)

@@ -362,6 +362,7 @@ void lbo3_collide(lbo3 *s, int write_fields)
                  * (k, opposite k) with omega+ = 1/tau, the antisymmetric half with omega- from the magic parameter */
                 if (s->trt_magic > 0.0) {
                     const double omega_minus = 1.0 / (s->trt_magic / (tau - 0.5) + 0.5);
+                    const double fr = (1.0 - 0.5 * omega_minus) / (1.0 - 0.5 * omega_rho);
                     F[0] = (F[0] - omega_rho * (F[0] - feq[0])) + fp[0];
                     for (int k = 1; k < 19; k++) {
                         int kb = OPP3[k];
@@ -369,8 +370,11 @@ void lbo3_collide(lbo3 *s, int write_fields)
                         double fpl = 0.5 * (F[k] + F[kb]), fmi = 0.5 * (F[k] - F[kb]);
                         double epl = 0.5 * (feq[k] + feq[kb]), emi = 0.5 * (feq[k] - feq[kb]);
                         double a = omega_rho * (fpl - epl), b = omega_minus * (fmi - emi);
-                        F[k] = ((F[k] - a) - b) + fp[k];
-                        F[kb] = ((F[kb] - a) + b) + fp[kb];
+                        /* force populations: symmetric half with (1 - omega/2) (already in fp), antisymmetric half
+                         * with (1 - omega_minus/2): the first moment of a step's change is then exactly F */
+                        double fsy = 0.5 * (fp[k] + fp[kb]), fan = fr * (0.5 * (fp[k] - fp[kb]));
+                        F[k] = ((F[k] - a) - b) + (fsy + fan);
+                        F[kb] = ((F[kb] - a) + b) + (fsy - fan);
                     }
                 }
                 /* lattice.hpp:483-488 then the push */

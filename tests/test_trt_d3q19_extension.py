@@ -47,6 +47,42 @@ def test_oracle_trt_reduces_to_bgk_when_both_rates_coincide():
     assert np.max(np.abs(other["uz"] - bgk["uz"])) > 1e-9
 
 
+@pytest.mark.parametrize("magic", [0.0, 3.0 / 16.0, 0.25, 0.64, 2.0])
+@pytest.mark.parametrize("tau_liq,tau_gas", [(1.3, 1.3), (2.5, 0.7)])
+def test_trt_collision_adds_exactly_the_force_to_the_momentum(emu_libs, magic, tau_liq, tau_gas):
+    """The per-node collision of csrc/d3q19_node.h (the very code the kernels compile, run here on the CPU): whatever
+    Lambda is, one collision must change the node's momentum by exactly the body force F -- the antisymmetric half of
+    the Guo force populations has to carry (1 - omega_minus/2), not the BGK prefactor -- and must conserve the mass
+    and the order parameter."""
+    import ctypes as C
+    L = C.CDLL(emu_libs["d3q19"])
+    dp = C.POINTER(C.c_double)
+    L.emu3_collide_node.argtypes = [dp, C.c_double, dp, dp, dp, dp]
+    L.emu3_collide_node.restype = None
+    cx = np.array([0, 1, -1, 0, 0, 0, 0, 1, -1, 1, -1, 0, 0, 0, 0, 1, -1, 1, -1], dtype=np.float64)
+    cy = np.array([0, 0, 0, 1, -1, 0, 0, 1, 1, -1, -1, 1, -1, 1, -1, 0, 0, 0, 0], dtype=np.float64)
+    cz = np.array([0, 0, 0, 0, 0, 1, -1, 0, 0, 0, 0, 1, 1, -1, -1, 1, 1, -1, -1], dtype=np.float64)
+    w = np.array([1 / 3.0] + [1 / 18.0] * 6 + [1 / 36.0] * 12)
+    force = np.array([1e-3, -2e-3, 3e-3])
+    params = np.array([0.04, 0.04, 1.0, 0.02, 0.0, 0.5, 2.0, tau_liq, tau_gas, force[0], force[1], force[2]])
+    rng = np.random.default_rng(7)
+    for trial in range(20):
+        F = w * (1.0 + 0.1 * rng.standard_normal(19))
+        ph0 = rng.uniform(-1, 1)
+        PH = ph0 + 0.05 * rng.standard_normal(19)
+        PH[0] = ph0
+        G = w * ph0 * (1.0 + 0.1 * rng.standard_normal(19))
+        G[0] += ph0 - G.sum()                                   # g sums to the phase value the stencil sees
+        F0, G0 = F.copy(), G.copy()
+        out4 = np.zeros(4)
+        L.emu3_collide_node(params.ctypes.data_as(dp), magic, F.ctypes.data_as(dp), G.ctypes.data_as(dp),
+                            PH.ctypes.data_as(dp), out4.ctypes.data_as(dp))
+        for c, fc in zip((cx, cy, cz), force):
+            assert abs((c * F).sum() - (c * F0).sum() - fc) <= 1e-15 * 19, (trial, magic)
+        assert abs(F.sum() - F0.sum()) <= 1e-15 * 19
+        assert abs(G.sum() - G0.sum()) <= 1e-15 * 19
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("shape,params,magic", [((12, 10, 8), CONST_TAU, 0.64), ((27, 27, 20), TWO_TAU, 3.0 / 16.0),
                                                 ((9, 7, 5), TWO_TAU, 0.25)])
@@ -90,6 +126,6 @@ def test_gpu_trt_limits():
     with pytest.raises(api.LbmError):
         api.Context(cfg)
     cfg.trt_magic = 0.25
-    cfg.kernel_variant = 91
+    cfg.kernel_variant = 1                                   # the plain cross-check kernel has no TRT form
     with pytest.raises(api.LbmError):
         api.Context(cfg)
