@@ -152,6 +152,11 @@ lbm_status lbm_sync(lbm_ctx *ctx);
  * binary.cpp:357-384, mrt.cpp:254-270) and Solver::getWhole* for one slab
  * (solver.hpp:121-277).  n = lbm_local_nodes(). */
 lbm_status lbm_get_field(lbm_ctx *ctx, int field, double *host, size_t n);
+/* Same copy, queued only: `host` (page-locked memory from lbm_host_alloc, or the call degenerates to the blocking
+ * form) holds the field after the next lbm_sync.  Lets a host program queue all five getWhole* copies of
+ * solver.hpp:121-277 and wait once.  lbm_set_field is queued the same way: a pageable source is staged before the
+ * call returns, a page-locked one must stay unchanged until the next call that waits. */
+lbm_status lbm_get_field_async(lbm_ctx *ctx, int field, double *host, size_t n);
 
 /* Replaces: calculateDensities' sums (shanchen.cpp:49-70), the mass print-out of
  * CurvedSolid (binary_shape.cpp:654-661) and the NaN probes (binary.cpp:359,
@@ -163,6 +168,12 @@ lbm_status lbm_diagnostics(lbm_ctx *ctx, double *mass, double momentum[3], doubl
 void *lbm_get_stream(lbm_ctx *ctx);                /* cudaStream_t the step runs on */
 lbm_status lbm_set_stream(lbm_ctx *ctx, void *cuda_stream);
 unsigned long long lbm_launch_count(const lbm_ctx *ctx); /* kernels launched by this context so far */
+int lbm_population_bytes(const lbm_ctx *ctx);      /* storage size of one population value: 8, or 4 in liblbm_b200_f32.so;
+                                                      the element size of the F/G halo messages of lbm_slab_halo */
+/* D3Q19 one-pass step (kernel_variant 0): number of steps so far in which a block gave up waiting for the blocks its
+ * phase-field part depends on and the phase field was recomputed by the separate kernel instead (results are the
+ * same either way; a non-zero value only says the step was slower than it should be).  Waits for the stream. */
+unsigned long long lbm_phase_fallbacks(lbm_ctx *ctx);
 /* Per-kernel device timing (CUDA events around every kernel launched while enabled); the report is a JSON
  * object {"kernel": {"launches": n, "ms": total}} and clears the record.  Replaces the reference's only
  * instrumentation, time(NULL) around the loop (shanchen.cpp:117-118,212-214). */
@@ -186,7 +197,8 @@ typedef enum {
     LBM_HALO_R_F_FROM_BELOW, LBM_HALO_R_G_FROM_BELOW, LBM_HALO_R_F_FROM_ABOVE, LBM_HALO_R_G_FROM_ABOVE,
     LBM_HALO_S_PHI_UP, LBM_HALO_S_PHI_DOWN, LBM_HALO_R_PHI_FROM_BELOW, LBM_HALO_R_PHI_FROM_ABOVE
 } lbm_halo_id;
-/* device pointer and length (doubles) of one halo message; S_x_UP pairs with the upper
+/* device pointer and length in ELEMENTS of one halo message -- F/G messages: elements of lbm_population_bytes()
+ * bytes (double; float in liblbm_b200_f32.so), PHI messages: doubles; S_x_UP pairs with the upper
  * neighbour's R_x_FROM_BELOW, S_x_DOWN with the lower neighbour's R_x_FROM_ABOVE */
 lbm_status lbm_slab_halo(lbm_ctx *ctx, int halo_id, void **device_ptr, size_t *count);
 lbm_status lbm_slab_init_fields(lbm_ctx *ctx);  /* then exchange PHI */
@@ -208,7 +220,9 @@ lbm_status lbm_slab_finish(lbm_ctx *ctx);
  * LBM_NOALLOC_MAX_BLOCKS*8192 = 134 217 728 (LBM_EINVAL beyond that).  All calls share that array: calls
  * whose kernels overlap on one GPU race -- serialise them.  Nothing needs clearing between calls (each
  * call overwrites every entry it reads).  The first call on a device looks the array's address up
- * (cudaGetSymbolAddress); make that first call before any stream capture. */
+ * (cudaGetSymbolAddress); make that first call before any stream capture.
+ * liblbm_b200_f32.so exports the same function with the same signature: it sums `double` arrays there too, so it
+ * cannot be pointed at that build's float-stored populations (use lbm_diagnostics on the context for those). */
 #define LBM_NOALLOC_MAX_BLOCKS 16384
 lbm_status lbm_population_sums_noalloc(const double *f_dev, const double *g_dev, int q, size_t n_nodes, size_t stride_k,
                                        void *cuda_stream, double *sums6_dev);

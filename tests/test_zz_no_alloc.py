@@ -53,6 +53,40 @@ def test_noalloc_sums_match_diagnostics_twice():
             assert got[5] == 1.0
 
 
+def test_noalloc_d3q19_with_g_and_a_nan_in_g_twice():
+    """The 19-direction table and the g accumulation: two calls in a row on different data, the second with a NaN
+    placed in g only (f stays clean, so the f sums stay finite and comparable).  Checked against float64 numpy sums
+    of the same arrays (summation order differs: relative tolerance)."""
+    import torch
+    from latticeboltzmannmethod_b200 import api
+    cx = np.array([0, 1, -1, 0, 0, 0, 0, 1, -1, 1, -1, 0, 0, 0, 0, 1, -1, 1, -1], dtype=np.float64)
+    cy = np.array([0, 0, 0, 1, -1, 0, 0, 1, 1, -1, -1, 1, -1, 1, -1, 0, 0, 0, 0], dtype=np.float64)
+    cz = np.array([0, 0, 0, 0, 0, 1, -1, 0, 0, 0, 0, 1, 1, -1, -1, 1, 1, -1, -1], dtype=np.float64)
+    n, stride = 50_021, 50_048                           # ragged tail; directions padded apart (stride_k > n_nodes)
+    rng = np.random.default_rng(77)
+    out = torch.zeros(6, dtype=torch.float64, device="cuda")
+    stream = torch.cuda.current_stream().cuda_stream
+    for call in range(2):
+        f = rng.uniform(0.01, 0.2, (19, stride)) * (1.0 + 2 * call)
+        g = rng.uniform(-0.1, 0.1, (19, stride)) * (1.0 + call)
+        if call == 1:
+            g[7, 31_000] = np.nan
+        fd, gd = torch.from_numpy(f).cuda(), torch.from_numpy(g).cuda()
+        api.population_sums_noalloc(fd.data_ptr(), gd.data_ptr(), 19, n, stride, stream, out.data_ptr())
+        torch.cuda.synchronize()
+        got = out.cpu().numpy()
+        fn = f[:, :n]
+        scale = abs(fn.sum())
+        assert abs(got[0] - fn.sum()) <= TOL * scale
+        for c, tab in zip((1, 2, 3), (cx, cy, cz)):
+            assert abs(got[c] - (tab[:, None] * fn).sum()) <= TOL * scale, c
+        if call == 0:
+            assert abs(got[4] - g[:, :n].sum()) <= TOL * np.abs(g[:, :n]).sum()
+            assert got[5] == 0.0
+        else:
+            assert np.isnan(got[4]) and got[5] == 1.0    # one NaN, counted once, and it poisons the g sum only
+
+
 def test_noalloc_rejects_sizes_beyond_the_scratch():
     import torch
     from latticeboltzmannmethod_b200 import api
