@@ -1,8 +1,11 @@
 // solver_b200.h -- the public interface of the reference's Solver<D> (Microchannel3D/*/solver.h:10-86) on top of
 // liblbm_b200.so, so that a main.cpp written against the reference compiles against this header with
 // `Solver<Descriptor>` replaced by `Solver`: same method names, same arguments, same files written.
-//   * one GPU, one slab (the reference's rank 0 of 1); multi-GPU runs are one process per GPU through the C ABI
-//     (lbm_comm_attach)
+//   * LBM_GPUS=N in the environment (default 1) spreads the grid over N GPUs of this machine as N z-slabs with the
+//     reference's own slab rule (solver.hpp:24-30): one host thread and one context per GPU (devices LBM_DEVICE ..
+//     LBM_DEVICE+N-1), halos exchanged inside the library over NCCL (lbm_comm_attach), put* / getWhole* / the writers
+//     work on the whole grid exactly as the reference's rank 0 does after its gather (solver.hpp:121-277) -- the
+//     replacement of `mpiexec -n N` (binary.pbs:58) on a single multi-GPU box.  Results do not depend on N.
 //   * every .vts is the file VTK 5's vtkXMLStructuredGridWriter would write in raw appended mode
 //   * additions with no reference counterpart are marked "extension"
 #ifndef LBM_SOLVER_B200_H
@@ -12,6 +15,7 @@
 #include <cstring>
 #include <map>
 #include <stdexcept>
+#include <thread>
 #include "host_common.h"
 
 // params_list.h: name -> value(s); the hosts only ever add one number per name
@@ -34,7 +38,7 @@ private:
 class Solver {
 public:
     // solver.hpp:17-47 (Solver) + lattice.hpp constructor: sizes and constants from the list
-    explicit Solver(const ParamsList &p) : NX((int)p.get("NX")), NY((int)p.get("NY")), NZ((int)p.get("NZ")), ctx_(0)
+    explicit Solver(const ParamsList &p) : NX((int)p.get("NX")), NY((int)p.get("NY")), NZ((int)p.get("NZ"))
     {
         lbm_config cfg;
         lbm_config_default(&cfg, LBM_BINARY_D3Q19);
@@ -43,20 +47,44 @@ public:
         cfg.wall_gradient = p.get("phase_gradient"); cfg.rho_wall = p.get("rho_wall");
         cfg.tau_phi = p.get("tau_phi"); cfg.tau_liq = p.get("tau_liq"); cfg.tau_gas = p.get("tau_gas");
         cfg.force[0] = p.get("force_x"); cfg.force[1] = p.get("force_y"); cfg.force[2] = p.get("force_z");
-        cfg.device = device_from_env();
-        LBM_CHECK(0, lbm_create(&cfg, &ctx_));
+        const char *e = std::getenv("LBM_GPUS");
+        const int ngpu = e ? std::atoi(e) : 1;
+        if (ngpu < 1 || NZ / ngpu < 2) throw std::runtime_error("LBM_GPUS: need at least 2 z planes per GPU");
+        slabs_.resize(ngpu);
+        for (int r = 0; r < ngpu; r++) {
+            cfg.device = device_from_env() + r;
+            cfg.slab_rank = r; cfg.slab_count = ngpu;
+            LBM_CHECK(0, lbm_create(&cfg, &slabs_[r].ctx));
+            int z0 = 0, nzl = 0;
+            LBM_CHECK(slabs_[r].ctx, lbm_slab_extent(slabs_[r].ctx, &z0, &nzl));
+            slabs_[r].first = (size_t)z0 * NX * NY;
+            slabs_[r].count = (size_t)nzl * NX * NY;
+        }
+        if (ngpu > 1) {
+            // one communicator over the slabs: every rank has to join at the same time, hence one thread each
+            char id[LBM_COMM_ID_BYTES];
+            LBM_CHECK(0, lbm_comm_unique_id(id));
+            each_slab([&](Slab &s) { LBM_CHECK(s.ctx, lbm_comm_attach(s.ctx, id)); });
+        }
         n_ = (size_t)NX * NY * NZ;
         rho_.assign(n_, 0.0); phi_.assign(n_, 0.0); ux_.assign(n_, 0.0); uy_.assign(n_, 0.0); uz_.assign(n_, 0.0);
         density.assign(n_, 0.0); phase.assign(n_, 0.0); velocity.assign(3 * n_, 0.0);
     }
-    ~Solver() { lbm_destroy(ctx_); }
+    ~Solver()
+    {
+        for (size_t r = 0; r < slabs_.size(); r++) lbm_destroy(slabs_[r].ctx);
+    }
 
     // solver.hpp:49-55 probes one node of the last gathered phase array; this probes every population on the device
     bool checkNAN()
     {
-        int has_nan = 0;
-        LBM_CHECK(ctx_, lbm_diagnostics(ctx_, 0, 0, 0, &has_nan));
-        return has_nan != 0;
+        bool any = false;
+        for (size_t r = 0; r < slabs_.size(); r++) {
+            int has_nan = 0;
+            LBM_CHECK(slabs_[r].ctx, lbm_diagnostics(slabs_[r].ctx, 0, 0, 0, &has_nan));
+            any = any || has_nan != 0;
+        }
+        return any;
     }
 
     // solver.hpp:58-118 / lattice.hpp putDensity...: inclusive index boxes into the fields init() starts from
@@ -73,26 +101,30 @@ public:
     // solver.hpp:871-879
     void init()
     {
-        LBM_CHECK(ctx_, lbm_set_field(ctx_, LBM_RHO, rho_.data(), n_));
-        LBM_CHECK(ctx_, lbm_set_field(ctx_, LBM_PHASE, phi_.data(), n_));
-        LBM_CHECK(ctx_, lbm_set_field(ctx_, LBM_UX, ux_.data(), n_));
-        LBM_CHECK(ctx_, lbm_set_field(ctx_, LBM_UY, uy_.data(), n_));
-        LBM_CHECK(ctx_, lbm_set_field(ctx_, LBM_UZ, uz_.data(), n_));
-        LBM_CHECK(ctx_, lbm_init(ctx_));
+        each_slab([&](Slab &s) {
+            LBM_CHECK(s.ctx, lbm_set_field(s.ctx, LBM_RHO, rho_.data() + s.first, s.count));
+            LBM_CHECK(s.ctx, lbm_set_field(s.ctx, LBM_PHASE, phi_.data() + s.first, s.count));
+            LBM_CHECK(s.ctx, lbm_set_field(s.ctx, LBM_UX, ux_.data() + s.first, s.count));
+            LBM_CHECK(s.ctx, lbm_set_field(s.ctx, LBM_UY, uy_.data() + s.first, s.count));
+            LBM_CHECK(s.ctx, lbm_set_field(s.ctx, LBM_UZ, uz_.data() + s.first, s.count));
+            LBM_CHECK(s.ctx, lbm_init(s.ctx));
+        });
     }
     // solver.hpp:881-891; collide_stream(n) (extension) queues n steps at once and only the last one leaves the
     // macroscopic fields behind, which is all the writers can see in the reference too
-    void collide_stream() { LBM_CHECK(ctx_, lbm_step(ctx_, 1)); }
-    void collide_stream(int nsteps) { LBM_CHECK(ctx_, lbm_step(ctx_, nsteps)); }
+    void collide_stream() { collide_stream(1); }
+    void collide_stream(int nsteps)
+    {
+        each_slab([&](Slab &s) { LBM_CHECK(s.ctx, lbm_step(s.ctx, nsteps)); });
+    }
 
-    // solver.hpp:121-277: into the public arrays density, phase, velocity (interleaved 3*i+c)
-    void getWholeDensity() { LBM_CHECK(ctx_, lbm_get_field(ctx_, LBM_RHO, density.data(), n_)); }
-    void getWholePhase() { LBM_CHECK(ctx_, lbm_get_field(ctx_, LBM_PHASE, phase.data(), n_)); }
+    // solver.hpp:121-277: every slab's part lands at its place in the public arrays density, phase, velocity
+    // (interleaved 3*i+c) -- the gather to rank 0 of the reference
+    void getWholeDensity() { get_whole(LBM_RHO, density); }
+    void getWholePhase() { get_whole(LBM_PHASE, phase); }
     void getWholeVelocity()
     {
-        LBM_CHECK(ctx_, lbm_get_field(ctx_, LBM_UX, ux_.data(), n_));
-        LBM_CHECK(ctx_, lbm_get_field(ctx_, LBM_UY, uy_.data(), n_));
-        LBM_CHECK(ctx_, lbm_get_field(ctx_, LBM_UZ, uz_.data(), n_));
+        get_whole(LBM_UX, ux_); get_whole(LBM_UY, uy_); get_whole(LBM_UZ, uz_);
         for (size_t i = 0; i < n_; i++) { velocity[3 * i] = ux_[i]; velocity[3 * i + 1] = uy_[i]; velocity[3 * i + 2] = uz_[i]; }
     }
 
@@ -194,7 +226,7 @@ public:
         const int64_t head[6] = {0x504f50324c424dLL, NX, NY, NZ, 19, time_counter};
         out.write((const char *)head, sizeof head);
         for (int set = 0; set < 2; set++) {
-            LBM_CHECK(ctx_, lbm_get_populations(ctx_, set, pop.data(), pop.size()));
+            each_slab([&](Slab &s) { LBM_CHECK(s.ctx, lbm_get_populations(s.ctx, set, pop.data() + s.first * 19, s.count * 19)); });
             out.write((const char *)pop.data(), pop.size() * sizeof(double));
         }
     }
@@ -212,19 +244,37 @@ public:
         for (int set = 0; set < 2; set++) {
             in.read((char *)pop.data(), pop.size() * sizeof(double));
             if (!in) throw std::runtime_error("loadPopulations: file too short");
-            LBM_CHECK(ctx_, lbm_set_populations(ctx_, set, pop.data(), pop.size()));
+            // all slabs at once: setting populations also refreshes the ghost planes from the neighbours
+            each_slab([&](Slab &s) { LBM_CHECK(s.ctx, lbm_set_populations(s.ctx, set, pop.data() + s.first * 19, s.count * 19)); });
         }
         return (int)head[5];
     }
 
-    lbm_ctx *context() { return ctx_; }
+    lbm_ctx *context(int slab = 0) { return slabs_[slab].ctx; }
+    int gpus() const { return (int)slabs_.size(); }
     const int NX, NY, NZ;
     std::vector<double> density, phase, velocity;          // public in spirit: what getWhole* fill (solver.h:82-84)
 
 private:
     struct VtsArray { const char *name; int ncomp; const double *data; };
-    lbm_ctx *ctx_;
+    struct Slab { lbm_ctx *ctx; size_t first, count; };   // context of one GPU; its nodes are [first, first+count) of the grid
+    std::vector<Slab> slabs_;
     size_t n_;
+
+    // runs fn on every slab: directly with one GPU, one host thread per GPU otherwise (calls that exchange halos
+    // block until the neighbours have made the same call)
+    template <class Fn>
+    void each_slab(Fn fn)
+    {
+        if (slabs_.size() == 1) { fn(slabs_[0]); return; }
+        std::vector<std::thread> th;
+        for (size_t r = 0; r < slabs_.size(); r++) th.push_back(std::thread([this, r, &fn] { fn(slabs_[r]); }));
+        for (size_t r = 0; r < th.size(); r++) th[r].join();
+    }
+    void get_whole(int field, std::vector<double> &dst)
+    {
+        each_slab([&](Slab &s) { LBM_CHECK(s.ctx, lbm_get_field(s.ctx, field, dst.data() + s.first, s.count)); });
+    }
     std::vector<double> rho_, phi_, ux_, uy_, uz_;         // what put*/load_file fill and init() uploads
 
     size_t at(int x, int y, int z) const { return ((size_t)z * NY + y) * NX + x; }

@@ -174,3 +174,43 @@ def test_microchannel_checkpoint_restart(tmp_path):
     a, b = _read_vts(one / "phase00200.vts"), _read_vts(two / "phase00200.vts")
     for k in ("Velocity", "Phase", "Density"):
         assert np.array_equal(a[k], b[k]), k
+
+
+def _ngpu():
+    try:
+        import torch
+        return torch.cuda.device_count()
+    except Exception:
+        return 0
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs at least 2 GPUs")
+@pytest.mark.parametrize("gpus", [2, 4])
+def test_microchannel_on_several_gpus_writes_the_same_files(gpus, tmp_path):
+    """LBM_GPUS=N: the C++ drop-in spreads its grid over N GPUs of the box (one host thread and one slab context per
+    GPU, NCCL halos inside the library) -- the replacement of the reference's `mpiexec -n N` (binary.pbs:58,
+    solver.hpp:24-30, :121-277).  stdout, every .vts and the checkpoint must be byte-identical to the 1-GPU run; the
+    solver self-test (all writers, both restarts) must pass on N GPUs as well."""
+    if _ngpu() < gpus:
+        pytest.skip("needs %d GPUs" % gpus)
+    one, many = tmp_path / "one", tmp_path / "many"
+    os.mkdir(one)
+    os.mkdir(many)
+    env = {"LBM_NUMTIME": "201", "LBM_CHECKPOINT": "ck"}
+    out1 = _run("microchannel_quarter", [], str(one), env=env)
+    outn = _run("microchannel_quarter", [], str(many), env=dict(env, LBM_GPUS=str(gpus)))
+    assert out1 == outn
+    files = sorted(os.listdir(one))
+    assert files == sorted(os.listdir(many)) and "phase00200.vts" in files and "ck.pop" in files
+    for f in files:
+        assert open(one / f, "rb").read() == open(many / f, "rb").read(), f
+    # continue the N-GPU checkpoint on one GPU and the other way round: same files again
+    for src, dst, g in ((many, one, "1"), (one, many, str(gpus))):
+        _run("microchannel_quarter", [], str(dst), env={"LBM_NUMTIME": "301", "LBM_RESTART": str(src / "ck"), "LBM_GPUS": g})
+    assert open(one / "phase00300.vts", "rb").read() == open(many / "phase00300.vts", "rb").read()
+    st = tmp_path / "selftest"
+    os.mkdir(st)
+    out = _run("solver_selftest", [], str(st), env={"LBM_GPUS": str(gpus)})
+    assert "solver_selftest OK" in out
+    for name, sha in REFERENCE_TEXT_FILES.items():
+        assert _sha16(st / name) == sha, name
