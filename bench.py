@@ -33,11 +33,12 @@ def parse():
     ap.add_argument("--nx", type=int, default=512)
     ap.add_argument("--ny", type=int, default=512)
     ap.add_argument("--nz-per-gpu", type=int, default=512)
-    ap.add_argument("--variant", type=int, default=0, help="kernel_variant (0 default, 1 plain two-kernel path)")
+    ap.add_argument("--variant", type=int, default=0, help="kernel_variant (0 default: one-pass step; 5 two-pass with interior + rim kernels; 1 two-pass, plain kernel)")
     ap.add_argument("--e2e-steps", type=int, default=100, help="lattice steps per end-to-end segment (QuarterChannel NUMOUTPUT)")
     ap.add_argument("--precision", default="f64", choices=["f64", "f32"], help="f32: liblbm_b200_f32.so, populations stored as float (not the parity build; the headline is f64)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the bit-equality check of the multi-GPU path (N > 1 only)")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     return ap.parse_args()
 
@@ -116,18 +117,16 @@ def reference_arm(args, rank):
         return
     ranks = host_ranks()
     nx, ny, nz = cpu_sample_grid(ranks)
-    # the same config block as our arm prints for this --gpus (the job the numbers are about); the reference's CPU
-    # code runs a bounded sample of it, named in `sample`
+    # `config` is the grid the reference's CPU code actually runs here: a bounded sample of the job our arm runs
+    # for this --gpus (same program, same parameters, smaller cross-section and fewer planes); the job is named in `sample_of`
     world = max(1, args.gpus)
     if args.workload == "full":
-        wl = "Microchannel3D/FullChannel 92x52x1500 (BASELINE.json configs[3]), z-slabs over %d GPU(s)" % world
-        jx, jy, jz = 92, 52, 1500
+        job = "Microchannel3D/FullChannel 92x52x1500 (BASELINE.json configs[3]), z-slabs over %d GPU(s)" % world
     else:
-        jx, jy, jz = args.nx, args.ny, args.nz_per_gpu * world
-        wl = "Microchannel3D/QuarterChannel scaled to %dx%dx%d (%d planes per GPU; BASELINE.json configs[4])" % (jx, jy, jz, args.nz_per_gpu)
-    cfg = {"workload": wl, "nx": jx, "ny": jy, "nz": jz, "nodes": jx * jy * jz, "precision": "fp64",
-           "sample": "the unmodified reference Lattice/Solver on a %dx%dx%d sample of that job, %d host ranks (mini-MPI z-slabs)" % (nx, ny, nz, ranks),
-           "host_ranks": ranks}
+        job = "Microchannel3D/QuarterChannel scaled to %dx%dx%d (%d planes per GPU; BASELINE.json configs[4])" % (
+            args.nx, args.ny, args.nz_per_gpu * world, args.nz_per_gpu)
+    cfg = {"workload": "Microchannel3D/QuarterChannel Lattice/Solver (unmodified reference) on %dx%dx%d, %d host ranks (mini-MPI z-slabs)" % (nx, ny, nz, ranks),
+           "nx": nx, "ny": ny, "nz": nz, "nodes": nx * ny * nz, "precision": "fp64", "sample_of": job, "host_ranks": ranks}
     if ref_binary():
         r = run_reference_cpu(nx, ny, nz, args.warmup, args.steps, ranks)
         kind, val, sec = "reference", r["mlups"], r["seconds"]
@@ -239,6 +238,74 @@ class quiet_stdout:
         os.close(self.saved)
 
 
+def multi_gpu_parity(api, dist, torch, np, args, rank, world, local_rank):
+    """Bit-equality check of the path the timed region runs at N > 1 -- lbm_comm_attach, then lbm_init / lbm_step with
+    the NCCL halo exchange overlapped with the collision (Slab3D::step_overlapped) -- against ONE slab holding the whole
+    grid on rank 0's GPU (the reference's own property: 1 rank == N ranks bit for bit, solver.hpp:893-928,
+    lattice.hpp:809-840).  Small grid, 12 planes per rank so that the overlapped branch is the one taken."""
+    nx, ny, nzl, steps, width = 35, 18, 12, 9, 4
+    nz = nzl * world
+    params = (0.04, 0.04, 1.0, 0.03, 0.5, 2.0, 2.5, 0.7)     # a, k, gamma, wall gradient, rho_wall, tau_phi, tau_liq, tau_gas
+    force = (1e-5, 0.0, 3e-5)
+
+    def make(slab_rank, slab_count):
+        c = api.microchannel_config("quarter", nx, ny, nz, device=local_rank, slab_rank=slab_rank, slab_count=slab_count)
+        c.aconst, c.kconst, c.gammaconst, c.wall_gradient, c.rho_wall, c.tau_phi, c.tau_liq, c.tau_gas = params
+        c.force[0], c.force[1], c.force[2] = force
+        c.kernel_variant = args.variant
+        return api.Context(c, args.precision)
+
+    rng = np.random.default_rng(11)
+    n = nx * ny * nz
+    x = np.arange(nx)[None, None, :] <= nx - width - 1
+    y = np.arange(ny)[None, :, None] <= ny - width - 1
+    z = np.arange(nz)[:, None, None]
+    ph = np.where(x & y & (z >= (nz - 1) // 3) & (z <= 2 * (nz - 1) // 3), -1.0, 1.0).reshape(-1)
+    flds = [1 + 0.05 * rng.standard_normal(n), np.clip(ph + 0.3 * rng.standard_normal(n), -1.2, 1.2),
+            0.01 * rng.standard_normal(n), 0.01 * rng.standard_normal(n), 0.01 * rng.standard_normal(n)]
+    names = ("rho", "phase", "ux", "uy", "uz")
+
+    ctx = make(rank, world)
+    with quiet_stdout():
+        uid = [api.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        ctx.comm_attach(uid[0])
+    z0, nl = ctx.slab_extent()
+    pl = nx * ny
+    for name, a in zip(names, flds):
+        ctx.set_field(name, a[z0 * pl:(z0 + nl) * pl])
+    ctx.init()
+    ctx.step(steps)
+    mine = [ctx.get_field(k) for k in names] + [ctx.get_populations(0).ravel(), ctx.get_populations(1).ravel()]
+    fb = ctx.phase_fallbacks
+    ctx.close()
+    parts = [None] * world if rank == 0 else None
+    dist.gather_object(mine, parts, dst=0)
+    res = None
+    if rank == 0:
+        one = make(0, 1)
+        for name, a in zip(names, flds):
+            one.set_field(name, a)
+        one.init()
+        one.step(steps)
+        want = [one.get_field(k) for k in names] + [one.get_populations(0).ravel(), one.get_populations(1).ravel()]
+        one.close()
+        ndiff = 0
+        for i, w in enumerate(want):
+            got = np.concatenate([p[i] for p in parts])
+            ndiff += int(np.count_nonzero(~((got == w) | (np.isnan(got) & np.isnan(w)))))
+        res = {"grid": "%dx%dx%d" % (nx, ny, nz), "slabs": world, "steps": steps, "path": "lbm_comm_attach + lbm_init + lbm_step (NCCL, overlapped)",
+               "compared": "rho, phase, ux, uy, uz, f, g against one slab on one GPU", "values": int(sum(w.size for w in want)),
+               "ndiff": ndiff, "phase_fallbacks": fb}
+    flag = torch.tensor([0 if res is None else res["ndiff"]], dtype=torch.int64, device="cuda")
+    dist.broadcast(flag, src=0)
+    if int(flag.item()) != 0:
+        if rank == 0:
+            sys.stderr.write("bench.py: multi-GPU parity check FAILED: %s\n" % json.dumps(res))
+        sys.exit(3)
+    return res
+
+
 def ours(args, rank, world, local_rank):
     import numpy as np
     import torch
@@ -253,6 +320,10 @@ def ours(args, rank, world, local_rank):
         with quiet_stdout():
             dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
             dist.barrier()
+
+    parity = None
+    if world > 1 and not args.no_parity:
+        parity = multi_gpu_parity(api, dist, torch, np, args, rank, world, local_rank)
 
     if args.workload == "full":
         nx, ny, nz, width, which = 92, 52, 1500, 8, "full"
@@ -313,7 +384,6 @@ def ours(args, rank, world, local_rank):
     clocks = ClockSampler(local_rank)
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     launches0 = ctx.launch_count
-    ctx.profile(True)
     clocks.start()
     barrier()
     ev0.record(stream)
@@ -322,9 +392,15 @@ def ours(args, rank, world, local_rank):
     barrier()
     clk = clocks.stop()
     ms = ev0.elapsed_time(ev1)
+    launches = ctx.launch_count - launches0
+    fallbacks = ctx.phase_fallbacks
+    # per-kernel split: a second, untimed-for-the-headline pass with one CUDA event pair around every launch
+    psteps = min(args.steps, 20)
+    ctx.profile(True)
+    ctx.step(psteps)
+    barrier()
     prof = ctx.profile_report()
     ctx.profile(False)
-    launches = ctx.launch_count - launches0
     t = torch.tensor([ms], dtype=torch.float64, device="cuda")
     if dist is not None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -332,33 +408,40 @@ def ours(args, rank, world, local_rank):
     total_nodes = nx * ny * nz
     value = total_nodes * args.steps / (ms_max * 1e-3) / 1e6
 
-    # dominant kernel: the one with the largest share of the profiled time
-    roof = None
+    # roofline: the whole step first (what the MLUPS figure means in bytes), then the dominant kernel
+    peak, which_peak = peaks()
+    step_achieved = value * 1e6 * b_alg / world / 1e9          # GB/s per GPU on the algorithmic-bytes basis
+    roof = {"bound": "hbm", "peak": peak, "unit": "GB/s", "peak_source": which_peak,
+            "step_achieved": step_achieved, "step_frac": step_achieved / peak,
+            "algorithmic_bytes_per_lattice_update": b_alg}
     if prof:
         name = max(prof, key=lambda k: prof[k]["ms"])
-        # one launch covers the whole slab on one GPU; the overlapped multi-GPU step cuts the same kernel
-        # into three launches (both slab ends, then the planes between), so bytes and time are per launch
-        # with launches_per_step launches making up one pass over the slab
-        launches_per_step = prof[name]["launches"] / args.steps
+        launches_per_step = prof[name]["launches"] / psteps
         per_launch_ms = prof[name]["ms"] / prof[name]["launches"]
-        peak, which_peak = peaks()
-        achieved = b_alg * nloc / launches_per_step / (per_launch_ms * 1e-3) / 1e9
-        traffic = None
+        # nodes one launch of the dominant kernel updates: the collide kernels take every bulk node except the rim
+        # rows iY = 1, NY-2 (those go to k_collide_rim) of nz_local + 2 planes (the two redundantly collided ghost
+        # planes are work the slab design adds, not lattice updates: they are NOT counted)
+        launch_nodes = (nx - 2) * (ny - 4) * nz_local / launches_per_step if name in ("k_collide_lag", "k_collide_interior") else nloc / launches_per_step
+        achieved = b_alg * launch_nodes / (per_launch_ms * 1e-3) / 1e9
+        traffic = step_traffic = None
         tp = os.path.join(ROOT, "profiles", "traffic.json")
-        if os.path.exists(tp):
-            traffic = json.load(open(tp)).get(name, {}).get("dram_bytes_per_lattice_update")
-            if traffic is not None:
-                traffic = traffic * nloc / launches_per_step if args.precision == "f64" else None   # the ncu capture is of the fp64 build
-        roof = {"bound": "hbm", "kernel": name, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": traffic, "peak_source": which_peak, "algorithmic_bytes_per_launch": b_alg * nloc / launches_per_step,
-                "launches_per_step": launches_per_step, "avg_launch_ms": per_launch_ms, "share_of_step": prof[name]["ms"] / sum(v["ms"] for v in prof.values()),
-                "kernels": prof}
+        if os.path.exists(tp) and args.precision == "f64" and (nx, ny, nz_local) == (512, 512, 512):
+            tj = json.load(open(tp)).get("kernels", {})
+            if name in tj:      # only a capture of this very kernel counts
+                traffic = tj[name]["dram_bytes_per_launch"]
+            if all(k in tj for k in prof):
+                step_traffic = sum(tj[k]["dram_bytes_per_launch"] * prof[k]["launches"] / psteps for k in prof)
+        roof.update({"kernel": name, "achieved": achieved, "frac": achieved / peak, "traffic": traffic,
+                     "algorithmic_bytes_per_launch": b_alg * launch_nodes, "launches_per_step": launches_per_step,
+                     "avg_launch_ms": per_launch_ms, "share_of_step": prof[name]["ms"] / sum(v["ms"] for v in prof.values()),
+                     "step_traffic": step_traffic, "step_traffic_per_lattice_update": step_traffic / nloc if step_traffic else None,
+                     "kernels": prof, "profiled_steps": psteps})
 
     # every rank's own view (the step time above is the max over ranks; a slab waits for its neighbours, so
     # one slow GPU sets the pace): kernel time per step, wall per step, median SM clock
     per_rank = None
     if dist is not None:
-        mine = torch.tensor([sum(v["ms"] for v in prof.values()) / args.steps if prof else 0.0, ms / args.steps,
+        mine = torch.tensor([sum(v["ms"] for v in prof.values()) / psteps if prof else 0.0, ms / args.steps,
                              float(clk.get("sm_mhz") or 0)], dtype=torch.float64, device="cuda")
         allr = [torch.zeros_like(mine) for _ in range(world)]
         dist.all_gather(allr, mine)
@@ -373,7 +456,7 @@ def ours(args, rank, world, local_rank):
         upload_and_init()
         ctx.step(S)
         for name in ("rho", "phase", "ux", "uy", "uz"):
-            ctx.get_field(name, host[name][1])
+            ctx.get_field_async(name, host[name][0])
         barrier()
         dt = time.perf_counter() - t0
         tt = torch.tensor([dt], dtype=torch.float64, device="cuda")
@@ -381,7 +464,7 @@ def ours(args, rank, world, local_rank):
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         dt = float(tt.item())
         e2e = {"value": total_nodes * S / dt / 1e6, "unit": "MLUPS", "h2d_bytes_per_step": 5 * 8 * nloc / S,
-               "d2h_bytes_per_step": 5 * 8 * nloc / S, "segment": "lbm_set_field x5 (pinned host) + lbm_init + lbm_step(%d) + lbm_get_field x5" % S,
+               "d2h_bytes_per_step": 5 * 8 * nloc / S, "segment": "lbm_set_field x5 (pinned host) + lbm_init + lbm_step(%d) + lbm_get_field_async x5 + lbm_sync" % S,
                "seconds": dt}
 
     cb = None
@@ -392,15 +475,17 @@ def ours(args, rank, world, local_rank):
             cb = {"value": None, "unit": "MLUPS", "cores": 0, "kind": "unavailable", "sample": str(e)[:200]}
 
     if rank == 0:
-        line = {"metric": "MLUPS (aggregate), D3Q19 binary-liquid collide-stream, fp64", "value": value, "unit": "MLUPS",
-                "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_max / args.steps,
-                "higher_is_better": True, "scaling": scaling, "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        line = {"metric": "MLUPS (aggregate), D3Q19 binary-liquid collide-stream, %s" % ("fp64" if args.precision == "f64" else "fp64 arithmetic on fp32-stored populations"),
+                "value": value, "unit": "MLUPS", "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_max / args.steps,
+                "higher_is_better": True, "scaling": scaling, "vs_baseline": None, "dtype": "f64" if args.precision == "f64" else "f64 (populations stored as f32)", "data": "synthetic",
                 "config": {"workload": wl, "nx": nx, "ny": ny, "nz": nz, "nodes": total_nodes,
                            "precision": "fp64" if args.precision == "f64" else "fp32 storage of the populations, fp64 arithmetic and fields (not the parity build)",
                            "kernel_variant": args.variant, "l2": "inputs (%.1f GB of populations per GPU) exceed the 126 MB L2" % (nloc * b_alg / 2 / 1e9),
                            "parallelism": "z-slab x%d" % world},
                 "mlups_per_gpu": value / world, "roofline": roof, "cpu_baseline": cb, "e2e": e2e, "clocks": clk,
-                "gpu_launches": launches}
+                "gpu_launches": launches, "phase_fallbacks": fallbacks}
+        if parity is not None:
+            line["parity"] = parity
         if per_rank:
             line["per_rank"] = per_rank
         print(json.dumps(line), flush=True)

@@ -69,6 +69,7 @@ def load_library(precision="f64"):
         "lbm_local_nodes": (sz, [vp]),
         "lbm_set_field": (ci, [vp, ci, vp, sz]),
         "lbm_get_field": (ci, [vp, ci, vp, sz]),
+        "lbm_get_field_async": (ci, [vp, ci, vp, sz]),
         "lbm_set_geometry": (ci, [vp, vp, sz]),
         "lbm_init": (ci, [vp]),
         "lbm_set_populations": (ci, [vp, ci, vp, sz]),
@@ -79,6 +80,8 @@ def load_library(precision="f64"):
         "lbm_get_stream": (vp, [vp]),
         "lbm_set_stream": (ci, [vp, vp]),
         "lbm_launch_count": (C.c_ulonglong, [vp]),
+        "lbm_population_bytes": (ci, [vp]),
+        "lbm_phase_fallbacks": (C.c_ulonglong, [vp]),
         "lbm_profile": (ci, [vp, ci]),
         "lbm_profile_report": (ci, [vp, C.c_char_p, sz]),
         "lbm_host_alloc": (vp, [sz]),
@@ -102,7 +105,7 @@ def load_library(precision="f64"):
 
 
 EXPORTS = ["lbm_config_default", "lbm_create", "lbm_destroy", "lbm_last_error", "lbm_slab_extent", "lbm_local_nodes",
-           "lbm_set_field", "lbm_get_field", "lbm_set_geometry", "lbm_init", "lbm_set_populations", "lbm_get_populations", "lbm_step",
+           "lbm_set_field", "lbm_get_field", "lbm_get_field_async", "lbm_population_bytes", "lbm_phase_fallbacks", "lbm_set_geometry", "lbm_init", "lbm_set_populations", "lbm_get_populations", "lbm_step",
            "lbm_sync", "lbm_diagnostics", "lbm_get_stream", "lbm_set_stream", "lbm_launch_count", "lbm_profile",
            "lbm_profile_report", "lbm_host_alloc",
            "lbm_host_free", "lbm_comm_unique_id", "lbm_comm_attach", "lbm_slab_halo", "lbm_slab_init_fields",
@@ -185,6 +188,10 @@ class Context:
         self._ck(self.L.lbm_get_field(self.h, FIELDS[field] if isinstance(field, str) else field, _ptr(out), self.local_nodes))
         return out
 
+    def get_field_async(self, field, host_addr):
+        """Queues the copy into page-locked host memory at `host_addr`; valid after sync()."""
+        self._ck(self.L.lbm_get_field_async(self.h, FIELDS[field] if isinstance(field, str) else field, _ptr(host_addr), self.local_nodes))
+
     def init(self):
         self._ck(self.L.lbm_init(self.h))
 
@@ -221,6 +228,14 @@ class Context:
     def launch_count(self):
         return int(self.L.lbm_launch_count(self.h))
 
+    @property
+    def population_bytes(self):
+        return int(self.L.lbm_population_bytes(self.h))
+
+    @property
+    def phase_fallbacks(self):
+        return int(self.L.lbm_phase_fallbacks(self.h))
+
     def profile(self, enable=True):
         self._ck(self.L.lbm_profile(self.h, int(bool(enable))))
 
@@ -236,9 +251,12 @@ class Context:
         self._ck(self.L.lbm_comm_attach(self.h, buf))
 
     def slab_halo(self, name):
+        """(device address, element count, bytes per element) of one halo message: F/G messages are made of
+        population values (8 bytes; 4 in the fp32-storage build), PHI messages of doubles."""
         p, n = C.c_void_p(), C.c_size_t()
-        self._ck(self.L.lbm_slab_halo(self.h, HALO[name] if isinstance(name, str) else name, C.byref(p), C.byref(n)))
-        return p.value, n.value
+        hid = HALO[name] if isinstance(name, str) else name
+        self._ck(self.L.lbm_slab_halo(self.h, hid, C.byref(p), C.byref(n)))
+        return p.value, n.value, (8 if hid >= HALO["S_PHI_UP"] else self.population_bytes)
 
     def slab_init_fields(self):
         self._ck(self.L.lbm_slab_init_fields(self.h))

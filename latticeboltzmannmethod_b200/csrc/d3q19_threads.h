@@ -36,14 +36,12 @@ LBM_HD long long pop_index(const Geom &g, int zs, int k, long long idx) { return
 // the permuted copy), :75-106 (wall nodes: inner neighbour - phase_gradient).
 // The thread of bulk node (ix,iy) also writes the mirror/wall nodes whose inner
 // neighbour it is, so no second pass is needed.
-LBM_HD void phase_thread(const Geom &g, const Params &P, const pop_t *gpop, double *phi, int zs, int ix, int iy)
+// phase field of bulk node (ix,iy) of plane zs from its 19 g populations already in registers (G), incl. the
+// mirror / wall nodes this node is the inner neighbour of
+LBM_HD void phase_node(const Geom &g, const Params &P, const double *G, double *phi, int zs, int ix, int iy)
 {
     const int NX = g.nx, NY = g.ny;
-    if (ix < 1 || ix > NX - 2 || iy < 1 || iy > NY - 2) return;
     const long long idx = (long long)iy * NX + ix;
-    double G[19];
-#pragma unroll
-    for (int k = 0; k < 19; k++) G[k] = gpop[pop_index(g, zs, k, idx)];
     double *ph = phi + (long long)zs * g.pl;
     const double own = sum19(G);
     ph[idx] = own;
@@ -62,6 +60,17 @@ LBM_HD void phase_thread(const Geom &g, const Params &P, const pop_t *gpop, doub
         if (yhi) ph[idx + NX - 1] = m - P.phase_gradient;
     }
     if (xlo && ylo) ph[idx - NX - 1] = sum19_mirror<3>(G);
+}
+
+LBM_HD void phase_thread(const Geom &g, const Params &P, const pop_t *gpop, double *phi, int zs, int ix, int iy)
+{
+    const int NX = g.nx, NY = g.ny;
+    if (ix < 1 || ix > NX - 2 || iy < 1 || iy > NY - 2) return;
+    const long long idx = (long long)iy * NX + ix;
+    double G[19];
+#pragma unroll
+    for (int k = 0; k < 19; k++) G[k] = gpop[pop_index(g, zs, k, idx)];
+    phase_node(g, P, G, phi, zs, ix, iy);
 }
 
 // ---- push of one post-collision population -------------------------------
@@ -119,9 +128,13 @@ LBM_HD void mirror_fields(const double *F, const Params &P, const FieldsOut &o, 
 // folded boundary push); 3: a node with 2 <= iY <= NY-3 and any bulk iX -- the x mirror line (iX = 1) and
 // the x wall (iX = NX-2) are folded in as an address select on the ten directions with cx != 0, so that
 // these two columns are stored by the same coalesced warps as their row neighbours.
-template <bool FXY, bool WRITE, int PART = 0, bool TRT = false>
+struct PlainStore {   // how the interior push writes a value: plain stores (kernels may pass cache-hinted ones)
+    LBM_HD void f(pop_t *p, double v) const { *p = (pop_t)v; }
+    LBM_HD void g(pop_t *p, double v) const { *p = (pop_t)v; }
+};
+template <bool FXY, bool WRITE, int PART = 0, bool TRT = false, class ST = PlainStore>
 LBM_HD void collide_push_node(const Geom &g, const Params &P, double *F, double *G, const double *PH, pop_t *fout,
-                              pop_t *gout, const FieldsOut &o, int zs, int ix, int iy)
+                              pop_t *gout, const FieldsOut &o, int zs, int ix, int iy, const ST &st = ST())
 {
     const int NX = g.nx, NY = g.ny;
     const long long idx = (long long)iy * NX + ix;
@@ -156,8 +169,8 @@ LBM_HD void collide_push_node(const Geom &g, const Params &P, double *F, double 
                 const long long tb = pop_index(g, zs, OPP[k], idx);
                 t = xhi ? tb : t;
             }
-            fout[t] = F[k];
-            gout[t] = G[k];
+            st.f(fout + t, F[k]);
+            st.g(gout + t, G[k]);
         }
     } else {
         for (int k = 0; k < 19; k++) push_border(g, fout, gout, zs, ix, iy, k, F[k], G[k]);

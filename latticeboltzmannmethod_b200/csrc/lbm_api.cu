@@ -125,6 +125,7 @@ void lbm_destroy(lbm_ctx *ctx)
     if (ctx->bound) cudaSetDevice(ctx->rt.device);     // a context whose device never existed owns nothing on it
     if (ctx->rt.stream) cudaStreamSynchronize(ctx->rt.stream);
     delete ctx->model;
+    ctx->rt.profile_release();
     if (ctx->rt.own_stream && ctx->rt.stream) cudaStreamDestroy(ctx->rt.stream);
     delete ctx;
 }
@@ -163,6 +164,13 @@ lbm_status lbm_get_field(lbm_ctx *ctx, int field, double *host, size_t n)
     LBM_ENTER(ctx);
     if (!host || n != ctx->model->local_nodes()) return ctx->rt.fail(LBM_EINVAL, "lbm_get_field: n must equal lbm_local_nodes()");
     return ctx->model->get_field(field, host);
+}
+
+lbm_status lbm_get_field_async(lbm_ctx *ctx, int field, double *host, size_t n)
+{
+    LBM_ENTER(ctx);
+    if (!host || n != ctx->model->local_nodes()) return ctx->rt.fail(LBM_EINVAL, "lbm_get_field_async: n must equal lbm_local_nodes()");
+    return ctx->model->get_field_async(field, host);
 }
 
 lbm_status lbm_init(lbm_ctx *ctx)
@@ -224,11 +232,18 @@ lbm_status lbm_set_stream(lbm_ctx *ctx, void *stream)
 }
 
 unsigned long long lbm_launch_count(const lbm_ctx *ctx) { return ctx ? ctx->rt.launches : 0; }
+int lbm_population_bytes(const lbm_ctx *ctx) { return ctx && ctx->model ? ctx->model->pop_bytes() : 0; }
+unsigned long long lbm_phase_fallbacks(lbm_ctx *ctx)
+{
+    if (!have_ctx(ctx) || bind_device(ctx) != LBM_OK) return 0;
+    return ctx->model->fallbacks();
+}
 
 lbm_status lbm_profile(lbm_ctx *ctx, int enable)
 {
     LBM_ENTER(ctx);
     ctx->rt.profile = enable != 0;
+    if (!enable) ctx->rt.profile_release();   // also drops a record nobody asked the report of
     return LBM_OK;
 }
 

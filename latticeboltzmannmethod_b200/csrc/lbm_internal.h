@@ -38,23 +38,39 @@ struct Runtime {
         return e == cudaErrorMemoryAllocation ? LBM_ENOMEM : LBM_ECUDA;
     }
     // call right before / right after a kernel launch
+    std::vector<cudaEvent_t> spare;   // events of collected records, reused: no cudaEventCreate in steady state
+    cudaEvent_t take_event()
+    {
+        cudaEvent_t e = nullptr;
+        if (!spare.empty()) { e = spare.back(); spare.pop_back(); }
+        else cudaEventCreate(&e);
+        return e;
+    }
     void about_to_launch()
     {
         if (!profile) return;
-        cudaEventCreate(&pending_start);
+        if (!pending_start) pending_start = take_event();
         cudaEventRecord(pending_start, stream);
     }
     lbm_status launched(const char *kernel)
     {
         ++launches;
         if (profile && pending_start) {
-            cudaEvent_t t1;
-            cudaEventCreate(&t1);
+            cudaEvent_t t1 = take_event();
             cudaEventRecord(t1, stream);
             timed.push_back(Timed{kernel, pending_start, t1});
             pending_start = nullptr;
         }
         return cuda(cudaGetLastError(), kernel);
+    }
+    // drops every recorded and spare event (profiling switched off, context destroyed)
+    void profile_release()
+    {
+        for (auto &t : timed) { spare.push_back(t.t0); spare.push_back(t.t1); }
+        timed.clear();
+        if (pending_start) { spare.push_back(pending_start); pending_start = nullptr; }
+        for (auto e : spare) cudaEventDestroy(e);
+        spare.clear();
     }
     // synchronises, sums the recorded durations per kernel name, releases the events
     std::map<std::string, std::pair<int, double>> profile_collect()
@@ -68,8 +84,8 @@ struct Runtime {
                 e.first += 1;
                 e.second += ms;
             }
-            cudaEventDestroy(t.t0);
-            cudaEventDestroy(t.t1);
+            spare.push_back(t.t0);
+            spare.push_back(t.t1);
         }
         timed.clear();
         return out;
@@ -93,6 +109,10 @@ public:
     virtual lbm_status set_field(int field, const double *host) = 0;
     virtual lbm_status set_geometry(const int *) { return LBM_EINVAL; }  // masked models only
     virtual lbm_status get_field(int field, double *host) = 0;
+    // queues the copy only (valid after the next lbm_sync); models without an asynchronous form copy and wait
+    virtual lbm_status get_field_async(int field, double *host) { return get_field(field, host); }
+    virtual int pop_bytes() const { return (int)sizeof(double); }      // storage size of one population value
+    virtual unsigned long long fallbacks() { return 0; }               // steps whose phase field had to be recomputed
     virtual lbm_status init() = 0;
     virtual lbm_status step(int nsteps) = 0;
     virtual lbm_status set_populations(int set, const double *host_aos) = 0;

@@ -7,7 +7,8 @@ the CPU tests).  It replaces Solver::updatePhase and Solver::propagate (Microcha
 893-928) and follows the same call order as the library's own ``lbm_init`` / ``lbm_step``.
 
 `engine` is anything with the slab phase methods of :class:`latticeboltzmannmethod_b200.api.Context`;
-`tensor_of(ptr, count)` turns one halo message into a 1-D float64 tensor that aliases it.
+`tensor_of(ptr, count, elem_bytes)` turns one halo message into a 1-D tensor (float64, or float32 for the
+population messages of the fp32-storage build) that aliases it.
 """
 import torch
 import torch.distributed as dist
@@ -24,10 +25,10 @@ def slab_bounds(nz, rank, world):
     return z0, z1 - z0 + 1
 
 
-def cuda_tensor_of(ptr, count):
-    """A float64 CUDA tensor aliasing `count` doubles of device memory at `ptr`."""
+def cuda_tensor_of(ptr, count, elem_bytes=8):
+    """A CUDA tensor aliasing `count` values of `elem_bytes` bytes (8: float64, 4: float32) of device memory at `ptr`."""
     class _Mem:
-        __cuda_array_interface__ = {"shape": (count,), "typestr": "<f8", "data": (ptr, False), "version": 2}
+        __cuda_array_interface__ = {"shape": (count,), "typestr": "<f%d" % elem_bytes, "data": (ptr, False), "version": 2}
     return torch.as_tensor(_Mem(), device="cuda")
 
 

@@ -83,7 +83,7 @@ def _free_port():
 
 
 @pytest.mark.skipif(_ngpu() < 2, reason="needs at least 2 GPUs")
-@pytest.mark.parametrize("transport,precision", [("nccl", "f64"), ("torch", "f64"), ("nccl", "f32")])
+@pytest.mark.parametrize("transport,precision", [("nccl", "f64"), ("torch", "f64"), ("nccl", "f32"), ("torch", "f32")])
 def test_slab_ring_on_gpus_equals_one_gpu(transport, precision, tmp_path):
     """f32: the fp32-storage build sends float halo messages; its slab ring must equal its own one-GPU run."""
     import torch.multiprocessing as mp

@@ -51,7 +51,7 @@ def _worker(rank, world, port, out_dir):
     pl = NX * NY
     eng = OracleSlabEngine(NX, NY, nzl, PARAMS)
     eng.o.set_fields(*[f[z0 * pl:(z0 + nzl) * pl] for f in _fields()])
-    drv = SlabDriver(eng, rank, world, tensor_of=lambda a, n: torch.from_numpy(a))
+    drv = SlabDriver(eng, rank, world, tensor_of=lambda a, n, eb=8: torch.from_numpy(a))
     drv.init()
     snaps = {"init": eng.o.fields()}
     drv.step(1)
