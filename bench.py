@@ -38,6 +38,7 @@ def parse():
     ap.add_argument("--precision", default="f64", choices=["f64", "f32"], help="f32: liblbm_b200_f32.so, populations stored as float (not the parity build; the headline is f64)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-secondary", action="store_true", help="skip the 2-D models (N = 1) / the FullChannel strong-scaling point (N > 1)")
     ap.add_argument("--no-parity", action="store_true", help="skip the bit-equality check of the multi-GPU path (N > 1 only)")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     return ap.parse_args()
@@ -306,6 +307,44 @@ def multi_gpu_parity(api, dist, torch, np, args, rank, world, local_rank):
     return res
 
 
+def strong_scaling_point(api, dist, torch, args, rank, world, local_rank, peak):
+    """FullChannel 92x52x1500 (BASELINE.json configs[3]) over the `world` GPUs of this run: the fixed-size job of the
+    reference's own 32-rank script (binary.pbs:58), timed like the headline (CUDA events, max over ranks)."""
+    nx, ny, nz, steps, warm = 92, 52, 1500, 200, 20
+    cfg = api.microchannel_config("full", nx, ny, nz, device=local_rank, slab_rank=rank, slab_count=world)
+    cfg.kernel_variant = args.variant
+    ctx = api.Context(cfg, args.precision)
+    with quiet_stdout():
+        uid = [api.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        ctx.comm_attach(uid[0])
+    z0, nzl = ctx.slab_extent()
+    import numpy as np
+    flds = {"rho": np.ones(nx * ny * nzl), "phase": slab_initial_fields(api, nx, ny, nz, z0, nzl, 8, np)}
+    for k in ("ux", "uy", "uz"):
+        flds[k] = np.zeros(nx * ny * nzl)
+    for k, a in flds.items():
+        ctx.set_field(k, a)
+    ctx.init()
+    ctx.step(warm)
+    stream = torch.cuda.ExternalStream(ctx.stream)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ctx.sync(); torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
+    ev0.record(stream)
+    ctx.step(steps)
+    ev1.record(stream)
+    ctx.sync(); torch.cuda.synchronize(); dist.barrier()
+    t = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item()) / steps
+    fb = ctx.phase_fallbacks
+    ctx.close()
+    mlups = nx * ny * nz / ms / 1e3
+    return {"workload": "Microchannel3D/FullChannel 92x52x1500 (BASELINE.json configs[3]), z-slabs over %d GPUs" % world,
+            "scaling": "strong", "steps": steps, "warmup": warm, "ms_per_step": ms, "value": mlups, "unit": "MLUPS",
+            "frac_of_measured_hbm_per_gpu": mlups * 1e6 * B_ALG / world / 1e9 / peak, "phase_fallbacks": fb}
+
+
 def ours(args, rank, world, local_rank):
     import numpy as np
     import torch
@@ -421,7 +460,7 @@ def ours(args, rank, world, local_rank):
         # nodes one launch of the dominant kernel updates: the collide kernels take every bulk node except the rim
         # rows iY = 1, NY-2 (those go to k_collide_rim) of nz_local + 2 planes (the two redundantly collided ghost
         # planes are work the slab design adds, not lattice updates: they are NOT counted)
-        launch_nodes = (nx - 2) * (ny - 4) * nz_local / launches_per_step if name in ("k_collide_lag", "k_collide_interior") else nloc / launches_per_step
+        launch_nodes = (nx - 2) * (ny - 4) * nz_local / launches_per_step if name in ("k_collide_lag", "k_collide_interior", "k_step_one", "k_collide_core") else nloc / launches_per_step
         achieved = b_alg * launch_nodes / (per_launch_ms * 1e-3) / 1e9
         traffic = step_traffic = None
         tp = os.path.join(ROOT, "profiles", "traffic.json")
@@ -467,6 +506,26 @@ def ours(args, rank, world, local_rank):
                "d2h_bytes_per_step": 5 * 8 * nloc / S, "segment": "lbm_set_field x5 (pinned host) + lbm_init + lbm_step(%d) + lbm_get_field_async x5 + lbm_sync" % S,
                "seconds": dt}
 
+    # ---- the other configurations of BASELINE.json, outside the headline's timed region ----
+    secondary = None
+    if rank == 0 and world == 1 and not args.no_secondary:
+        ctx.close()            # give the 87 GB of the headline run back first
+        ctx = None
+        try:
+            sys.path.insert(0, os.path.join(ROOT, "tools"))
+            import bench2d
+            sc = ClockSampler(local_rank)
+            sc.start()
+            models = bench2d.measure(8192, 20, alternatives=False, peak=peak)
+            secondary = {"what": "the D2Q9 programs on a synthetic 8192x8192 grid (BASELINE.json configs[0..2] + the two widened models), "
+                                 "20 steps each after 5 warm-up steps, CUDA events on the library's stream, fp64",
+                         "models": models, "clocks": sc.stop()}
+        except Exception as e:
+            secondary = {"error": str(e)[:300]}
+    strong = None
+    if world > 1 and args.workload == "quarter" and not args.no_secondary:
+        strong = strong_scaling_point(api, dist, torch, args, rank, world, local_rank, peak)
+
     cb = None
     if rank == 0 and world == 1 and not args.no_cpu:
         try:
@@ -486,10 +545,15 @@ def ours(args, rank, world, local_rank):
                 "gpu_launches": launches, "phase_fallbacks": fallbacks}
         if parity is not None:
             line["parity"] = parity
+        if secondary is not None:
+            line["secondary"] = secondary
+        if strong is not None:
+            line["strong"] = strong
         if per_rank:
             line["per_rank"] = per_rank
         print(json.dumps(line), flush=True)
-    ctx.close()
+    if ctx is not None:
+        ctx.close()
     for ptr, _ in host.values():
         L.lbm_host_free(ptr)
     if dist is not None:

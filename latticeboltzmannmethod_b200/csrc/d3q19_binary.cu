@@ -10,7 +10,7 @@
 
 #include <mutex>
 
-#include "d3q19_lag.cuh"
+#include "d3q19_step.cuh"
 #include "d3q19_threads.h"
 #include "lbm_internal.h"
 
@@ -118,20 +118,24 @@ __global__ void __launch_bounds__(128) k_collide_rim(Geom g, Params P, const pop
     lbm3::collide_push_node_streamed<FXY, WRITE>(g, P, F, [Gp](int k) { return Gp[k]; }, PH, fout, gout, o, zs, ix, iy);
 }
 
-// Recomputes the phase field of planes [zs0, zs1) from gpop when the one-pass kernel reported (ctrl[0] != 0) that a
-// warp gave up waiting for the blocks it depends on.  A small grid that normally reads one word and exits.
-__global__ void __launch_bounds__(kThreads) k_phase_repair(Geom g, Params P, const pop_t *gpop, double *phi, unsigned *ctrl,
+// End of a one-pass step: the phase field of the four ghost planes (0, 1, nz+2, nz+3), whose g populations the halo
+// exchange has just delivered, and -- only when the one-pass kernel reported (ctrl[0] != 0) that a warp gave up
+// waiting for the blocks it depends on -- the phase field of the owned planes [zs0, zs1) all over again.
+__global__ void __launch_bounds__(kThreads) k_phase_finish(Geom g, Params P, const pop_t *gpop, double *phi, const unsigned *ctrl,
                                                             unsigned *sticky, int zs0, int zs1)
 {
-    if (*reinterpret_cast<volatile unsigned *>(ctrl) == 0u) return;
-    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(sticky, 1u);
-    const long long per = (long long)g.nx * g.ny, total = per * (zs1 - zs0);
-    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
-        const long long idx = t % per;
-        lbm3::phase_thread(g, P, gpop, phi, zs0 + (int)(t / per), (int)(idx % g.nx), (int)(idx / g.nx));
+    const long long per = (long long)g.nx * g.ny;
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const int ghost = (int)blockIdx.y < 2 ? (int)blockIdx.y : g.nz + (int)blockIdx.y;
+    if (idx < per) lbm3::phase_thread(g, P, gpop, phi, ghost, (int)(idx % g.nx), (int)(idx / g.nx));
+    if (*reinterpret_cast<const volatile unsigned *>(ctrl) == 0u) return;
+    if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) atomicAdd(sticky, 1u);
+    const long long total = per * (zs1 - zs0), nthreads = (long long)gridDim.x * gridDim.y * blockDim.x;
+    for (long long t = ((long long)blockIdx.y * gridDim.x + blockIdx.x) * blockDim.x + threadIdx.x; t < total; t += nthreads) {
+        const long long i = t % per;
+        lbm3::phase_thread(g, P, gpop, phi, zs0 + (int)(t / per), (int)(i % g.nx), (int)(i / g.nx));
     }
 }
-
 
 __global__ void k_init_fields(Geom g, Params P, double *phi, double *rho)
 {
@@ -218,9 +222,10 @@ class Slab3D : public Model {
 public:
     Slab3D(Runtime &rt, const lbm_config &cfg) : rt_(rt), cfg_(cfg) {}
 
-    // kernel_variant: 0 one-pass step (collide + next step's phase field in one launch, d3q19_lag.cuh);
-    // 5 two-pass (k_phase, then interior + rim kernels); 1 two-pass with the plain whole-plane collide kernel
-    bool one_pass() const { return cfg_.kernel_variant == 0; }
+    // kernel_variant: 0 one-pass step (collide + next step's phase field in one launch, d3q19_step.cuh); 5 two-pass
+    // (k_phase, then the collide kernels); 1 two-pass with the plain whole-plane collide kernel (the cross-check).
+    // The TRT extension exists in the array form of the collision only and always takes the two-pass path.
+    bool one_pass() const { return cfg_.kernel_variant == 0 && P_.trt_magic <= 0.0; }
 
     lbm_status setup()
     {
@@ -257,7 +262,7 @@ public:
         }
         // two phase-field buffers: the one-pass kernel writes the field of step t+1 while step t reads its own
         const size_t phi_bytes = (size_t)(g_.nz + 4) * g_.pl * sizeof(double);
-        for (int b = 0; b < (one_pass() ? 2 : 1); b++) {
+        for (int b = 0; b < (cfg_.kernel_variant == 0 ? 2 : 1); b++) {
             LBM_CUDA(rt_, cudaMalloc(&phib_[b], phi_bytes));
             LBM_CUDA(rt_, cudaMemsetAsync(phib_[b], 0, phi_bytes, rt_.stream));
         }
@@ -269,23 +274,23 @@ public:
         }
         LBM_CUDA(rt_, cudaMalloc(&diag_, (size_t)(diagnostics_scratch_blocks() + 1) * 6 * sizeof(double)));
         if (one_pass()) {
-            // strip / lag geometry of the one-pass kernel (d3q19_lag.cuh)
-            int resident = 148 * 3;
-            cudaDeviceProp prop;
-            if (cudaGetDeviceProperties(&prop, rt_.device) == cudaSuccess) resident = prop.multiProcessorCount * 3;
+            // strip / lag geometry of the one-pass kernel (d3q19_step.cuh).  A strip is `sb_` blocks of 128 in-plane
+            // nodes; the phase part trails the collide part by `lag_` plane-steps = kLagWindows times the number of
+            // blocks the GPU holds at once (measured at 512^3: 1.0 -> 16.4, 1.5 -> 15.4, 2 -> 15.7, 3 -> 16.3 ms).
+            if ((long long)g_.nx * g_.ny >= (1ll << 30) || g_.nz + 4 + 64 > 65535)
+                return rt_.fail(LBM_EINVAL, "D3Q19 one-pass step: a plane must hold fewer than 2^30 nodes and a slab fewer than 65 000 planes (use kernel_variant 5)");
+            int sms = 148;
+            cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, rt_.device);
+            double lag_windows = 1.5;
+            if (const char *e = getenv("LBM_TUNE_LAGK")) lag_windows = atof(e);     // measurement knobs, not part of the ABI
+            if (const char *e = getenv("LBM_TUNE_POL")) pol_ = atoi(e);
             nblk_ = (int)(((long long)g_.nx * g_.ny + 127) / 128);
             dshift_ = 1 + g_.nx / 128;
-            int sb = 64;
-            double lag_k = 1.5;
-            if (const char *e = getenv("LBM_TUNE_SB")) sb = atoi(e);
-            if (const char *e = getenv("LBM_TUNE_LAGK")) lag_k = atof(e);
-            if (const char *e = getenv("LBM_TUNE_POL")) pol_ = atoi(e);
-            if (const char *e = getenv("LBM_TUNE_ABLATE")) ablate_ = atoi(e);
-            sb_ = std::max(sb, 2 * dshift_);
+            sb_ = std::max(64, 2 * dshift_);
             if (nblk_ + dshift_ <= sb_) sb_ = nblk_ + dshift_;   // one strip
             nstrips_ = (nblk_ + dshift_ + sb_ - 1) / sb_;
-            lag_ = 2 + (int)(lag_k * resident / sb_);
-            ctrl_words_ = (size_t)nstrips_ * (g_.nz + 4 + lag_) + 2;
+            lag_ = 2 + (int)(lag_windows * (sms * 4) / sb_);
+            ctrl_words_ = ((size_t)nstrips_ * (g_.nz + 4 + lag_) + 2) * lbm3::LAG_PAD + 64;
             LBM_CUDA(rt_, cudaMalloc(&ctrl_, ctrl_words_ * sizeof(unsigned)));
             LBM_CUDA(rt_, cudaMemsetAsync(ctrl_, 0, ctrl_words_ * sizeof(unsigned), rt_.stream));
         }
@@ -435,39 +440,70 @@ public:
         return rt_.launched("k_collide_interior");
     }
 
+    // the same planes through k_step_one<PHI = false>: the streamed collision with g staged through shared memory
+    // (128 registers, 16 warps per SM), collide only
+    lbm_status collide_core(int zs0, int n0, int zs1, int n1, int write_fields)
+    {
+        if (n0 + n1 <= 0) return LBM_OK;
+        const int a = cur_, b = 1 - cur_;
+        lbm3::LagPlan L{};
+        const int nb = (int)(((long long)g_.nx * g_.ny + 127) / 128);
+        L.sb = nb; L.nstrips = 1; L.lag = 0; L.dshift = 0;
+        L.c0 = -(1 << 30); L.c1 = 1 << 30; L.p0 = 0; L.p1 = 0;
+        L.z0 = zs0; L.pz = n0 + n1;
+        L.zjump_at = n0; L.zjump_by = zs1 - (zs0 + n0);
+        const FieldsOut o = fields_out();
+        const dim3 grid(L.sb, L.pz, 1);
+        const size_t smem = 19 * 128 * sizeof(pop_t);
+        rt_.about_to_launch();
+        with_flavour(write_fields, [&](auto fxy, auto wr, auto) {
+            lbm3::k_step_one<decltype(fxy)::value, decltype(wr)::value, 0, false>
+                <<<grid, 128, smem, rt_.stream>>>(g_, P_, f_[a], gq_[a], phib_[pf_], f_[b], gq_[b], o, nullptr, nullptr, nullptr, L);
+        });
+        return rt_.launched("k_collide_core");
+    }
+
+    // every bulk node except the rim rows, collide only: the staged kernel, or (the TRT extension, which exists in
+    // the array form of the collision only) the register kernel
+    lbm_status collide_bulk(int zs0, int n0, int zs1, int n1, int write_fields)
+    {
+        if (P_.trt_magic > 0.0) return collide_interior(zs0, n0, zs1, n1, write_fields);
+        return collide_core(zs0, n0, zs1, n1, write_fields);
+    }
+
     // One-pass kernel: collide planes [c0, c1) (all bulk nodes except the rim rows) and the next step's phase field
     // of planes [p0, p1) into the other phase buffer.  Every collide that pushes into planes [p0, p1) must either
     // be part of this launch or have been launched before it.
-    lbm_status collide_lag(int c0, int c1, int p0, int p1, int write_fields)
+    lbm_status step_one(int c0, int c1, int p0, int p1, int write_fields)
     {
         const int a = cur_, b = 1 - cur_;
-        lbm3::LagPlan L;
+        lbm3::LagPlan L{};
         L.sb = sb_; L.nstrips = nstrips_; L.lag = lag_; L.dshift = dshift_;
         L.c0 = c0; L.c1 = c1; L.p0 = p0; L.p1 = p1;
         L.z0 = std::min(c0, p0 + lag_);
+        L.zjump_at = 1 << 30; L.zjump_by = 0;
         L.pz = std::max(c1, p1 + lag_) - L.z0;
-        L.warps_per_group = 4u * (unsigned)sb_;
+        L.full = (unsigned)sb_;
         L.spin_limit = 4000;
-        L.ablate = ablate_;
         const size_t groups = (size_t)nstrips_ * L.pz;
-        if (groups + 2 > ctrl_words_) return rt_.fail(LBM_ESTATE, "one-pass kernel: group counters too small");
-        LBM_CUDA(rt_, cudaMemsetAsync(ctrl_, 0, (groups + 1) * sizeof(unsigned), rt_.stream));
+        if (groups * lbm3::LAG_PAD + 34 > ctrl_words_) return rt_.fail(LBM_ESTATE, "one-pass kernel: group counters too small");
+        // [0] give-up flag, [32 + 32 i] counter of group i, [last] number of steps that fell back
+        LBM_CUDA(rt_, cudaMemsetAsync(ctrl_, 0, (groups * lbm3::LAG_PAD + 33) * sizeof(unsigned), rt_.stream));
         const FieldsOut o = fields_out();
-        const unsigned grid = (unsigned)(groups * sb_);
-        const size_t smem = 19 * 128 * sizeof(pop_t);
-        unsigned *sticky = ctrl_ + ctrl_words_ - 1;
+        const dim3 grid(sb_, L.pz, nstrips_);
+        const size_t smem = 2 * 19 * 128 * sizeof(pop_t);
         rt_.about_to_launch();
-        with_flavour(write_fields, [&](auto fxy, auto wr, auto trt) {
-            if (pol_ == 1)
-                lbm3::k_collide_lag<decltype(fxy)::value, decltype(wr)::value, decltype(trt)::value, 1>
-                    <<<grid, 128, smem, rt_.stream>>>(g_, P_, f_[a], gq_[a], phib_[pf_], f_[b], gq_[b], o, phib_[1 - pf_], ctrl_ + 1, ctrl_, L);
-            else
-                lbm3::k_collide_lag<decltype(fxy)::value, decltype(wr)::value, decltype(trt)::value, 0>
-                    <<<grid, 128, smem, rt_.stream>>>(g_, P_, f_[a], gq_[a], phib_[pf_], f_[b], gq_[b], o, phib_[1 - pf_], ctrl_ + 1, ctrl_, L);
+        with_flavour(write_fields, [&](auto fxy, auto wr, auto) {
+            auto launch = [&](auto kern) {
+                cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+                kern<<<grid, 128, smem, rt_.stream>>>(g_, P_, f_[a], gq_[a], phib_[pf_], f_[b], gq_[b], o, phib_[1 - pf_], ctrl_ + 32, ctrl_, L);
+            };
+            constexpr bool FXY = decltype(fxy)::value, WR = decltype(wr)::value;
+            if (pol_ == 1) launch(lbm3::k_step_one<FXY, WR, 1, true>);
+            else launch(lbm3::k_step_one<FXY, WR, 0, true>);
         });
-        LBM_TRY(rt_.launched("k_collide_lag"));
-        k_phase_repair<<<296, kThreads, 0, rt_.stream>>>(g_, P_, gq_[b], phib_[1 - pf_], ctrl_, sticky, p0, p1);
-        LBM_TRY(rt_.launched("k_phase_repair"));
+        LBM_TRY(rt_.launched("k_step_one"));
+        pend_p0_ = p0; pend_p1_ = p1;
         lag_pending_ = true;
         return LBM_OK;
     }
@@ -485,12 +521,12 @@ public:
         if (one_pass()) {
             LBM_TRY(ensure_phi());
             LBM_TRY(collide_rim(1, nz + 2, 0, 0, write_fields));
-            return collide_lag(1, nz + 3, 2, nz + 2, write_fields);
+            return step_one(1, nz + 3, 2, nz + 2, write_fields);
         }
         LBM_TRY(phase_planes(gq_[cur_], phib_[pf_], 0, nz + 4));
         po_ = pf_;
-        if (cfg_.kernel_variant == 5) {
-            LBM_TRY(collide_interior(1, nz + 2, 0, 0, write_fields));
+        if (cfg_.kernel_variant != 1) {
+            LBM_TRY(collide_bulk(1, nz + 2, 0, 0, write_fields));
             return collide_rim(1, nz + 2, 0, 0, write_fields);
         }
         const int a = cur_, b = 1 - cur_;
@@ -509,9 +545,9 @@ public:
         cur_ = 1 - cur_;
         if (lag_pending_) {
             lag_pending_ = false;
-            double *next = phib_[1 - pf_];
-            LBM_TRY(phase_planes(gq_[cur_], next, 0, 2));
-            LBM_TRY(phase_planes(gq_[cur_], next, g_.nz + 2, 2));
+            rt_.about_to_launch();
+            k_phase_finish<<<plane_grid(4), kThreads, 0, rt_.stream>>>(g_, P_, gq_[cur_], phib_[1 - pf_], ctrl_, ctrl_ + ctrl_words_ - 1, pend_p0_, pend_p1_);
+            LBM_TRY(rt_.launched("k_phase_finish"));
             po_ = pf_;
             pf_ = 1 - pf_;
             phi_valid_ = true;
@@ -644,15 +680,15 @@ public:
             po_ = pf_;
             LBM_TRY(collide_rim(1, 4, nz - 1, 4, write_fields));
         }
-        LBM_TRY(collide_interior(1, 4, nz - 1, 4, write_fields));   // z = -1 .. 2 and nz-3 .. nz in one launch
+        LBM_TRY(collide_bulk(1, 4, nz - 1, 4, write_fields));   // z = -1 .. 2 and nz-3 .. nz in one launch
         LBM_CUDA(rt_, cudaEventRecord(ev_fork_, rt_.stream));
         LBM_CUDA(rt_, cudaStreamWaitEvent(side_, ev_fork_, 0));
         LBM_TRY(exchange(false, side_));
         LBM_CUDA(rt_, cudaEventRecord(ev_join_, side_));
         if (one_pass()) {
-            LBM_TRY(collide_lag(5, nz - 1, 2, nz + 2, write_fields));   // z = 3 .. nz-4, phase field of all owned planes
+            LBM_TRY(step_one(5, nz - 1, 2, nz + 2, write_fields));   // z = 3 .. nz-4, phase field of all owned planes
         } else {
-            LBM_TRY(collide_interior(5, nz - 6, 0, 0, write_fields));
+            LBM_TRY(collide_bulk(5, nz - 6, 0, 0, write_fields));
             LBM_TRY(collide_rim(5, nz - 6, 0, 0, write_fields));
         }
         LBM_CUDA(rt_, cudaStreamWaitEvent(rt_.stream, ev_join_, 0));
@@ -749,9 +785,10 @@ private:
     double *phib_[2] = {nullptr, nullptr};
     int pf_ = 0, po_ = 0;
     bool phi_valid_ = false, lag_pending_ = false;
+    int pend_p0_ = 0, pend_p1_ = 0;      // owned planes whose phase field the pending one-pass step has written
     double *rho_ = nullptr, *ux_ = nullptr, *uy_ = nullptr, *uz_ = nullptr, *diag_ = nullptr;
     // one-pass kernel: strip geometry and its control words ([0] give-up flag, [1..] group counters, last: fallback count)
-    int nblk_ = 0, dshift_ = 0, sb_ = 0, nstrips_ = 0, lag_ = 0, pol_ = 0, ablate_ = 0;
+    int nblk_ = 0, dshift_ = 0, sb_ = 0, nstrips_ = 0, lag_ = 0, pol_ = 0;
     unsigned *ctrl_ = nullptr;
     size_t ctrl_words_ = 0;
     double *stage_ = nullptr;

@@ -71,15 +71,17 @@ def test_d3q19_vs_oracle(shape, params, rand, variant):
     o.close()
 
 
+@pytest.mark.parametrize("variant", [0, 5])
 @pytest.mark.parametrize("shape,seed", [((200, 150, 40), 3), ((131, 77, 19), 4), ((640, 33, 12), 5)])
-def test_d3q19_one_pass_equals_two_pass_on_many_strips(shape, seed):
+def test_d3q19_default_paths_equal_the_plain_kernel_on_larger_grids(shape, seed, variant):
     """Grids large enough for several strips, many plane-steps and a lag shorter than the slab: the one-pass step
-    (kernel_variant 0) must leave exactly the state of the two-pass step (5, itself equal to the oracle on the small
-    grids above) and must never have had to fall back to the separate phase kernel."""
+    (kernel_variant 0) and the two-pass step with the staged collide kernel (5) must leave exactly the state of the
+    plain whole-plane kernel (1: array form of the collision, no staging, no strips -- itself equal to the oracle on
+    the small grids above), and the one-pass step must never have had to fall back to the separate phase kernel."""
     nx, ny, nz = shape
     flds = _random_fields(nx, ny, nz, seed)
-    a = _ctx3(nx, ny, nz, GENERAL, flds, 0)
-    b = _ctx3(nx, ny, nz, GENERAL, flds, 5)
+    a = _ctx3(nx, ny, nz, GENERAL, flds, variant)
+    b = _ctx3(nx, ny, nz, GENERAL, flds, 1)
     for s in (1, 2, 7):
         a.step(s)
         b.step(s)
