@@ -16,6 +16,7 @@
 #include <map>
 #include <stdexcept>
 #include <thread>
+#include <unistd.h>
 #include "host_common.h"
 
 // params_list.h: name -> value(s); the hosts only ever add one number per name
@@ -64,7 +65,16 @@ public:
             // one communicator over the slabs: every rank has to join at the same time, hence one thread each
             char id[LBM_COMM_ID_BYTES];
             LBM_CHECK(0, lbm_comm_unique_id(id));
+            // NCCL prints a version banner on stdout at the first communicator when NCCL_DEBUG=VERSION is set; the
+            // program's stdout has to stay the reference's, so file descriptor 1 points at stderr meanwhile
+            std::cout.flush();
+            std::fflush(stdout);
+            const int saved = dup(1);
+            dup2(2, 1);
             each_slab([&](Slab &s) { LBM_CHECK(s.ctx, lbm_comm_attach(s.ctx, id)); });
+            std::fflush(stdout);
+            dup2(saved, 1);
+            close(saved);
         }
         n_ = (size_t)NX * NY * NZ;
         rho_.assign(n_, 0.0); phi_.assign(n_, 0.0); ux_.assign(n_, 0.0); uy_.assign(n_, 0.0); uz_.assign(n_, 0.0);

@@ -85,10 +85,11 @@ typedef struct {
     int device;                /* CUDA device ordinal */
     int slab_rank, slab_count; /* z-slab decomposition (3-D only): this context owns slab `rank` of `count` */
     int kernel_variant;        /* 0 = default (fastest measured).  Other values select alternative kernels of the same
-                                  model, kept for cross-checks and measurements and held to the same parity tests:
-                                  D3Q19 see DESIGN.md section 6; Shan-Chen 1 = density pass + collide, 2/3/5 = other
-                                  tiles of the fused kernel; binary D2Q9 1 = 256-thread blocks, 2-4 = fused tile
-                                  kernel; curved solid 1/2 = other block shapes.  Results never depend on it. */
+                                  model, kept for cross-checks and held to the same parity tests.  D3Q19: 0 one-pass
+                                  step, 5 two-pass (phase kernel + collide kernels), 1 two-pass with the plain
+                                  whole-plane kernel; Shan-Chen 1 = density pass + collide, 2/3/5 = other tiles of the
+                                  fused kernel; binary D2Q9 1 = 256-thread blocks, 2-4 = fused tile kernel; curved
+                                  solid 1/2 = other block shapes.  Results never depend on it. */
     double trt_magic;          /* LBM_BINARY_D3Q19 only, EXTENSION with no counterpart in the reference: 0 (default) keeps
                                   the reference's BGK collision; Lambda > 0 relaxes the antisymmetric half of f with
                                   omega- = 1/(Lambda/(tau-1/2) + 1/2) (two-relaxation-time), everything else unchanged.
@@ -170,6 +171,11 @@ lbm_status lbm_set_stream(lbm_ctx *ctx, void *cuda_stream);
 unsigned long long lbm_launch_count(const lbm_ctx *ctx); /* kernels launched by this context so far */
 int lbm_population_bytes(const lbm_ctx *ctx);      /* storage size of one population value: 8, or 4 in liblbm_b200_f32.so;
                                                       the element size of the F/G halo messages of lbm_slab_halo */
+/* Debugging aid with no reference counterpart: with LBM_GUARD=1 in the environment at lbm_create, every device buffer
+ * of the context lies between two 1 MiB guard bands holding a byte pattern; this returns how many guard bytes have
+ * been overwritten so far (0 = no kernel wrote outside its buffers by less than 1 MiB; always 0 without LBM_GUARD).
+ * Waits for the stream. */
+unsigned long long lbm_guard_check(lbm_ctx *ctx);
 /* D3Q19 one-pass step (kernel_variant 0): number of steps so far in which a block gave up waiting for the blocks its
  * phase-field part depends on and the phase field was recomputed by the separate kernel instead (results are the
  * same either way; a non-zero value only says the step was slower than it should be).  Waits for the stream. */

@@ -82,6 +82,7 @@ def load_library(precision="f64"):
         "lbm_launch_count": (C.c_ulonglong, [vp]),
         "lbm_population_bytes": (ci, [vp]),
         "lbm_phase_fallbacks": (C.c_ulonglong, [vp]),
+        "lbm_guard_check": (C.c_ulonglong, [vp]),
         "lbm_profile": (ci, [vp, ci]),
         "lbm_profile_report": (ci, [vp, C.c_char_p, sz]),
         "lbm_host_alloc": (vp, [sz]),
@@ -105,7 +106,7 @@ def load_library(precision="f64"):
 
 
 EXPORTS = ["lbm_config_default", "lbm_create", "lbm_destroy", "lbm_last_error", "lbm_slab_extent", "lbm_local_nodes",
-           "lbm_set_field", "lbm_get_field", "lbm_get_field_async", "lbm_population_bytes", "lbm_phase_fallbacks", "lbm_set_geometry", "lbm_init", "lbm_set_populations", "lbm_get_populations", "lbm_step",
+           "lbm_set_field", "lbm_get_field", "lbm_get_field_async", "lbm_population_bytes", "lbm_phase_fallbacks", "lbm_guard_check", "lbm_set_geometry", "lbm_init", "lbm_set_populations", "lbm_get_populations", "lbm_step",
            "lbm_sync", "lbm_diagnostics", "lbm_get_stream", "lbm_set_stream", "lbm_launch_count", "lbm_profile",
            "lbm_profile_report", "lbm_host_alloc",
            "lbm_host_free", "lbm_comm_unique_id", "lbm_comm_attach", "lbm_slab_halo", "lbm_slab_init_fields",
@@ -231,6 +232,10 @@ class Context:
     @property
     def population_bytes(self):
         return int(self.L.lbm_population_bytes(self.h))
+
+    def guard_check(self):
+        """Guard bytes overwritten so far (contexts created with LBM_GUARD=1 in the environment; else 0)."""
+        return int(self.L.lbm_guard_check(self.h))
 
     @property
     def phase_fallbacks(self):

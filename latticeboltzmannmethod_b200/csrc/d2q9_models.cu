@@ -244,9 +244,9 @@ public:
     ~Model2D() override
     {
         cudaSetDevice(rt_.device);
-        for (int b = 0; b < 2; b++) { cudaFree(f_[b]); cudaFree(g_[b]); }
-        for (double *p : fields_) cudaFree(p);
-        cudaFree(aux_); cudaFree(diag_);
+        for (int b = 0; b < 2; b++) { rt_.dev_free(f_[b]); rt_.dev_free(g_[b]); }
+        for (double *p : fields_) rt_.dev_free(p);
+        rt_.dev_free(aux_); rt_.dev_free(diag_);
     }
     lbm_status alloc_common()
     {
@@ -254,18 +254,18 @@ public:
         n_ = (long long)cfg_.nx * cfg_.ny;
         if (n_ >= (1ll << 31)) return rt_.fail(LBM_EINVAL, "2-D model: nx*ny must stay below 2^31");
         for (int b = 0; b < 2; b++) {
-            LBM_CUDA(rt_, cudaMalloc(&f_[b], 9 * n_ * sizeof(double)));
+            LBM_CUDA(rt_, rt_.dev_alloc(&f_[b], 9 * n_ * sizeof(double)));
             LBM_CUDA(rt_, cudaMemsetAsync(f_[b], 0, 9 * n_ * sizeof(double), rt_.stream));
             if (nsets_ == 2) {
-                LBM_CUDA(rt_, cudaMalloc(&g_[b], 9 * n_ * sizeof(double)));
+                LBM_CUDA(rt_, rt_.dev_alloc(&g_[b], 9 * n_ * sizeof(double)));
                 LBM_CUDA(rt_, cudaMemsetAsync(g_[b], 0, 9 * n_ * sizeof(double), rt_.stream));
             }
         }
         for (double *&p : fields_) {
-            LBM_CUDA(rt_, cudaMalloc(&p, n_ * sizeof(double)));
+            LBM_CUDA(rt_, rt_.dev_alloc(&p, n_ * sizeof(double)));
             LBM_CUDA(rt_, cudaMemsetAsync(p, 0, n_ * sizeof(double), rt_.stream));
         }
-        LBM_CUDA(rt_, cudaMalloc(&diag_, (size_t)(diagnostics_scratch_blocks() + 1) * 6 * sizeof(double)));
+        LBM_CUDA(rt_, rt_.dev_alloc(&diag_, (size_t)(diagnostics_scratch_blocks() + 1) * 6 * sizeof(double)));
         LBM_CUDA(rt_, cudaStreamSynchronize(rt_.stream));
         return LBM_OK;
     }
@@ -291,7 +291,7 @@ public:
     {
         if (set < 0 || set >= nsets_) return rt_.fail(LBM_EINVAL, "no such population set");
         double *stage = nullptr;
-        LBM_CUDA(rt_, cudaMalloc(&stage, 9 * n_ * sizeof(double)));
+        LBM_CUDA(rt_, rt_.dev_alloc(&stage, 9 * n_ * sizeof(double)));
         lbm_status st = rt_.cuda(cudaMemcpyAsync(stage, host, 9 * n_ * sizeof(double), cudaMemcpyHostToDevice, rt_.stream), "H2D populations");
         if (st == LBM_OK) {
             k_aos_to_soa9<<<blocks_for(9 * n_), kThreads, 0, rt_.stream>>>(n_, stage, set == 0 ? f_[cur_] : g_[cur_]);
@@ -299,7 +299,7 @@ public:
         }
         if (st == LBM_OK) st = after_set_populations(set);
         if (st == LBM_OK) st = rt_.cuda(cudaStreamSynchronize(rt_.stream), "sync");
-        cudaFree(stage);
+        rt_.dev_free(stage);
         return st;
     }
     virtual lbm_status after_set_populations(int) { return LBM_OK; }
@@ -307,12 +307,12 @@ public:
     {
         if (set < 0 || set >= nsets_) return rt_.fail(LBM_EINVAL, "no such population set");
         double *stage = nullptr;
-        LBM_CUDA(rt_, cudaMalloc(&stage, 9 * n_ * sizeof(double)));
+        LBM_CUDA(rt_, rt_.dev_alloc(&stage, 9 * n_ * sizeof(double)));
         k_soa_to_aos9<<<blocks_for(9 * n_), kThreads, 0, rt_.stream>>>(n_, set == 0 ? f_[cur_] : g_[cur_], stage);
         lbm_status st = rt_.launched("k_soa_to_aos9");
         if (st == LBM_OK) st = rt_.cuda(cudaMemcpyAsync(host, stage, 9 * n_ * sizeof(double), cudaMemcpyDeviceToHost, rt_.stream), "D2H populations");
         if (st == LBM_OK) st = rt_.cuda(cudaStreamSynchronize(rt_.stream), "sync");
-        cudaFree(stage);
+        rt_.dev_free(stage);
         return st;
     }
     lbm_status diag_common(int skip_border, double *mass, double *mom, double *phase_mass, int *has_nan)
@@ -347,7 +347,7 @@ public:
     {
         LBM_TRY(alloc_common());
         P_ = lbm2::sc_params(cfg_.nx, cfg_.ny, cfg_.tau, cfg_.g);
-        LBM_CUDA(rt_, cudaMalloc(&aux_, n_ * sizeof(double)));   // psi
+        LBM_CUDA(rt_, rt_.dev_alloc(&aux_, n_ * sizeof(double)));   // psi
         return LBM_OK;
     }
     bool has_field(int f) const override { return f == LBM_RHO || f == LBM_UX || f == LBM_UY; }
@@ -491,7 +491,7 @@ public:
         std::vector<double> force(cfg_.nx);
         lbm2::mrt_build_tables(&P_, cfg_.model == LBM_MRT_GS_D2Q9 ? 0 : 1, cfg_.nx, cfg_.ny, cfg_.omega, cfg_.omega_bulk,
                                cfg_.force_ampl, force.data());
-        LBM_CUDA(rt_, cudaMalloc(&aux_, cfg_.nx * sizeof(double)));
+        LBM_CUDA(rt_, rt_.dev_alloc(&aux_, cfg_.nx * sizeof(double)));
         LBM_CUDA(rt_, cudaMemcpy(aux_, force.data(), cfg_.nx * sizeof(double), cudaMemcpyHostToDevice));
         return LBM_OK;
     }
@@ -524,12 +524,12 @@ private:
 class Trt : public Model2D {
 public:
     Trt(Runtime &rt, const lbm_config &cfg) : Model2D(rt, cfg, 1) {}
-    ~Trt() override { cudaFree(links_); }
+    ~Trt() override { rt_.dev_free(links_); }
     lbm_status setup()
     {
         LBM_TRY(alloc_common());
         P_ = lbm2::TrtParams{cfg_.nx, cfg_.ny, 2.0 - cfg_.omega, cfg_.omega, cfg_.ce, cfg_.conc_wall};   // cylinder.cpp:38-40
-        LBM_CUDA(rt_, cudaMalloc(&links_, n_ * sizeof(unsigned short)));
+        LBM_CUDA(rt_, rt_.dev_alloc(&links_, n_ * sizeof(unsigned short)));
         LBM_CUDA(rt_, cudaMemset(links_, 0, n_ * sizeof(unsigned short)));
         return LBM_OK;
     }
@@ -603,13 +603,13 @@ private:
 class BinaryShape : public Model2D {
 public:
     BinaryShape(Runtime &rt, const lbm_config &cfg) : Model2D(rt, cfg, 2) {}
-    ~BinaryShape() override { cudaFree(links_); }
+    ~BinaryShape() override { rt_.dev_free(links_); }
     lbm_status setup()
     {
         LBM_TRY(alloc_common());
         P_ = lbm2::BsParams{cfg_.nx, cfg_.ny, cfg_.aconst, cfg_.kconst, cfg_.gammaconst, cfg_.wall_gradient, cfg_.tau_gas,
                             cfg_.tau_liq - cfg_.tau_gas, 1.0 / cfg_.tau_phi, cfg_.force[0], cfg_.force[1]};
-        LBM_CUDA(rt_, cudaMalloc(&links_, n_ * sizeof(unsigned short)));
+        LBM_CUDA(rt_, rt_.dev_alloc(&links_, n_ * sizeof(unsigned short)));
         LBM_CUDA(rt_, cudaMemset(links_, 0, n_ * sizeof(unsigned short)));
         return LBM_OK;
     }

@@ -255,28 +255,29 @@ public:
 
         const size_t pop_bytes = (size_t)(g_.nz + 4) * 19 * g_.pl * sizeof(pop_t);
         for (int b = 0; b < 2; b++) {
-            LBM_CUDA(rt_, cudaMalloc(&f_[b], pop_bytes));
-            LBM_CUDA(rt_, cudaMalloc(&gq_[b], pop_bytes));
+            LBM_CUDA(rt_, rt_.dev_alloc(&f_[b], pop_bytes));
+            LBM_CUDA(rt_, rt_.dev_alloc(&gq_[b], pop_bytes));
             LBM_CUDA(rt_, cudaMemsetAsync(f_[b], 0, pop_bytes, rt_.stream));
             LBM_CUDA(rt_, cudaMemsetAsync(gq_[b], 0, pop_bytes, rt_.stream));
         }
         // two phase-field buffers: the one-pass kernel writes the field of step t+1 while step t reads its own
         const size_t phi_bytes = (size_t)(g_.nz + 4) * g_.pl * sizeof(double);
         for (int b = 0; b < (cfg_.kernel_variant == 0 ? 2 : 1); b++) {
-            LBM_CUDA(rt_, cudaMalloc(&phib_[b], phi_bytes));
+            LBM_CUDA(rt_, rt_.dev_alloc(&phib_[b], phi_bytes));
             LBM_CUDA(rt_, cudaMemsetAsync(phib_[b], 0, phi_bytes, rt_.stream));
         }
         const size_t fld_bytes = (size_t)g_.nz * g_.pl * sizeof(double);
         double **fl[4] = {&rho_, &ux_, &uy_, &uz_};
         for (auto p : fl) {
-            LBM_CUDA(rt_, cudaMalloc(p, fld_bytes));
+            LBM_CUDA(rt_, rt_.dev_alloc(p, fld_bytes));
             LBM_CUDA(rt_, cudaMemsetAsync(*p, 0, fld_bytes, rt_.stream));
         }
-        LBM_CUDA(rt_, cudaMalloc(&diag_, (size_t)(diagnostics_scratch_blocks() + 1) * 6 * sizeof(double)));
+        LBM_CUDA(rt_, rt_.dev_alloc(&diag_, (size_t)(diagnostics_scratch_blocks() + 1) * 6 * sizeof(double)));
         if (one_pass()) {
             // strip / lag geometry of the one-pass kernel (d3q19_step.cuh).  A strip is `sb_` blocks of 128 in-plane
             // nodes; the phase part trails the collide part by `lag_` plane-steps = kLagWindows times the number of
-            // blocks the GPU holds at once (measured at 512^3: 1.0 -> 16.4, 1.5 -> 15.4, 2 -> 15.7, 3 -> 16.3 ms).
+            // blocks the GPU holds at once (measured at 512^3: 1.0 -> 16.4, 1.25 -> 16.2, 1.5 -> 15.3, 1.75 -> 15.4,
+            // 2 -> 15.5, 3 -> 16.3 ms: shorter and blocks wait for their producers, longer and L2 loses the g* rows).
             if ((long long)g_.nx * g_.ny >= (1ll << 30) || g_.nz + 4 + 64 > 65535)
                 return rt_.fail(LBM_EINVAL, "D3Q19 one-pass step: a plane must hold fewer than 2^30 nodes and a slab fewer than 65 000 planes (use kernel_variant 5)");
             int sms = 148;
@@ -289,9 +290,10 @@ public:
             sb_ = std::max(64, 2 * dshift_);
             if (nblk_ + dshift_ <= sb_) sb_ = nblk_ + dshift_;   // one strip
             nstrips_ = (nblk_ + dshift_ + sb_ - 1) / sb_;
+            if (const char *e = getenv("LBM_TUNE_TIGHT")) if (atoi(e)) sb_ = std::max((nblk_ + dshift_ + nstrips_ - 1) / nstrips_, 2 * dshift_);   // same strip count, least padding
             lag_ = 2 + (int)(lag_windows * (sms * 4) / sb_);
             ctrl_words_ = ((size_t)nstrips_ * (g_.nz + 4 + lag_) + 2) * lbm3::LAG_PAD + 64;
-            LBM_CUDA(rt_, cudaMalloc(&ctrl_, ctrl_words_ * sizeof(unsigned)));
+            LBM_CUDA(rt_, rt_.dev_alloc(&ctrl_, ctrl_words_ * sizeof(unsigned)));
             LBM_CUDA(rt_, cudaMemsetAsync(ctrl_, 0, ctrl_words_ * sizeof(unsigned), rt_.stream));
         }
         LBM_CUDA(rt_, cudaStreamSynchronize(rt_.stream));
@@ -306,8 +308,8 @@ public:
             if (api && api->CommDestroy) api->CommDestroy(comm_);
         }
         if (side_) { cudaStreamDestroy(side_); cudaEventDestroy(ev_fork_); cudaEventDestroy(ev_join_); }
-        for (int b = 0; b < 2; b++) { cudaFree(f_[b]); cudaFree(gq_[b]); cudaFree(phib_[b]); }
-        cudaFree(rho_); cudaFree(ux_); cudaFree(uy_); cudaFree(uz_); cudaFree(diag_); cudaFree(ctrl_); cudaFree(stage_);
+        for (int b = 0; b < 2; b++) { rt_.dev_free(f_[b]); rt_.dev_free(gq_[b]); rt_.dev_free(phib_[b]); }
+        rt_.dev_free(rho_); rt_.dev_free(ux_); rt_.dev_free(uy_); rt_.dev_free(uz_); rt_.dev_free(diag_); rt_.dev_free(ctrl_); rt_.dev_free(stage_);
     }
 
     size_t local_nodes() const override { return (size_t)g_.nx * g_.ny * g_.nz; }
@@ -717,7 +719,7 @@ public:
         if (stage_) return LBM_OK;
         const size_t per_plane = (size_t)g_.nx * g_.ny * 19 * sizeof(double);
         stage_planes_ = (int)std::max<size_t>(1, std::min<size_t>((size_t)g_.nz, ((size_t)256 << 20) / per_plane));
-        LBM_CUDA(rt_, cudaMalloc(&stage_, per_plane * stage_planes_));
+        LBM_CUDA(rt_, rt_.dev_alloc(&stage_, per_plane * stage_planes_));
         return LBM_OK;
     }
     lbm_status set_populations(int set, const double *host) override
@@ -788,7 +790,8 @@ private:
     int pend_p0_ = 0, pend_p1_ = 0;      // owned planes whose phase field the pending one-pass step has written
     double *rho_ = nullptr, *ux_ = nullptr, *uy_ = nullptr, *uz_ = nullptr, *diag_ = nullptr;
     // one-pass kernel: strip geometry and its control words ([0] give-up flag, [1..] group counters, last: fallback count)
-    int nblk_ = 0, dshift_ = 0, sb_ = 0, nstrips_ = 0, lag_ = 0, pol_ = 0;
+    int nblk_ = 0, dshift_ = 0, sb_ = 0, nstrips_ = 0, lag_ = 0;
+    int pol_ = 1;     // L2 residency hints on (15.28 vs 15.63 ms at 512^3)
     unsigned *ctrl_ = nullptr;
     size_t ctrl_words_ = 0;
     double *stage_ = nullptr;

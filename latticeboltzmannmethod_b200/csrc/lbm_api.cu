@@ -1,4 +1,5 @@
 // lbm_api.cu -- the extern "C" boundary of liblbm_b200.so (include/lbm_b200.h).
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -82,6 +83,8 @@ lbm_status lbm_create(const lbm_config *cfg, lbm_ctx **out)
     }
     ctx->cfg = *cfg;
     ctx->rt.device = cfg->device;
+    const char *guard = std::getenv("LBM_GUARD");
+    ctx->rt.guard = guard && guard[0] == '1';
     lbm_status st = LBM_OK;
     int ndev = 0;
     st = ctx->rt.cuda(cudaGetDeviceCount(&ndev), "cudaGetDeviceCount");
@@ -233,6 +236,11 @@ lbm_status lbm_set_stream(lbm_ctx *ctx, void *stream)
 
 unsigned long long lbm_launch_count(const lbm_ctx *ctx) { return ctx ? ctx->rt.launches : 0; }
 int lbm_population_bytes(const lbm_ctx *ctx) { return ctx && ctx->model ? ctx->model->pop_bytes() : 0; }
+unsigned long long lbm_guard_check(lbm_ctx *ctx)
+{
+    if (!have_ctx(ctx) || bind_device(ctx) != LBM_OK) return 0;
+    return ctx->rt.guard_check();
+}
 unsigned long long lbm_phase_fallbacks(lbm_ctx *ctx)
 {
     if (!have_ctx(ctx) || bind_device(ctx) != LBM_OK) return 0;

@@ -26,6 +26,53 @@ struct Runtime {
     std::vector<Timed> timed;
     cudaEvent_t pending_start = nullptr;
 
+    // Device allocations of the models go through here.  With LBM_GUARD=1 in the environment when the context is
+    // created every buffer sits between two 1 MiB guard bands filled with a byte pattern; guard_check() counts the
+    // guard bytes that no longer hold it -- the out-of-bounds-write check that can run where compute-sanitizer cannot.
+    bool guard = false;
+    static constexpr size_t kGuardBytes = 1u << 20;
+    struct Alloc { char *base; size_t bytes; };
+    std::map<void *, Alloc> allocs;
+    cudaError_t dev_alloc(void **p, size_t bytes)
+    {
+        const size_t g = guard ? kGuardBytes : 0;
+        char *base = nullptr;
+        cudaError_t e = cudaMalloc((void **)&base, bytes + 2 * g);
+        if (e != cudaSuccess) return e;
+        if (g) {
+            cudaMemset(base, 0xA5, g);
+            cudaMemset(base + g + bytes, 0xA5, g);
+        }
+        *p = base + g;
+        allocs[*p] = Alloc{base, bytes};
+        return cudaSuccess;
+    }
+    template <class T>
+    cudaError_t dev_alloc(T **p, size_t bytes) { return dev_alloc((void **)p, bytes); }
+    void dev_free(void *p)
+    {
+        if (!p) return;
+        auto it = allocs.find(p);
+        if (it == allocs.end()) { cudaFree(p); return; }
+        cudaFree(it->second.base);
+        allocs.erase(it);
+    }
+    // number of guard bytes overwritten so far (0 without LBM_GUARD); waits for the stream
+    unsigned long long guard_check()
+    {
+        if (!guard) return 0;
+        cudaStreamSynchronize(stream);
+        std::vector<unsigned char> h(kGuardBytes);
+        unsigned long long bad = 0;
+        for (auto &kv : allocs)
+            for (int side = 0; side < 2; side++) {
+                const char *src = side == 0 ? kv.second.base : kv.second.base + kGuardBytes + kv.second.bytes;
+                if (cudaMemcpy(h.data(), src, kGuardBytes, cudaMemcpyDeviceToHost) != cudaSuccess) return ~0ull;
+                for (unsigned char c : h) bad += c != 0xA5;
+            }
+        return bad;
+    }
+
     lbm_status fail(lbm_status st, const std::string &what)
     {
         err = what;

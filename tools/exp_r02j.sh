@@ -1,0 +1,29 @@
+#!/bin/bash
+# round 2, run J: per-block flags (fine) vs per-group counters, lag and L2 hints once more
+set -x
+cd "$GRAFT_REPO_ROOT" 2>/dev/null || cd /root/repo
+O=gpurun_out/r02j; mkdir -p $O
+timeout 200 python -m pytest tests/test_gpu_parity.py -x -q -m gpu -k "d3q19" > $O/pytest_d3q19.log 2>&1; rc=$?; echo "pytest rc=$rc" >> $O/pytest_d3q19.log
+tail -3 $O/pytest_d3q19.log
+if [ $rc -ne 0 ]; then echo "parity failed or hung: stopping"; exit 1; fi
+B="python bench.py --steps 30 --warmup 5 --no-e2e --no-cpu --no-secondary"
+run() { n=$1; shift; env "$@" timeout 100 $B --variant 0 > $O/bench_$n.json 2> $O/bench_$n.err; r=$?; echo "$n rc=$r"; if [ $r -eq 124 ]; then echo "hung: stopping"; exit 1; fi; }
+run coarse_p1_k1.5 LBM_TUNE_FINE=0 LBM_TUNE_POL=1
+run fine_p1_k1.5 LBM_TUNE_POL=1
+run fine_p1_k1.25 LBM_TUNE_POL=1 LBM_TUNE_LAGK=1.25
+run fine_p1_k1.0 LBM_TUNE_POL=1 LBM_TUNE_LAGK=1.0
+run fine_p1_k0.75 LBM_TUNE_POL=1 LBM_TUNE_LAGK=0.75
+run fine_p1_k2.0 LBM_TUNE_POL=1 LBM_TUNE_LAGK=2.0
+run fine_p2_k1.5 LBM_TUNE_POL=2
+run fine_p2_k1.0 LBM_TUNE_POL=2 LBM_TUNE_LAGK=1.0
+run fine_p0_k1.0 LBM_TUNE_POL=0 LBM_TUNE_LAGK=1.0
+run coarse_p2_k1.5 LBM_TUNE_FINE=0 LBM_TUNE_POL=2
+for f in $O/bench_*.json; do echo $f; python - "$f" <<'PY'
+import json,sys
+try:
+    d=json.loads(open(sys.argv[1]).read().strip().splitlines()[-1])
+    print(round(d["value"]),round(d["ms_per_step"],3),round(d["roofline"].get("step_frac"),4),{k:round(v["ms"]/v["launches"],3) for k,v in d["roofline"]["kernels"].items()},d.get("phase_fallbacks"))
+except Exception as e: print("ERR",e)
+PY
+done | tee $O/summary.txt
+echo done

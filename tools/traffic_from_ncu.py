@@ -25,6 +25,8 @@ def main():
     for d in launches.values():
         m = re.search(r"(k_[a-z_0-9]+)(<[^>]*>)?", d["name"])
         base, targs = m.group(1), m.group(2) or ""
+        if base == "k_step_one" and targs.endswith(", 0>"):
+            base = "k_collide_core"      # k_step_one<.., PHI = false>: the name the library's profiler gives the collide-only launches
         # output-step flavours (<FXY, WRITE=1, ...>) also write the four macroscopic fields: one step in a hundred
         if base.startswith("k_collide") and re.match(r"<\d+, 1", targs):
             continue
