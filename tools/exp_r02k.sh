@@ -10,7 +10,7 @@ timeout 600 python -m pytest tests/test_gpu_multi.py tests/test_gpu_hosts.py -x 
 tail -12 $O/pytest_multi.log
 if [ $rc -ne 0 ]; then echo "multi-GPU tests failed: stopping"; exit 1; fi
 TR="python -m torch.distributed.run --nnodes=1 --master-addr 127.0.0.1"
-for n in 2 4 8; do
+for n in ${BENCH_N:-2 4 8}; do
   if [ $n -le $NG ]; then
     timeout 420 $TR --nproc-per-node $n --master-port $((29600+n)) bench.py --gpus $n --steps 50 --warmup 5 > $O/bench_n$n.json 2> $O/bench_n$n.err; echo "bench n=$n rc=$?"
     tail -c 400 $O/bench_n$n.json
