@@ -94,6 +94,12 @@ typedef struct {
                                   the reference's BGK collision; Lambda > 0 relaxes the antisymmetric half of f with
                                   omega- = 1/(Lambda/(tau-1/2) + 1/2) (two-relaxation-time), everything else unchanged.
                                   Parity unpinned: validated against the BGK limit Lambda = (tau-1/2)^2. */
+    double mrt_rates[5];       /* LBM_BINARY_D3Q19 only, EXTENSION with no counterpart in the reference: all 0 (default)
+                                  keeps BGK; otherwise f collides in the moment space of d'Humieres et al. (2002) with
+                                  the stress moments at 1/tau (the reference's viscosity) and these rates for the energy,
+                                  energy-square, heat-flux, fourth-order and third-order moments (an entry <= 0 means
+                                  1/tau; e.g. {1.19, 1.4, 1.2, 1.4, 1.98}).  Excludes trt_magic.  Parity unpinned:
+                                  validated against the BGK limit (all rates 1/tau) and by momentum/mass balances. */
 } lbm_config;
 
 /* Fills *cfg with the constants of the reference program for `model`

@@ -37,7 +37,7 @@ class Config(C.Structure):
                 ("omega", C.c_double), ("omega_bulk", C.c_double), ("force_ampl", C.c_double),
                 ("ce", C.c_double), ("conc_wall", C.c_double),
                 ("device", C.c_int), ("slab_rank", C.c_int), ("slab_count", C.c_int), ("kernel_variant", C.c_int),
-                ("trt_magic", C.c_double)]
+                ("trt_magic", C.c_double), ("mrt_rates", C.c_double * 5)]
 
 
 _LIB_F32 = os.path.join(_PKG, "liblbm_b200_f32.so")

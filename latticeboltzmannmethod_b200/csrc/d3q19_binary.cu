@@ -48,7 +48,7 @@ __global__ void __launch_bounds__(kThreads) k_collide_push(Geom g, Params P, con
 // select on the ten directions with cx != 0 (PART 3 of collide_push_node), so they stay in the coalesced warps.
 // The rim kernel runs the rows iY = 1 and NY-2 (and, on output steps, the wall-node fields).
 // zsel: planes zs0 .. zs0+n0-1 come first in blockIdx.y, then planes zs1 .. (both ends of a slab in one launch).
-template <bool FXY, bool WRITE, bool TRT = false>
+template <bool FXY, bool WRITE, int COLL = 0>
 __global__ void __launch_bounds__(128, 3) k_collide_interior(Geom g, Params P, const pop_t *__restrict__ fin,
                                                               const pop_t *__restrict__ gin, const double *__restrict__ phi,
                                                               pop_t *__restrict__ fout, pop_t *__restrict__ gout, FieldsOut o,
@@ -70,10 +70,10 @@ __global__ void __launch_bounds__(128, 3) k_collide_interior(Geom g, Params P, c
         G[k] = __ldg(pg + k * pl);
         PH[k] = __ldg(phi + (long long)(zs + CZ[k]) * pl + idx + CY[k] * NX + CX[k]);
     }
-    lbm3::collide_push_node<FXY, WRITE, 3, TRT>(g, P, F, G, PH, fout, gout, o, zs, ix, iy);
+    lbm3::collide_push_node<FXY, WRITE, 3, COLL>(g, P, F, G, PH, fout, gout, o, zs, ix, iy);
 }
 
-template <bool FXY, bool WRITE, bool TRT = false>
+template <bool FXY, bool WRITE, int COLL = 0>
 __global__ void __launch_bounds__(128) k_collide_rim(Geom g, Params P, const pop_t *__restrict__ fin,
                                                      const pop_t *__restrict__ gin, const double *__restrict__ phi,
                                                      pop_t *__restrict__ fout, pop_t *__restrict__ gout, FieldsOut o,
@@ -109,8 +109,8 @@ __global__ void __launch_bounds__(128) k_collide_rim(Geom g, Params P, const pop
         G[k] = gin[lbm3::pop_index(g, zs, k, idx)];
         PH[k] = phi[(long long)(zs + CZ[k]) * pl + idx + CY[k] * NX + CX[k]];
     }
-    if (TRT) {   // the two-rate extension exists in the array form of the collision only
-        lbm3::collide_push_node<FXY, WRITE, 0, true>(g, P, F, G, PH, fout, gout, o, zs, ix, iy);
+    if (COLL != 0) {   // the TRT and MRT extensions exist in the array form of the collision only
+        lbm3::collide_push_node<FXY, WRITE, 0, COLL>(g, P, F, G, PH, fout, gout, o, zs, ix, iy);
         return;
     }
     // compile-time direction indices in the folded push (no table look-ups in local memory)
@@ -225,7 +225,8 @@ public:
     // kernel_variant: 0 one-pass step (collide + next step's phase field in one launch, d3q19_step.cuh); 5 two-pass
     // (k_phase, then the collide kernels); 1 two-pass with the plain whole-plane collide kernel (the cross-check).
     // The TRT extension exists in the array form of the collision only and always takes the two-pass path.
-    bool one_pass() const { return cfg_.kernel_variant == 0 && P_.trt_magic <= 0.0; }
+    int coll() const { return mrt_ ? 2 : (P_.trt_magic > 0.0 ? 1 : 0); }
+    bool one_pass() const { return cfg_.kernel_variant == 0 && coll() == 0; }
 
     lbm_status setup()
     {
@@ -249,8 +250,14 @@ public:
         P_.phase_gradient = cfg_.wall_gradient; P_.rho_wall = cfg_.rho_wall;
         P_.trt_magic = cfg_.trt_magic;
         if (cfg_.trt_magic < 0.0) return rt_.fail(LBM_EINVAL, "trt_magic must be >= 0 (0 = BGK, the reference's collision)");
-        if (cfg_.trt_magic > 0.0 && cfg_.kernel_variant == 1)
-            return rt_.fail(LBM_EINVAL, "the TRT extension exists for kernel_variant 0 and 5 only");
+        for (int i = 0; i < 5; i++) {
+            P_.mrt[i] = cfg_.mrt_rates[i];
+            mrt_ = mrt_ || cfg_.mrt_rates[i] != 0.0;
+            if (cfg_.mrt_rates[i] >= 2.0) return rt_.fail(LBM_EINVAL, "mrt_rates must be below 2 (<= 0: use 1/tau)");
+        }
+        if (mrt_ && cfg_.trt_magic > 0.0) return rt_.fail(LBM_EINVAL, "trt_magic and mrt_rates exclude each other");
+        if (coll() != 0 && cfg_.kernel_variant == 1)
+            return rt_.fail(LBM_EINVAL, "the TRT and MRT extensions exist for kernel_variant 0 and 5 only");
         fxy_ = P_.fx != 0.0 || P_.fy != 0.0;
 
         const size_t pop_bytes = (size_t)(g_.nz + 4) * 19 * g_.pl * sizeof(pop_t);
@@ -366,14 +373,15 @@ public:
     dim3 plane_grid(int planes) const { return dim3((unsigned)(((long long)g_.nx * g_.ny + kThreads - 1) / kThreads), planes); }
     FieldsOut fields_out() const { return FieldsOut{rho_, ux_, uy_, uz_}; }
 
-    // compile-time flavour of a collide kernel from the run-time switches: fn(FXY, WRITE, TRT) with std::bool_constant tags
+    // compile-time flavour of a collide kernel from the run-time switches: fn(FXY, WRITE, COLL) with integral_constant tags
     template <class Fn>
     void with_flavour(int write_fields, Fn &&fn)
     {
-        const bool trt = P_.trt_magic > 0.0;
+        const int c = coll();
         auto l3 = [&](auto fxy, auto wr) {
-            if (trt) fn(fxy, wr, std::true_type{});
-            else fn(fxy, wr, std::false_type{});
+            if (c == 2) fn(fxy, wr, std::integral_constant<int, 2>{});
+            else if (c == 1) fn(fxy, wr, std::integral_constant<int, 1>{});
+            else fn(fxy, wr, std::integral_constant<int, 0>{});
         };
         auto l2 = [&](auto fxy) {
             if (write_fields) l3(fxy, std::true_type{});
@@ -469,7 +477,7 @@ public:
     // the array form of the collision only) the register kernel
     lbm_status collide_bulk(int zs0, int n0, int zs1, int n1, int write_fields)
     {
-        if (P_.trt_magic > 0.0) return collide_interior(zs0, n0, zs1, n1, write_fields);
+        if (coll() != 0) return collide_interior(zs0, n0, zs1, n1, write_fields);
         return collide_core(zs0, n0, zs1, n1, write_fields);
     }
 
@@ -780,7 +788,7 @@ private:
     lbm_config cfg_;
     Geom g_{};
     Params P_{};
-    bool fxy_ = false;
+    bool fxy_ = false, mrt_ = false;
     int z_begin_ = 0, cur_ = 0;
     pop_t *f_[2] = {nullptr, nullptr}, *gq_[2] = {nullptr, nullptr};
     // phase field: phib_[pf_] belongs to the front populations (valid when phi_valid_), phib_[po_] is the public one

@@ -34,7 +34,38 @@ struct Params {
     double fx, fy, fz;
     double phase_gradient, rho_wall;
     double trt_magic;          // 0: BGK as in the reference; > 0: two-relaxation-time collision of f (extension, no reference)
+    double mrt[5];             // all 0: off; else multiple-relaxation-time collision of f (extension): rates of the energy,
+                               // energy-square, heat-flux, fourth-order and third-order moments; an entry <= 0 means 1/tau
 };
+
+// Moment basis of d'Humieres et al. (Phil. Trans. R. Soc. A 360, 2002) for D3Q19, row i as a polynomial of the
+// direction (cx, cy, cz): density, energy e, energy square eps, j_x, q_x, j_y, q_y, j_z, q_z, 3p_xx, 3pi_xx, p_ww, pi_ww,
+// p_xy, p_yz, p_xz, m_x, m_y, m_z.  The rows are mutually orthogonal, so M^-1 = M^T diag(1 / |row|^2).
+LBM_HD constexpr int mrt19_row(int i, int cx, int cy, int cz)
+{
+    const int c2 = cx * cx + cy * cy + cz * cz;
+    switch (i) {
+    case 0: return 1;
+    case 1: return 19 * c2 - 30;
+    case 2: return (21 * c2 * c2 - 53 * c2 + 24) / 2;
+    case 3: return cx;
+    case 4: return (5 * c2 - 9) * cx;
+    case 5: return cy;
+    case 6: return (5 * c2 - 9) * cy;
+    case 7: return cz;
+    case 8: return (5 * c2 - 9) * cz;
+    case 9: return 3 * cx * cx - c2;
+    case 10: return (3 * c2 - 5) * (3 * cx * cx - c2);
+    case 11: return cy * cy - cz * cz;
+    case 12: return (3 * c2 - 5) * (cy * cy - cz * cz);
+    case 13: return cx * cy;
+    case 14: return cy * cz;
+    case 15: return cx * cz;
+    case 16: return (cy * cy - cz * cz) * cx;
+    case 17: return (cz * cz - cx * cx) * cy;
+    default: return (cx * cx - cy * cy) * cz;
+    }
+}
 
 // direction table of descriptor.h:43-45 for the code that is not unrolled
 #define LBM3_CX {0, 1, -1, 0, 0, 0, 0, 1, -1, 1, -1, 0, 0, 0, 0, 1, -1, 1, -1}
@@ -84,12 +115,18 @@ LBM_HD void moments(const double *F, double &rho, double &ux, double &uy, double
 // FXY = false is the fast path for force_x == force_y == 0 (both shipped
 // configurations): the x and y force terms are then exact zeros in the reference.
 //
-// TRT = true is an EXTENSION with no counterpart in the reference (the north star names TRT on D3Q19, the reference
+// COLL selects the collision operator of f: 0 the reference's BGK; 1 (TRT) and 2 (MRT) are EXTENSIONS.
+// COLL = 2, multiple relaxation times: the non-equilibrium part of f is taken to the moment space of mrt19_row, every
+// moment relaxed with its own rate -- the stress moments (rows 9, 11, 13-15) with 1/tau, which keeps the reference's
+// viscosity, density and momentum rows with 1/tau as well, the other five groups with P.mrt[] -- and brought back; the
+// Guo force populations go the same way with (1 - s_i/2) per moment, so that a step adds exactly F to the momentum.
+// Equilibria and the g collision are the reference's.  With every rate equal to 1/tau the scheme is BGK up to rounding.
+// COLL = 1 is an EXTENSION with no counterpart in the reference (the north star names TRT on D3Q19, the reference
 // has none): the f populations relax with two rates -- the symmetric part (f_k + f_kbar)/2 with omega+ = 1/tau, which
 // keeps the reference's viscosity, the antisymmetric part with omega- = 1/(Lambda/(tau - 1/2) + 1/2), Lambda =
 // P.trt_magic -- while equilibria, Guo force populations and the g collision stay exactly the reference's.  With
 // Lambda = (tau - 1/2)^2 both rates coincide and the scheme is BGK up to rounding; that limit is the validation.
-template <bool FXY, bool TRT = false>
+template <bool FXY, int COLL = 0>
 LBM_HD void collide(double *F, double *G, double ph, double gx, double gy, double gz, double lap, const Params &P,
                     double &rho, double &ux, double &uy, double &uz)
 {
@@ -172,7 +209,7 @@ LBM_HD void collide(double *F, double *G, double ph, double gx, double gy, doubl
     // lattice.hpp:465-467
     const double tau = P.tau_gas + (ph + 1.0) / 2.0 * P.dtau;
     const double omega = 1.0 / tau;
-    const double pref = 1.0 - 0.5 * omega;
+    const double pref = COLL == 2 ? 1.0 : 1.0 - 0.5 * omega;   // MRT applies (1 - s_i/2) per moment instead
     const double pw6 = pref * w6, pw12 = pref * w12;
 
     // Guo force populations, lattice.hpp:472-480
@@ -212,7 +249,45 @@ LBM_HD void collide(double *F, double *G, double ph, double gx, double gy, doubl
 
     // lattice.hpp:483-488
     const double mo = -omega, mop = -P.omega_phi;
-    if (TRT) {
+    if (COLL == 2) {
+        constexpr int MX[19] = LBM3_CX, MY[19] = LBM3_CY, MZ[19] = LBM3_CZ;
+        const double se = P.mrt[0] > 0.0 ? P.mrt[0] : omega, seps = P.mrt[1] > 0.0 ? P.mrt[1] : omega;
+        const double sq = P.mrt[2] > 0.0 ? P.mrt[2] : omega, spi = P.mrt[3] > 0.0 ? P.mrt[3] : omega;
+        const double sm = P.mrt[4] > 0.0 ? P.mrt[4] : omega;
+        const double S[19] = {omega, se, seps, omega, sq, omega, sq, omega, sq, omega, spi, omega, spi, omega, omega, omega, sm, sm, sm};
+        double fn[19], t[19];
+#pragma unroll
+        for (int k = 0; k < 19; k++) fn[k] = F[k] - feq[k];
+#pragma unroll
+        for (int i = 0; i < 19; i++) {
+            double m = 0.0, mf = 0.0;
+            int norm = 0;
+#pragma unroll
+            for (int k = 0; k < 19; k++) {
+                const int e = mrt19_row(i, MX[k], MY[k], MZ[k]);
+                norm += e * e;
+                if (e != 0) {
+                    m += (double)e * fn[k];
+                    mf += (double)e * fp[k];
+                }
+            }
+            const double inv = 1.0 / (double)norm;
+            t[i] = mf * ((1.0 - 0.5 * S[i]) * inv) - m * (S[i] * inv);
+        }
+#pragma unroll
+        for (int k = 0; k < 19; k++) {
+            double a = 0.0;
+#pragma unroll
+            for (int i = 0; i < 19; i++) {
+                const int e = mrt19_row(i, MX[k], MY[k], MZ[k]);
+                if (e != 0) a += (double)e * t[i];
+            }
+            F[k] += a;
+            G[k] += mop * (G[k] - geq[k]);
+        }
+        return;
+    }
+    if (COLL == 1) {
         const double omega_minus = 1.0 / (P.trt_magic / (tau - 0.5) + 0.5);
         // the force populations split like the populations themselves: the symmetric half keeps Guo's prefactor
         // (1 - omega/2) that fp[] already carries, the antisymmetric half -- the one that injects momentum -- takes

@@ -132,7 +132,7 @@ struct PlainStore {   // how the interior push writes a value: plain stores (ker
     LBM_HD void f(pop_t *p, double v) const { *p = (pop_t)v; }
     LBM_HD void g(pop_t *p, double v) const { *p = (pop_t)v; }
 };
-template <bool FXY, bool WRITE, int PART = 0, bool TRT = false, class ST = PlainStore>
+template <bool FXY, bool WRITE, int PART = 0, int COLL = 0, class ST = PlainStore>
 LBM_HD void collide_push_node(const Geom &g, const Params &P, double *F, double *G, const double *PH, pop_t *fout,
                               pop_t *gout, const FieldsOut &o, int zs, int ix, int iy, const ST &st = ST())
 {
@@ -147,7 +147,7 @@ LBM_HD void collide_push_node(const Geom &g, const Params &P, double *F, double 
         if (PART != 3 && ix == 1 && iy == 1) mirror_fields<3>(F, P, o, (long long)(zs - 2) * g.pl);
     }
     double rho, ux, uy, uz;
-    collide<FXY, TRT>(F, G, PH[0], gx, gy, gz, lap, P, rho, ux, uy, uz);
+    collide<FXY, COLL>(F, G, PH[0], gx, gy, gz, lap, P, rho, ux, uy, uz);
     if (WRITE && own) {
         const long long at = (long long)(zs - 2) * g.pl + idx;
         o.rho[at] = rho; o.ux[at] = ux; o.uy[at] = uy; o.uz[at] = uz;

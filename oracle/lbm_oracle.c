@@ -22,6 +22,33 @@ static const int C3Y[19] = {0, 0, 0, 1, -1, 0, 0, 1, 1, -1, -1, 1, -1, 1, -1, 0,
 static const int C3Z[19] = {0, 0, 0, 0, 0, 1, -1, 0, 0, 0, 0, 1, 1, -1, -1, 1, 1, -1, -1};
 /* opposite direction, descriptor.h:98 */
 static const int OPP3[19] = {0, 2, 1, 4, 3, 6, 5, 10, 9, 8, 7, 14, 13, 12, 11, 18, 17, 16, 15};
+/* moment basis of d'Humieres et al., Phil. Trans. R. Soc. A 360 (2002), for D3Q19: row i as a polynomial of the
+ * direction; used only by the MRT extension (no reference counterpart) */
+static int mrt19_entry(int i, int cx, int cy, int cz)
+{
+    int c2 = cx * cx + cy * cy + cz * cz;
+    switch (i) {
+    case 0: return 1;
+    case 1: return 19 * c2 - 30;
+    case 2: return (21 * c2 * c2 - 53 * c2 + 24) / 2;
+    case 3: return cx;
+    case 4: return (5 * c2 - 9) * cx;
+    case 5: return cy;
+    case 6: return (5 * c2 - 9) * cy;
+    case 7: return cz;
+    case 8: return (5 * c2 - 9) * cz;
+    case 9: return 3 * cx * cx - c2;
+    case 10: return (3 * c2 - 5) * (3 * cx * cx - c2);
+    case 11: return cy * cy - cz * cz;
+    case 12: return (3 * c2 - 5) * (cy * cy - cz * cz);
+    case 13: return cx * cy;
+    case 14: return cy * cz;
+    case 15: return cx * cz;
+    case 16: return (cy * cy - cz * cz) * cx;
+    case 17: return (cz * cz - cx * cx) * cy;
+    default: return (cx * cx - cy * cy) * cz;
+    }
+}
 
 static double W3[19];                                    /* descriptor.h:82-84 (3*w, rest 0) */
 static double QXX[19], QYY[19], QZZ[19], QXY[19], QXZ[19], QYZ[19];  /* descriptor.h:47-61 */
@@ -92,6 +119,8 @@ struct lbo3 {
     double *rho, *ux, *uy, *uz;/* [nz][pl] */
     double aconst, kconst, gammaconst, phase_gradient, rho_wall, tau_phi, tau_liq, tau_gas, fx, fy, fz;
     double trt_magic;          /* 0: the reference's BGK; > 0: the two-relaxation-time EXTENSION (no reference counterpart) */
+    double mrt[5];             /* all 0: off; else the multiple-relaxation-time EXTENSION (no reference counterpart) */
+    int mrt_on;
 };
 
 static inline size_t pidx(const lbo3 *s, int zs, int k, size_t node)
@@ -351,16 +380,46 @@ void lbo3_collide(lbo3 *s, int write_fields)
                 double sum_force = 0.0;
                 for (int k = 1; k < 19; k++) {
                     int cx = C3X[k], cy = C3Y[k], cz = C3Z[k];
-                    fp[k] = (1.0 - 0.5 * omega_rho) * W3[k] *
+                    fp[k] = (s->mrt_on ? 1.0 : 1.0 - 0.5 * omega_rho) * W3[k] *
                             (s->fx * ((cx - ux) + 3.0 * cx * (cx * ux + cy * uy + cz * uz)) +
                              s->fy * ((cy - uy) + 3.0 * cy * (cx * ux + cy * uy + cz * uz)) +
                              s->fz * ((cz - uz) + 3.0 * cz * (cx * ux + cy * uy + cz * uz)));
                     sum_force += fp[k];
                 }
                 fp[0] = -sum_force;
+                /* extension (no reference counterpart): multiple relaxation times for f in the moment basis of
+                 * d'Humieres et al. (2002), stress moments at 1/tau, Guo force populations with (1 - s_i/2) per moment */
+                if (s->mrt_on) {
+                    double se = s->mrt[0] > 0.0 ? s->mrt[0] : omega_rho, seps = s->mrt[1] > 0.0 ? s->mrt[1] : omega_rho;
+                    double sq = s->mrt[2] > 0.0 ? s->mrt[2] : omega_rho, spi = s->mrt[3] > 0.0 ? s->mrt[3] : omega_rho;
+                    double sm = s->mrt[4] > 0.0 ? s->mrt[4] : omega_rho;
+                    double S[19] = {omega_rho, se, seps, omega_rho, sq, omega_rho, sq, omega_rho, sq, omega_rho, spi, omega_rho, spi,
+                                    omega_rho, omega_rho, omega_rho, sm, sm, sm};
+                    double fn[19], t[19];
+                    for (int k = 0; k < 19; k++) fn[k] = F[k] - feq[k];
+                    for (int i = 0; i < 19; i++) {
+                        double m = 0.0, mf = 0.0;
+                        int norm = 0;
+                        for (int k = 0; k < 19; k++) {
+                            int e = mrt19_entry(i, C3X[k], C3Y[k], C3Z[k]);
+                            norm += e * e;
+                            if (e != 0) { m += (double)e * fn[k]; mf += (double)e * fp[k]; }
+                        }
+                        double inv = 1.0 / (double)norm;
+                        t[i] = mf * ((1.0 - 0.5 * S[i]) * inv) - m * (S[i] * inv);
+                    }
+                    for (int k = 0; k < 19; k++) {
+                        double a = 0.0;
+                        for (int i = 0; i < 19; i++) {
+                            int e = mrt19_entry(i, C3X[k], C3Y[k], C3Z[k]);
+                            if (e != 0) a += (double)e * t[i];
+                        }
+                        F[k] += a;
+                    }
+                }
                 /* extension (no reference counterpart): two relaxation rates for f -- the symmetric half of every pair
                  * (k, opposite k) with omega+ = 1/tau, the antisymmetric half with omega- from the magic parameter */
-                if (s->trt_magic > 0.0) {
+                if (!s->mrt_on && s->trt_magic > 0.0) {
                     const double omega_minus = 1.0 / (s->trt_magic / (tau - 0.5) + 0.5);
                     const double fr = (1.0 - 0.5 * omega_minus) / (1.0 - 0.5 * omega_rho);
                     F[0] = (F[0] - omega_rho * (F[0] - feq[0])) + fp[0];
@@ -379,7 +438,7 @@ void lbo3_collide(lbo3 *s, int write_fields)
                 }
                 /* lattice.hpp:483-488 then the push */
                 for (int k = 0; k < 19; k++) {
-                    if (s->trt_magic <= 0.0) F[k] += -omega_rho * (F[k] - feq[k]) + fp[k];
+                    if (s->trt_magic <= 0.0 && !s->mrt_on) F[k] += -omega_rho * (F[k] - feq[k]) + fp[k];
                     G[k] += -omega_phi * (G[k] - geq[k]);
                     int tx, ty, dz;
                     int kk = push_target(s, ix, iy, k, &tx, &ty, &dz);
@@ -533,6 +592,11 @@ void lbo3_get_pops(lbo3 *s, double *f, double *g)
 }
 
 void lbo3_set_trt(lbo3 *s, double magic) { s->trt_magic = magic; }
+void lbo3_set_mrt(lbo3 *s, const double *rates5)
+{
+    s->mrt_on = 0;
+    for (int i = 0; i < 5; i++) { s->mrt[i] = rates5[i]; if (rates5[i] != 0.0) s->mrt_on = 1; }
+}
 
 void lbo3_set_pops(lbo3 *s, const double *f, const double *g)
 {

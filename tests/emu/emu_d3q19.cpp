@@ -37,21 +37,23 @@ Emu *emu3_create(int nx, int ny, int nz, const double *p)
     return e;
 }
 void emu3_destroy(Emu *e) { delete e; }
-// one node through collide<>() of d3q19_node.h: F, G in/out; PH = the 19 neighbour phase values; out4 = rho, ux, uy, uz
-void emu3_collide_node(const double *p, double trt_magic, double *F, double *G, const double *PH, double *out4)
+// one node through collide<>() of d3q19_node.h: F, G in/out; PH = the 19 neighbour phase values; out4 = rho, ux, uy, uz;
+// mrt5: the five free rates of the MRT extension (all 0: off)
+void emu3_collide_node(const double *p, double trt_magic, const double *mrt5, double *F, double *G, const double *PH, double *out4)
 {
     Params P{};
     P.aconst = p[0]; P.kconst = p[1]; P.gammaconst = p[2]; P.phase_gradient = p[3];
     P.rho_wall = p[5]; P.omega_phi = 1.0 / p[6]; P.tau_gas = p[8]; P.dtau = p[7] - p[8];
     P.fx = p[9]; P.fy = p[10]; P.fz = p[11];
     P.trt_magic = trt_magic;
+    bool mrt = false;
+    for (int i = 0; i < 5; i++) { P.mrt[i] = mrt5[i]; mrt = mrt || mrt5[i] != 0.0; }
     double gx, gy, gz, lap;
     stencils(PH, gx, gy, gz, lap);
-    if (trt_magic > 0.0) collide<true, true>(F, G, PH[0], gx, gy, gz, lap, P, out4[0], out4[1], out4[2], out4[3]);
-    else collide<true, false>(F, G, PH[0], gx, gy, gz, lap, P, out4[0], out4[1], out4[2], out4[3]);
+    if (mrt) collide<true, 2>(F, G, PH[0], gx, gy, gz, lap, P, out4[0], out4[1], out4[2], out4[3]);
+    else if (trt_magic > 0.0) collide<true, 1>(F, G, PH[0], gx, gy, gz, lap, P, out4[0], out4[1], out4[2], out4[3]);
+    else collide<true, 0>(F, G, PH[0], gx, gy, gz, lap, P, out4[0], out4[1], out4[2], out4[3]);
 }
-void emu3_use_streamed(Emu *e, int on) { e->streamed = on; }
-
 static void put(Emu *e, double *dst, const double *src)
 {
     size_t n = (size_t)e->g.nx * e->g.ny;

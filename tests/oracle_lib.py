@@ -125,6 +125,12 @@ class Oracle3D:
         self.h = self.L.lbo3_create(nx, ny, nz, _p(p))
         assert self.h
 
+    def set_mrt(self, rates5):
+        """Extension without a reference counterpart: multiple-relaxation-time collision of f (all 0 = BGK)."""
+        r = (C.c_double * 5)(*rates5)
+        self.L.lbo3_set_mrt.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
+        self.L.lbo3_set_mrt(self.h, r)
+
     def set_trt(self, magic):
         """Extension without a reference counterpart: two-relaxation-time collision of f (0 = the reference's BGK)."""
         self.L.lbo3_set_trt.argtypes = [C.c_void_p, C.c_double]

@@ -57,8 +57,9 @@ def test_trt_collision_adds_exactly_the_force_to_the_momentum(emu_libs, magic, t
     import ctypes as C
     L = C.CDLL(emu_libs["d3q19"])
     dp = C.POINTER(C.c_double)
-    L.emu3_collide_node.argtypes = [dp, C.c_double, dp, dp, dp, dp]
+    L.emu3_collide_node.argtypes = [dp, C.c_double, dp, dp, dp, dp, dp]
     L.emu3_collide_node.restype = None
+    no_mrt = np.zeros(5)
     cx = np.array([0, 1, -1, 0, 0, 0, 0, 1, -1, 1, -1, 0, 0, 0, 0, 1, -1, 1, -1], dtype=np.float64)
     cy = np.array([0, 0, 0, 1, -1, 0, 0, 1, 1, -1, -1, 1, -1, 1, -1, 0, 0, 0, 0], dtype=np.float64)
     cz = np.array([0, 0, 0, 0, 0, 1, -1, 0, 0, 0, 0, 1, 1, -1, -1, 1, 1, -1, -1], dtype=np.float64)
@@ -75,7 +76,7 @@ def test_trt_collision_adds_exactly_the_force_to_the_momentum(emu_libs, magic, t
         G[0] += ph0 - G.sum()                                   # g sums to the phase value the stencil sees
         F0, G0 = F.copy(), G.copy()
         out4 = np.zeros(4)
-        L.emu3_collide_node(params.ctypes.data_as(dp), magic, F.ctypes.data_as(dp), G.ctypes.data_as(dp),
+        L.emu3_collide_node(params.ctypes.data_as(dp), magic, no_mrt.ctypes.data_as(dp), F.ctypes.data_as(dp), G.ctypes.data_as(dp),
                             PH.ctypes.data_as(dp), out4.ctypes.data_as(dp))
         for c, fc in zip((cx, cy, cz), force):
             assert abs((c * F).sum() - (c * F0).sum() - fc) <= 1e-15 * 19, (trial, magic)
