@@ -285,8 +285,8 @@ public:
             // nodes; the phase part trails the collide part by `lag_` plane-steps = kLagWindows times the number of
             // blocks the GPU holds at once (measured at 512^3: 1.0 -> 16.4, 1.25 -> 16.2, 1.5 -> 15.3, 1.75 -> 15.4,
             // 2 -> 15.5, 3 -> 16.3 ms: shorter and blocks wait for their producers, longer and L2 loses the g* rows).
-            if ((long long)g_.nx * g_.ny >= (1ll << 30) || g_.nz + 4 + 64 > 65535)
-                return rt_.fail(LBM_EINVAL, "D3Q19 one-pass step: a plane must hold fewer than 2^30 nodes and a slab fewer than 65 000 planes (use kernel_variant 5)");
+            if (g_.pl * 40 >= (1ll << 31) || g_.nz + 4 + 64 > 65535)
+                return rt_.fail(LBM_EINVAL, "D3Q19 one-pass step: a plane must hold fewer than 53 million nodes and a slab fewer than 65 000 planes (use kernel_variant 1)");
             int sms = 148;
             cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, rt_.device);
             double lag_windows = 1.5;
@@ -297,7 +297,6 @@ public:
             sb_ = std::max(64, 2 * dshift_);
             if (nblk_ + dshift_ <= sb_) sb_ = nblk_ + dshift_;   // one strip
             nstrips_ = (nblk_ + dshift_ + sb_ - 1) / sb_;
-            if (const char *e = getenv("LBM_TUNE_TIGHT")) if (atoi(e)) sb_ = std::max((nblk_ + dshift_ + nstrips_ - 1) / nstrips_, 2 * dshift_);   // same strip count, least padding
             lag_ = 2 + (int)(lag_windows * (sms * 4) / sb_);
             ctrl_words_ = ((size_t)nstrips_ * (g_.nz + 4 + lag_) + 2) * lbm3::LAG_PAD + 64;
             LBM_CUDA(rt_, rt_.dev_alloc(&ctrl_, ctrl_words_ * sizeof(unsigned)));

@@ -121,8 +121,8 @@ struct HintedStore {
 template <class ST>
 struct PushXRim {
     pop_t *fo, *go;      // fout/gout + pop_index(zs, 0, idx)
-    long long pl;
-    int nx;
+    int pl, nx;          // plane pitch and row length: offsets from fo/go stay below 2^31 elements (checked at set-up), so
+                         // an address is ONE 32x32+64 multiply-add from a 32-bit offset, and the select is on 32 bits
     bool xlo, xhi;
     ST st;
     template <int K>
@@ -131,13 +131,13 @@ struct PushXRim {
         constexpr int CX[19] = LBM3_CX, CY[19] = LBM3_CY, CZ[19] = LBM3_CZ;
         constexpr int OPP[19] = {0, 2, 1, 4, 3, 6, 5, 10, 9, 8, 7, 14, 13, 12, 11, 18, 17, 16, 15};
         constexpr int SYMX[19] = {0, 2, 1, 3, 4, 5, 6, 8, 7, 10, 9, 11, 12, 13, 14, 16, 15, 18, 17};
-        long long off = (long long)(CZ[K] * 19 + K) * pl + (CY[K] * nx + CX[K]);
+        int off = (CZ[K] * 19 + K) * pl + (CY[K] * nx + CX[K]);
         if (CX[K] == -1) {   // into the x mirror line: reflected, stays in column 1 (lattice.hpp:534-557)
-            const long long om = (long long)(CZ[K] * 19 + SYMX[K]) * pl + CY[K] * nx;
+            const int om = (CZ[K] * 19 + SYMX[K]) * pl + CY[K] * nx;
             off = xlo ? om : off;
         }
         if (CX[K] == 1) {    // into the x wall: back to its own node reversed (lattice.hpp:609-626)
-            const long long ob = (long long)OPP[K] * pl;
+            const int ob = OPP[K] * pl;
             off = xhi ? ob : off;
         }
         st.f(fo + off, fv);
@@ -217,11 +217,13 @@ k_step_one(Geom g, Params P, const pop_t *__restrict__ fin, const pop_t *__restr
         double F[19], PH[19];
         if (do_c) {
             const pop_t *pf = fin + pop_index(g, zs, 0, idx);
+            const double *pp = phi + (long long)zs * pl + idx;
+            const int pl32 = (int)pl;            // 19 pl < 2^31 (set-up): 32-bit offsets from one 64-bit base each
             constexpr int CX[19] = LBM3_CX, CY[19] = LBM3_CY, CZ[19] = LBM3_CZ;
 #pragma unroll
             for (int k = 0; k < 19; k++) {
-                F[k] = POL == 1 ? lag_ld_hint(pf + k * pl, pol_first) : (double)__ldg(pf + k * pl);
-                PH[k] = __ldg(phi + (long long)(zs + CZ[k]) * pl + idx + CY[k] * NX + CX[k]);
+                F[k] = POL == 1 ? lag_ld_hint(pf + k * pl32, pol_first) : (double)__ldg(pf + k * pl32);
+                PH[k] = __ldg(pp + (CZ[k] * pl32 + CY[k] * NX + CX[k]));
             }
         }
         if (c_plane && bbase + wbase < nplane)
@@ -251,10 +253,10 @@ k_step_one(Geom g, Params P, const pop_t *__restrict__ fin, const pop_t *__restr
             const long long base = pop_index(g, zs, 0, idx);
             double rho, ux, uy, uz;
             if (POL == 1)
-                collide_streamed<FXY>(F, getG, PushXRim<HintedStore>{fout + base, gout + base, pl, NX, ix == 1, ix == NX - 2, HintedStore{pol_first, pol_last}},
+                collide_streamed<FXY>(F, getG, PushXRim<HintedStore>{fout + base, gout + base, (int)pl, NX, ix == 1, ix == NX - 2, HintedStore{pol_first, pol_last}},
                                       PH[0], gx, gy, gz, lap, P, rho, ux, uy, uz);
             else
-                collide_streamed<FXY>(F, getG, PushXRim<PlainStore>{fout + base, gout + base, pl, NX, ix == 1, ix == NX - 2, PlainStore{}},
+                collide_streamed<FXY>(F, getG, PushXRim<PlainStore>{fout + base, gout + base, (int)pl, NX, ix == 1, ix == NX - 2, PlainStore{}},
                                       PH[0], gx, gy, gz, lap, P, rho, ux, uy, uz);
             if (WRITE && own) {
                 const long long at = (long long)(zs - 2) * pl + idx;

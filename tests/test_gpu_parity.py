@@ -222,9 +222,10 @@ def test_shanchen_odd_sizes_vs_oracle(nx, ny, variant):
     o.close()
 
 
-@pytest.mark.parametrize("variant", [0, 1, 2, 3, 4])
+@pytest.mark.parametrize("variant", [0, 5, 1, 2, 3, 4])
 def test_binary2d_vs_oracle_and_golden(variant):
-    """variant 0/1: phase pass + collide (128- / 256-thread blocks); 2/3/4: the fused tile kernel (8x32, 4x32 at 96 registers, 4x32)."""
+    """variant 0: the one-pass step (collide + next step's phase field in one launch); 5/1: phase pass + collide (128- /
+    256-thread blocks); 2/3/4: the fused tile kernel (8x32, 4x32 at 96 registers, 4x32)."""
     api = _api()
     cfg = api.binary2d_config()
     cfg.kernel_variant = variant
@@ -253,7 +254,39 @@ def test_binary2d_vs_oracle_and_golden(variant):
             assert nd == 0, (tag, k, nd)
         assert gl.check(tag, "f", ctx.get_populations(0))[0] == 0
         assert gl.check(tag, "g", ctx.get_populations(1))[0] == 0
+    assert ctx.phase_fallbacks == 0
     ctx.close()
+
+
+@pytest.mark.parametrize("nx,ny", [(300, 130), (64, 1000), (1500, 40), (258, 257)])
+def test_binary2d_one_pass_equals_two_pass_on_larger_grids(nx, ny):
+    """Grids with many blocks, tall columns (pushes reach several blocks), the periodic seam in the flush zone, a restart
+    from loaded populations in between: the one-pass step must leave exactly the state of phase pass + collide."""
+    api = _api()
+    ph0 = np.random.default_rng(3).uniform(-1, 1, nx * ny)
+    ctxs = []
+    for variant in (0, 5):
+        cfg = api.binary2d_config(nx, ny)
+        cfg.kernel_variant = variant
+        c = api.Context(cfg)
+        c.set_field("phase", ph0)
+        c.init()
+        ctxs.append(c)
+    a, b = ctxs
+    for s in (1, 2, 9):
+        a.step(s)
+        b.step(s)
+        for k in ("phase", "rho", "ux", "uy"):
+            assert ndiff(a.get_field(k), b.get_field(k)) == 0, (s, k)
+        for q in (0, 1):
+            assert ndiff(a.get_populations(q), b.get_populations(q)) == 0, (s, q)
+    a.set_populations(1, b.get_populations(1))          # invalidates the phase field the one-pass step carries along
+    a.step(3)
+    b.step(3)
+    assert ndiff(a.get_field("phase"), b.get_field("phase")) == 0 and ndiff(a.get_populations(1), b.get_populations(1)) == 0
+    assert a.phase_fallbacks == 0
+    a.close()
+    b.close()
 
 
 @pytest.mark.parametrize("variant", [0, 2, 3, 4])
