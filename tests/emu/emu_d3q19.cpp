@@ -54,6 +54,8 @@ void emu3_collide_node(const double *p, double trt_magic, const double *mrt5, do
     else if (trt_magic > 0.0) collide<true, 1>(F, G, PH[0], gx, gy, gz, lap, P, out4[0], out4[1], out4[2], out4[3]);
     else collide<true, 0>(F, G, PH[0], gx, gy, gz, lap, P, out4[0], out4[1], out4[2], out4[3]);
 }
+void emu3_use_streamed(Emu *e, int on) { e->streamed = on; }
+
 static void put(Emu *e, double *dst, const double *src)
 {
     size_t n = (size_t)e->g.nx * e->g.ny;
