@@ -88,8 +88,8 @@ typedef struct {
                                   model, kept for cross-checks and held to the same parity tests.  D3Q19: 0 one-pass
                                   step, 5 two-pass (phase kernel + collide kernels), 1 two-pass with the plain
                                   whole-plane kernel; Shan-Chen 1 = density pass + collide, 2/3/5 = other tiles of the
-                                  fused kernel; binary D2Q9 0 one-pass step, 5 = phase pass + collide, 1 = the same with 256-thread blocks, 2-4 =
-                                  fused tile kernel; curved
+                                  fused kernel; binary D2Q9 1 = 256-thread blocks, 2-4 = fused tile kernel, 5 = one-pass step (the D3Q19
+                                  scheme; slower here); curved
                                   solid 1/2 = other block shapes.  Results never depend on it. */
     double trt_magic;          /* LBM_BINARY_D3Q19 only, EXTENSION with no counterpart in the reference: 0 (default) keeps
                                   the reference's BGK collision; Lambda > 0 relaxes the antisymmetric half of f with

@@ -173,6 +173,7 @@ __global__ void __launch_bounds__(32 * TS, MINB) k_b2_fused(lbm2::B2Params P, co
     if (WRITE) { rho[i] = d; ux[i] = vx; uy[i] = vy; }
     lbm2::b2_push(P, F, G, f2, g2, ix, iy);
 }
+// kernel_variant 5 (measured, not the default: slower than phase pass + collide on B200, see Binary2D::step).
 // One pass per binary-liquid step, the scheme of the D3Q19 k_step_one (csrc/d3q19_step.cuh) in two dimensions: block b
 // collides the 128 nodes [128 b, 128 b + 128) (memory order: iY fast) and also sums the NEXT step's phase field for
 // a block `lag` blocks behind, from the g* values that the blocks before it pushed into the back buffer -- read back
@@ -576,7 +577,7 @@ public:
     // that a block's producers wrap around the whole domain
     lbm_status setup_one_pass()
     {
-        if (cfg_.kernel_variant != 0) return LBM_OK;
+        if (cfg_.kernel_variant != 5) return LBM_OK;
         const int nblk = (int)((n_ + 127) / 128), reach = 1 + cfg_.ny / 128;
         if (n_ % 2 != 0 || nblk <= 4 * reach + 2 || 2 * reach / 64 + 2 > 16) return LBM_OK;
         int per_sm = 4, sms = 148;
@@ -634,7 +635,9 @@ public:
     lbm_status step(int nsteps) override
     {
         if (one_pass_) return step_one_pass(nsteps);
-        // kernel_variant 5 and 1 (and 0 on grids the one-pass kernel does not take): phase pass + collide (4.11 ms at 8192^2).  The fused
+        // kernel_variant 0 (default) and 1 (and 5 on grids the one-pass kernel does not take): phase pass + collide, the
+        // fastest measured (4.13 ms at 8192^2; the one-pass kernel, variant 5: 4.68 ms -- it moves 303 instead of 376 B per
+        // update, but this collision is short enough that the phase part's extra instructions cost more than its bytes).  The fused
         // tile kernel is kept as variants 2 (8 columns x 32 rows, 5.37 ms), 3 (4 x 32 capped at 96 registers, 4.52 ms)
         // and 4 (4 x 32, 5.08 ms): unlike Shan-Chen's, this collision needs ~125 registers, so the fused form gains
         // no occupancy and pays for the ring and the barrier.
