@@ -637,11 +637,13 @@ public:
         if (one_pass_) return step_one_pass(nsteps);
         // kernel_variant 0 (default) and 1 (and 5 on grids the one-pass kernel does not take): phase pass + collide, the
         // fastest measured (4.13 ms at 8192^2; the one-pass kernel, variant 5: 4.68 ms -- it moves 303 instead of 376 B per
-        // update, but this collision is short enough that the phase part's extra instructions cost more than its bytes).  The fused
+        // update, but this collision is short enough that the phase part's extra instructions cost more than its bytes;
+        // a staged, streamed form of the collide kernel at 5 / 6 / 8 blocks per SM: 4.29 / 4.19 / 4.79 ms -- the register
+        // form already moves its 288 B per update at 5.9 TB/s, occupancy is not what limits it).  The fused
         // tile kernel is kept as variants 2 (8 columns x 32 rows, 5.37 ms), 3 (4 x 32 capped at 96 registers, 4.52 ms)
         // and 4 (4 x 32, 5.08 ms): unlike Shan-Chen's, this collision needs ~125 registers, so the fused form gains
         // no occupancy and pays for the ring and the barrier.
-        if (cfg_.kernel_variant >= 2) {
+        if (cfg_.kernel_variant >= 2 && cfg_.kernel_variant <= 4) {
             for (int t = 0; t < nsteps; t++) {
                 const bool w = t == nsteps - 1;
                 rt_.about_to_launch();

@@ -289,7 +289,7 @@ def test_binary2d_one_pass_equals_two_pass_on_larger_grids(nx, ny):
     b.close()
 
 
-@pytest.mark.parametrize("variant", [0, 2, 3, 4])
+@pytest.mark.parametrize("variant", [0, 5, 2, 3, 4])
 @pytest.mark.parametrize("nx,ny", [(37, 23), (4, 70), (65, 34), (9, 33)])
 def test_binary2d_random_odd_size(nx, ny, variant):
     api = _api()
