@@ -292,6 +292,7 @@ public:
             double lag_windows = 1.5;
             if (const char *e = getenv("LBM_TUNE_LAGK")) lag_windows = atof(e);     // measurement knobs, not part of the ABI
             if (const char *e = getenv("LBM_TUNE_POL")) pol_ = atoi(e);
+            if (const char *e = getenv("LBM_TUNE_SPIN")) spin_limit_ = (unsigned)atoi(e);   // 0 with LAGK 0: every late block gives up (tests)
             nblk_ = (int)(((long long)g_.nx * g_.ny + 127) / 128);
             dshift_ = 1 + g_.nx / 128;
             sb_ = std::max(64, 2 * dshift_);
@@ -493,7 +494,7 @@ public:
         L.zjump_at = 1 << 30; L.zjump_by = 0;
         L.pz = std::max(c1, p1 + lag_) - L.z0;
         L.full = (unsigned)sb_;
-        L.spin_limit = 4000;
+        L.spin_limit = spin_limit_;
         const size_t groups = (size_t)nstrips_ * L.pz;
         if (groups * lbm3::LAG_PAD + 34 > ctrl_words_) return rt_.fail(LBM_ESTATE, "one-pass kernel: group counters too small");
         // [0] give-up flag, [32 + 32 i] counter of group i, [last] number of steps that fell back
@@ -799,6 +800,7 @@ private:
     // one-pass kernel: strip geometry and its control words ([0] give-up flag, [1..] group counters, last: fallback count)
     int nblk_ = 0, dshift_ = 0, sb_ = 0, nstrips_ = 0, lag_ = 0;
     int pol_ = 1;     // L2 residency hints on (15.28 vs 15.63 ms at 512^3)
+    unsigned spin_limit_ = 4000;   // polls of 200 ns before a warp of the one-pass kernel gives up (~1 ms)
     unsigned *ctrl_ = nullptr;
     size_t ctrl_words_ = 0;
     double *stage_ = nullptr;

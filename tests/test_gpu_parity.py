@@ -94,6 +94,30 @@ def test_d3q19_default_paths_equal_the_plain_kernel_on_larger_grids(shape, seed,
     b.close()
 
 
+def test_d3q19_one_pass_fallback_path_gives_the_same_result(monkeypatch):
+    """The give-up path of the one-pass step, forced: with no lag to speak of and no patience (LBM_TUNE_LAGK=0,
+    LBM_TUNE_SPIN=0 -- measurement knobs read at lbm_create) blocks find their producers unfinished, raise the flag,
+    and k_phase_finish recomputes the phase field the two-pass way.  The state must not care."""
+    monkeypatch.setenv("LBM_TUNE_LAGK", "0")
+    monkeypatch.setenv("LBM_TUNE_SPIN", "0")
+    nx, ny, nz = 200, 150, 40
+    flds = _random_fields(nx, ny, nz, 8)
+    a = _ctx3(nx, ny, nz, GENERAL, flds, 0)
+    monkeypatch.delenv("LBM_TUNE_LAGK")
+    monkeypatch.delenv("LBM_TUNE_SPIN")
+    b = _ctx3(nx, ny, nz, GENERAL, flds, 1)
+    for s in (1, 2, 6):
+        a.step(s)
+        b.step(s)
+        for k in F3:
+            assert ndiff(a.get_field(k), b.get_field(k)) == 0, (s, k)
+        for q in (0, 1):
+            assert ndiff(a.get_populations(q), b.get_populations(q)) == 0, (s, q)
+    assert a.phase_fallbacks > 0          # the path under test was taken
+    a.close()
+    b.close()
+
+
 @pytest.mark.parametrize("variant", [0, 5, 1])
 def test_d3q19_quarterchannel_golden(variant):
     """The reference's own QuarterChannel run, all 1001 steps, against values dumped from the unmodified reference."""
