@@ -89,7 +89,8 @@ typedef struct {
                                   step, 5 two-pass (phase kernel + collide kernels), 1 two-pass with the plain
                                   whole-plane kernel; Shan-Chen 1 = density pass + collide, 2/3/5 = other tiles of the
                                   fused kernel; binary D2Q9 1 = 256-thread blocks, 2-4 = fused tile kernel, 5 = one-pass step (the D3Q19
-                                  scheme; slower here); curved
+                                  scheme; slower here); MRT 0 = in-place AA-pattern streaming on ONE population array, 1 = two arrays with push
+                                  streaming; curved
                                   solid 1/2 = other block shapes.  Results never depend on it. */
     double trt_magic;          /* LBM_BINARY_D3Q19 only, EXTENSION with no counterpart in the reference: 0 (default) keeps
                                   the reference's BGK collision; Lambda > 0 relaxes the antisymmetric half of f with

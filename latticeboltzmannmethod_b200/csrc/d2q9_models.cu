@@ -330,6 +330,24 @@ __global__ void __launch_bounds__(kThreads) k_mrt_step(lbm2::MrtParams P, const 
     if (i < (long long)P.nx * P.ny)
         lbm2::mrt_thread_v<VARIANT>(P, f, force, f2, rho, ux, uy, (int)(i / P.ny), (int)(i % P.ny), WRITE);
 }
+// in-place AA-pattern form of the MRT step: ONE population array (the default; kernel_variant 1 = two arrays).
+// Measured at 8192^2: 1.80 / 1.68 ms (GS / Hermite) against 1.82 / 1.85 ms for the two-array push, 4.8 GB less memory.
+template <int VARIANT, bool ODD, bool WRITE>
+__global__ void __launch_bounds__(kThreads) k_mrt_step_aa(lbm2::MrtParams P, double *f, const double *__restrict__ force,
+                                                           double *__restrict__ rho, double *__restrict__ ux, double *__restrict__ uy)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < (long long)P.nx * P.ny)
+        lbm2::mrt_thread_aa<VARIANT, ODD>(P, f, force, rho, ux, uy, (int)(i / P.ny), (int)(i % P.ny), WRITE);
+}
+// the streamed populations in the reference's AoS order out of the AA array, whichever half of the cycle comes next
+__global__ void __launch_bounds__(kThreads) k_mrt_aa_to_aos9(lbm2::MrtParams P, const double *f, int odd_next, double *aos)
+{
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x, n = (long long)P.nx * P.ny;
+    if (t >= n * 9) return;
+    const long long i = t / 9;
+    aos[t] = lbm2::mrt_aa_streamed(P, f, odd_next, (int)(t % 9), (int)(i / P.ny), (int)(i % P.ny));
+}
 // ---- TRT diffusion kernels (node index i = iY*nx+iX) ----
 __global__ void __launch_bounds__(kThreads) k_trt_init(lbm2::TrtParams P, const double *rho, const double *ux, const double *uy,
                                                         double *fa, double *fb)
@@ -701,6 +719,8 @@ public:
     lbm_status setup()
     {
         LBM_TRY(alloc_common());
+        aa_ = cfg_.kernel_variant != 1;      // default: in-place AA streaming; 1: two arrays, push streaming
+        if (aa_) { rt_.dev_free(f_[1]); f_[1] = nullptr; }      // the point of the in-place form: one population array
         std::vector<double> force(cfg_.nx);
         lbm2::mrt_build_tables(&P_, cfg_.model == LBM_MRT_GS_D2Q9 ? 0 : 1, cfg_.nx, cfg_.ny, cfg_.omega, cfg_.omega_bulk,
                                cfg_.force_ampl, force.data());
@@ -711,6 +731,7 @@ public:
     bool has_field(int f) const override { return f == LBM_RHO || f == LBM_UX || f == LBM_UY; }
     lbm_status init() override
     {
+        odd_next_ = false;
         k_mrt_init<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, fields_[LBM_RHO], fields_[LBM_UX], fields_[LBM_UY], f_[cur_]);
         return rt_.launched("k_mrt_init");
     }
@@ -719,6 +740,16 @@ public:
         for (int t = 0; t < nsteps; t++) {
             rt_.about_to_launch();
             const bool w = t == nsteps - 1;
+            if (aa_) {
+                // even and odd half of the AA cycle alternate on the one array
+                auto kern = P_.variant == 0
+                    ? (odd_next_ ? (w ? k_mrt_step_aa<0, true, true> : k_mrt_step_aa<0, true, false>) : (w ? k_mrt_step_aa<0, false, true> : k_mrt_step_aa<0, false, false>))
+                    : (odd_next_ ? (w ? k_mrt_step_aa<1, true, true> : k_mrt_step_aa<1, true, false>) : (w ? k_mrt_step_aa<1, false, true> : k_mrt_step_aa<1, false, false>));
+                kern<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, f_[0], aux_, fields_[LBM_RHO], fields_[LBM_UX], fields_[LBM_UY]);
+                LBM_TRY(rt_.launched("k_mrt_step_aa"));
+                odd_next_ = !odd_next_;
+                continue;
+            }
             auto kern = P_.variant == 0 ? (w ? k_mrt_step<0, true> : k_mrt_step<0, false>) : (w ? k_mrt_step<1, true> : k_mrt_step<1, false>);
             kern<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, f_[cur_], aux_, f_[1 - cur_], fields_[LBM_RHO], fields_[LBM_UX],
                                                               fields_[LBM_UY]);
@@ -727,10 +758,34 @@ public:
         }
         return LBM_OK;
     }
-    lbm_status diagnostics(double *m, double *mom, double *pm, int *nan) override { return diag_common(0, m, mom, pm, nan); }
+    // AA mode: after an even step the array holds post-collision values in the opposite slots; the streamed populations
+    // are gathered out of it (no second array exists to un-swap into)
+    lbm_status get_populations(int set, double *host) override
+    {
+        if (!aa_ || !odd_next_) return Model2D::get_populations(set, host);
+        if (set != 0) return rt_.fail(LBM_EINVAL, "no such population set");
+        double *stage = nullptr;
+        LBM_CUDA(rt_, rt_.dev_alloc(&stage, 9 * n_ * sizeof(double)));
+        k_mrt_aa_to_aos9<<<blocks_for(9 * n_), kThreads, 0, rt_.stream>>>(P_, f_[0], 1, stage);
+        lbm_status st = rt_.launched("k_mrt_aa_to_aos9");
+        if (st == LBM_OK) st = rt_.cuda(cudaMemcpyAsync(host, stage, 9 * n_ * sizeof(double), cudaMemcpyDeviceToHost, rt_.stream), "D2H populations");
+        if (st == LBM_OK) st = rt_.cuda(cudaStreamSynchronize(rt_.stream), "sync");
+        rt_.dev_free(stage);
+        return st;
+    }
+    lbm_status after_set_populations(int) override { odd_next_ = false; return LBM_OK; }   // loaded in natural order
+    lbm_status diagnostics(double *m, double *mom, double *pm, int *nan) override
+    {
+        LBM_TRY(diag_common(0, m, mom, pm, nan));
+        // in the swapped half of the cycle slot k holds direction opp(k): the sums over all (periodic) nodes are those of
+        // the streamed populations with the momentum's sign flipped
+        if (aa_ && odd_next_ && mom) { mom[0] = -mom[0]; mom[1] = -mom[1]; }
+        return LBM_OK;
+    }
 
 private:
     lbm2::MrtParams P_{};
+    bool aa_ = false, odd_next_ = false;   // aa_: in-place AA streaming on f_[0]; odd_next_: the next step is an odd one
 };
 
 // DiffusionCylinder/cylinder.cpp: one launch per step; the geometry mask becomes one 16-bit link word per node

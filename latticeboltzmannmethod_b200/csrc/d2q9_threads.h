@@ -338,19 +338,17 @@ LBM_HD bool mrt_structural_nonzero(int variant, int m, int k)
      {0, 1, 0, -1, 0, 1, -1, -1, 1}, {0, -2, 0, 2, 0, 1, -1, -1, 1}, {0, 0, 1, 0, -1, 1, 1, -1, -1},                          \
      {0, 0, -2, 0, 2, 1, 1, -1, -1}, {0, 1, -1, 1, -1, 0, 0, 0, 0}, {0, 0, 0, 0, 0, 1, -1, 1, -1}}
 
+// the collision of one node in place on its nine (streamed) populations fl; returns rho and the velocity the program
+// writes out (GS: incl. the half-force shift).  mrt.cpp:146-240 / another_mrt.cpp:114-203.
 template <int VARIANT>
-LBM_HD void mrt_thread_v(const MrtParams &P, const double *f, const double *forcex_of_ix, double *f2, double *rho_o,
-                         double *ux_o, double *uy_o, int ix, int iy, bool write_fields)
+LBM_HD void mrt_collide_v(const MrtParams &P, double (&fl)[9], const double *forcex_of_ix, int ix, double &rho, double &ux, double &uy)
 {
-    const int NX = P.nx, NY = P.ny;
-    const long long n = (long long)NX * NY, i = (long long)ix * NY + iy;
     const int CX[9] = LBM2_CX, CY[9] = LBM2_CY;
     const double W[9] = LBM2_W;
-    double fl[9], eq[9], add[9];
-    double rho = 0.0, ux = 0.0, uy = 0.0;
+    double eq[9], add[9];
+    rho = 0.0; ux = 0.0; uy = 0.0;
 #pragma unroll
     for (int k = 0; k < 9; k++) {
-        fl[k] = f[k * n + i];
         rho += fl[k];
         ux += fl[k] * CX[k];
         uy += fl[k] * CY[k];
@@ -429,6 +427,20 @@ LBM_HD void mrt_thread_v(const MrtParams &P, const double *f, const double *forc
             if (mrt_structural_nonzero(VARIANT, m, k)) addit = addit + P.B[k][m] * add[m];
         fl[k] = VARIANT == 0 ? fl[k] + addit : fl[k] + W[k] * addit;
     }
+}
+
+template <int VARIANT>
+LBM_HD void mrt_thread_v(const MrtParams &P, const double *f, const double *forcex_of_ix, double *f2, double *rho_o,
+                         double *ux_o, double *uy_o, int ix, int iy, bool write_fields)
+{
+    const int NX = P.nx, NY = P.ny;
+    const long long n = (long long)NX * NY, i = (long long)ix * NY + iy;
+    const int CX[9] = LBM2_CX, CY[9] = LBM2_CY;
+    double fl[9];
+#pragma unroll
+    for (int k = 0; k < 9; k++) fl[k] = f[k * n + i];
+    double rho, ux, uy;
+    mrt_collide_v<VARIANT>(P, fl, forcex_of_ix, ix, rho, ux, uy);
     if (write_fields) { rho_o[i] = rho; ux_o[i] = ux; uy_o[i] = uy; }
 #pragma unroll
     for (int k = 0; k < 9; k++) {
@@ -436,6 +448,48 @@ LBM_HD void mrt_thread_v(const MrtParams &P, const double *f, const double *forc
         f2[k * n + t] = fl[k];
     }
 }
+
+// The same step with IN-PLACE "AA-pattern" streaming (Bailey et al. 2009) on ONE population array: an even step reads
+// the node's own slots and writes the post-collision value of direction k into the OPPOSITE slot of the same node; an
+// odd step reads direction k from the opposite slot of the upstream neighbour (which is where the even step left
+// what streams into this node) and writes it into slot k of the downstream neighbour (which is where the next even
+// step expects it).  Every step touches, per thread, one set of 9 slots for both its loads and its stores, so no second
+// buffer exists and no thread reads what another writes.  Arithmetic: mrt_collide_v, unchanged.
+template <int VARIANT, bool ODD>
+LBM_HD void mrt_thread_aa(const MrtParams &P, double *f, const double *forcex_of_ix, double *rho_o, double *ux_o, double *uy_o,
+                          int ix, int iy, bool write_fields)
+{
+    const int NX = P.nx, NY = P.ny;
+    const long long n = (long long)NX * NY, i = (long long)ix * NY + iy;
+    const int CX[9] = LBM2_CX, CY[9] = LBM2_CY, OPP[9] = LBM2_OPP;
+    long long up[9], down[9];      // neighbour against / along direction k
+#pragma unroll
+    for (int k = 0; k < 9; k++) {
+        up[k] = (long long)((ix - CX[k] + NX) % NX) * NY + (iy - CY[k] + NY) % NY;
+        down[k] = (long long)((ix + CX[k] + NX) % NX) * NY + (iy + CY[k] + NY) % NY;
+    }
+    double fl[9];
+#pragma unroll
+    for (int k = 0; k < 9; k++) fl[k] = ODD ? f[OPP[k] * n + up[k]] : f[k * n + i];
+    double rho, ux, uy;
+    mrt_collide_v<VARIANT>(P, fl, forcex_of_ix, ix, rho, ux, uy);
+    if (write_fields) { rho_o[i] = rho; ux_o[i] = ux; uy_o[i] = uy; }
+#pragma unroll
+    for (int k = 0; k < 9; k++) {
+        if (ODD) f[k * n + down[k]] = fl[k];
+        else f[OPP[k] * n + i] = fl[k];
+    }
+}
+// natural (streamed) population k of node (ix, iy) from the array in either phase of the AA cycle
+LBM_HD double mrt_aa_streamed(const MrtParams &P, const double *f, int odd_next, int k, int ix, int iy)
+{
+    const int NX = P.nx, NY = P.ny;
+    const long long n = (long long)NX * NY;
+    const int CX[9] = LBM2_CX, CY[9] = LBM2_CY, OPP[9] = LBM2_OPP;
+    if (!odd_next) return f[k * n + (long long)ix * NY + iy];
+    return f[OPP[k] * n + (long long)((ix - CX[k] + NX) % NX) * NY + (iy - CY[k] + NY) % NY];
+}
+
 LBM_HD void mrt_thread(const MrtParams &P, const double *f, const double *forcex_of_ix, double *f2, double *rho_o,
                        double *ux_o, double *uy_o, int ix, int iy, bool write_fields = true)
 {

@@ -11,7 +11,7 @@ struct EmuSc { ScParams P; std::vector<double> f[2], rho, psi, u1, u2; int cur =
 struct EmuB2 { B2Params P; std::vector<double> f[2], g[2], phase, rho, ux, uy; int cur = 0; };
 struct EmuTrt { TrtParams P; std::vector<double> f[2], rho, ux, uy; std::vector<unsigned short> links; int cur = 0; };
 struct EmuBs { BsParams P; std::vector<double> f[2], g[2], phi, rho, ux, uy; std::vector<unsigned short> links; int cur = 0; };
-struct EmuMrt { MrtParams P; std::vector<double> f[2], force, rho, ux, uy; int cur = 0; };
+struct EmuMrt { MrtParams P; std::vector<double> f[2], force, rho, ux, uy; int cur = 0; int aa = 0, odd_next = 0; };
 
 extern "C" {
 // ---- Shan-Chen ----
@@ -109,8 +109,28 @@ void emumrt_init(EmuMrt *e, const double *rho, const double *ux, const double *u
     memcpy(e->rho.data(), rho, n * 8); memcpy(e->ux.data(), ux, n * 8); memcpy(e->uy.data(), uy, n * 8);
     for (size_t i = 0; i < n; i++) mrt_init_thread(e->P, e->rho.data(), e->ux.data(), e->uy.data(), e->f[e->cur].data(), i);
 }
+// in-place AA-pattern mode: everything on f[0], even and odd steps alternating (mrt_thread_aa)
+void emumrt_use_aa(EmuMrt *e, int on) { e->aa = on; e->odd_next = 0; }
+static void aa_step(EmuMrt *e)
+{
+    for (int ix = 0; ix < e->P.nx; ix++) for (int iy = 0; iy < e->P.ny; iy++) {
+        double *f = e->f[0].data();
+        if (e->P.variant == 0) {
+            if (e->odd_next) mrt_thread_aa<0, true>(e->P, f, e->force.data(), e->rho.data(), e->ux.data(), e->uy.data(), ix, iy, true);
+            else mrt_thread_aa<0, false>(e->P, f, e->force.data(), e->rho.data(), e->ux.data(), e->uy.data(), ix, iy, true);
+        } else {
+            if (e->odd_next) mrt_thread_aa<1, true>(e->P, f, e->force.data(), e->rho.data(), e->ux.data(), e->uy.data(), ix, iy, true);
+            else mrt_thread_aa<1, false>(e->P, f, e->force.data(), e->rho.data(), e->ux.data(), e->uy.data(), ix, iy, true);
+        }
+    }
+    e->odd_next = !e->odd_next;
+}
 void emumrt_step(EmuMrt *e, int steps)
 {
+    if (e->aa) {
+        for (int t = 0; t < steps; t++) aa_step(e);
+        return;
+    }
     for (int t = 0; t < steps; t++) {
         int a = e->cur, b = 1 - a;
         for (int ix = 0; ix < e->P.nx; ix++) for (int iy = 0; iy < e->P.ny; iy++)
@@ -122,6 +142,11 @@ void emumrt_get(EmuMrt *e, double *rho, double *ux, double *uy, double *f)
 {
     size_t n = (size_t)e->P.nx * e->P.ny;
     memcpy(rho, e->rho.data(), n * 8); memcpy(ux, e->ux.data(), n * 8); memcpy(uy, e->uy.data(), n * 8);
+    if (e->aa) {
+        for (size_t i = 0; i < n; i++) for (int k = 0; k < 9; k++)
+            f[i * 9 + k] = mrt_aa_streamed(e->P, e->f[0].data(), e->odd_next, k, (int)(i / e->P.ny), (int)(i % e->P.ny));
+        return;
+    }
     for (size_t i = 0; i < n; i++) for (int k = 0; k < 9; k++) f[i * 9 + k] = e->f[e->cur][k * n + i];
 }
 void emumrt_wave(int variant, int nx, int ny, double ampl, double force_ampl, double *rho, double *ux, double *uy)

@@ -339,10 +339,14 @@ def test_binary2d_random_odd_size(nx, ny, variant):
 
 @pytest.mark.parametrize("tag,variant,omega,omega_bulk", [("mrt_gs_10_10", "gs", 1.0, 1.0), ("mrt_gs_12_8", "gs", 1.2, 0.8),
                                                            ("mrt_hermite", "hermite", 0.9, 0.1)])
-def test_mrt_golden(tag, variant, omega, omega_bulk):
+@pytest.mark.parametrize("kernel_variant", [0, 1])
+def test_mrt_golden(tag, variant, omega, omega_bulk, kernel_variant):
+    """kernel_variant 0: in-place AA-pattern streaming on one population array; 1: two arrays, push streaming."""
     api = _api()
     m = gl.meta(tag)
-    ctx = api.Context(api.mrt_config(variant, m["nx"], m["ny"], omega, omega_bulk))
+    cfg = api.mrt_config(variant, m["nx"], m["ny"], omega, omega_bulk)
+    cfg.kernel_variant = kernel_variant
+    ctx = api.Context(cfg)
     rho, ux, uy = api.mrt_initial_fields(variant, m["nx"], m["ny"])
     ctx.set_field("rho", rho)
     ctx.set_field("ux", ux)
@@ -355,26 +359,38 @@ def test_mrt_golden(tag, variant, omega, omega_bulk):
     ctx.close()
 
 
+@pytest.mark.parametrize("kernel_variant", [0, 1])
 @pytest.mark.parametrize("variant", ["gs", "hermite"])
-def test_mrt_y_dependent_vs_oracle(variant):
-    """The reference's 40x3 wave is y-independent; a seeded random state exercises y streaming too."""
+def test_mrt_y_dependent_vs_oracle(variant, kernel_variant):
+    """The reference's 40x3 wave is y-independent; a seeded random state exercises y streaming too.  kernel_variant 0
+    (in-place AA streaming): populations and diagnostics are read back in both halves of the AA cycle (after 1, 65, 68
+    steps), reloaded in between; 1 = two arrays."""
     api = _api()
     nx, ny = 48, 20
     rng = np.random.default_rng(12345)
     f0 = (np.array([4 / 9] + [1 / 9] * 4 + [1 / 36] * 4) * (1 + 1e-3 * rng.uniform(-1, 1, (nx * ny, 9))))
     v = 0 if variant == "gs" else 1
     om, ob = (1.2, 0.8) if v == 0 else (0.9, 0.1)
-    ctx = api.Context(api.mrt_config(variant, nx, ny, om, ob))
+    cfg = api.mrt_config(variant, nx, ny, om, ob)
+    cfg.kernel_variant = kernel_variant
+    ctx = api.Context(cfg)
     ctx.set_populations(0, f0)
     o = ol.OracleMRT(v, nx, ny, om, ob, 0.002 if v == 0 else 0.0)
     o.set_pops(f0)
-    for s in (1, 64):
+    cx = np.array([0, 1, 0, -1, 0, 1, -1, -1, 1.0])
+    for s in (1, 64, 3):
         ctx.step(s)
         o.step(s)
         a = o.fields()
         for k in ("rho", "ux", "uy"):
             assert ndiff(a[k], ctx.get_field(k)) == 0, (k, s)
-        assert ndiff(o.pops(), ctx.get_populations(0)) == 0
+        got = ctx.get_populations(0)
+        assert ndiff(o.pops(), got) == 0
+        d = ctx.diagnostics()
+        assert abs(d["mass"] - got.sum()) <= 1e-12 * got.sum()
+        assert abs(d["momentum"][0] - (got * cx).sum()) <= 1e-12 * got.sum()
+        if s == 64:
+            ctx.set_populations(0, got)          # reload in natural order: the AA cycle restarts with an even step
     ctx.close()
     o.close()
 

@@ -158,10 +158,14 @@ def test_binary2d_threads_match_oracle(emu_libs, nx, ny):
     o.close()
 
 
+@pytest.mark.parametrize("aa", [0, 1])
 @pytest.mark.parametrize("variant,om,ob,fa,shape", [(0, 1.0, 1.0, 0.002, (40, 3)), (0, 1.2, 0.8, 0.002, (33, 7)),
                                                     (1, 0.9, 0.1, 0.0, (40, 3))])
-def test_mrt_threads_match_oracle(emu_libs, variant, om, ob, fa, shape):
+def test_mrt_threads_match_oracle(emu_libs, variant, om, ob, fa, shape, aa):
+    """aa = 1: the in-place AA-pattern form (one population array, even and odd steps alternating); the streamed
+    populations gathered out of it must equal the oracle's after an odd as well as after an even number of steps."""
     L = _emu2(emu_libs["d2q9"])
+    L.emumrt_use_aa.argtypes = [C.c_void_p, C.c_int]
     nx, ny = shape
     n = nx * ny
     o = ol.OracleMRT(variant, nx, ny, om, ob, fa)
@@ -169,8 +173,9 @@ def test_mrt_threads_match_oracle(emu_libs, variant, om, ob, fa, shape):
     rho, ux, uy = np.empty(n), np.empty(n), np.empty(n)
     L.emumrt_wave(variant, nx, ny, 0.001, fa, _p(rho), _p(ux), _p(uy))
     e = L.emumrt_create(variant, nx, ny, om, ob, fa)
+    L.emumrt_use_aa(e, aa)
     L.emumrt_init(e, _p(rho), _p(ux), _p(uy))
-    for s in (0, 1, 50, 200):
+    for s in (0, 1, 50, 200, 3):
         o.step(s)
         L.emumrt_step(e, s)
         out = [np.empty(n) for _ in range(3)] + [np.empty(9 * n)]

@@ -87,8 +87,12 @@ def measure(n=8192, steps=20, alternatives=True, peak=None):
         ctx.close()
     del ph
     f64 = fp64_peak()
-    for variant, om, ob in (("gs", 1.2, 0.8), ("hermite", 0.9, 0.1)):
-        ctx = api.Context(api.mrt_config(variant, n, n, om, ob))
+    for variant, om, ob, kv in (("gs", 1.2, 0.8, 0), ("hermite", 0.9, 0.1, 0), ("gs", 1.2, 0.8, 1)):
+        if kv and not alternatives:
+            continue
+        cfg = api.mrt_config(variant, n, n, om, ob)
+        cfg.kernel_variant = kv
+        ctx = api.Context(cfg)
         x = np.arange(n)
         fa = 0.002 if variant == "gs" else 0.0
         ux = np.repeat(1e-3 * np.cos(x / n * 2 * np.pi) - fa / 2 * np.cos(x / n * 2 * np.pi), n)
@@ -102,7 +106,7 @@ def measure(n=8192, steps=20, alternatives=True, peak=None):
             rate = n * n / ms / 1e6 * MRT_DP_INSTR[variant]          # G double-precision thread-instructions per second
             more = {"dp_instr_per_node": MRT_DP_INSTR[variant], "dp_ginstr_per_s": rate,
                     "fp64_peak_ginstr_per_s": f64["fp64_unfused_ginstr_per_s"], "frac_of_measured_fp64": rate / f64["fp64_unfused_ginstr_per_s"]}
-        add("mrt_%s_d2q9" % variant, ms, n * n, 144, **more)
+        add("mrt_%s_d2q9" % variant + (" (two population arrays, push streaming)" if kv else ""), ms, n * n, 144, **more)
         ctx.close()
     # TRT diffusion: the reference disc scaled to the grid (radius 40/129 of the side); updates = fluid nodes;
     # 9 reads + 9 writes + rho write + ux, uy reads = 168 B per fluid node, + 2 B link word per node of the array
