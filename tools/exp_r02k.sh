@@ -6,7 +6,7 @@ cd "$GRAFT_REPO_ROOT" 2>/dev/null || cd /root/repo
 NG=${1:-2}
 O=gpurun_out/r02k_n$NG; mkdir -p $O
 nvidia-smi -L > $O/gpus.txt
-timeout 600 python -m pytest tests/test_gpu_multi.py tests/test_gpu_hosts.py -x -q -m gpu -k "slab_ring or several_gpus" -v > $O/pytest_multi.log 2>&1; rc=$?; echo "pytest rc=$rc" >> $O/pytest_multi.log
+timeout 150 python -m pytest tests/test_gpu_multi.py tests/test_gpu_hosts.py -x -q -m gpu -k "slab_ring or several_gpus" -v > $O/pytest_multi.log 2>&1; rc=$?; echo "pytest rc=$rc" >> $O/pytest_multi.log
 tail -12 $O/pytest_multi.log
 if [ $rc -ne 0 ]; then echo "multi-GPU tests failed: stopping"; exit 1; fi
 TR="python -m torch.distributed.run --nnodes=1 --master-addr 127.0.0.1"
