@@ -468,185 +468,6 @@ LBM_HD void collide_streamed(double *F, GetG getG, Emit emit, double ph, double 
     }
 }
 
-// ---------------------------------------------------------------------------
-// The collision split by population set, for kernels that give the f and the g
-// populations of a node to two different threads (twice the resident warps for
-// the same register file: each thread holds 19 populations instead of 38).
-// The f thread computes the moments and hands (ux,uy,uz) to the g thread; the g
-// thread computes the phase stencils and hands (phi,gx,gy,gz,lap) to the f
-// thread.  Expressions and summation orders are those of collide<>().
-template <bool FXY>
-LBM_HD void moments_shifted(const double *F, const Params &P, double &rho, double &ux, double &uy, double &uz)
-{
-    moments(F, rho, ux, uy, uz);
-    const double two_rho = 2.0 * rho;
-    if (FXY) {
-        ux += P.fx / two_rho;
-        uy += P.fy / two_rho;
-    }
-    uz += P.fz / two_rho;
-}
-
-// f populations: lattice.hpp:425-426,448-452,461,465-480,486.  emit: template <int K> void operator()(double f_new)
-template <bool FXY, class Emit>
-LBM_HD void collide_f_part(const double *F, Emit emit, double ph, double gx, double gy, double gz, double lap,
-                           double rho, double ux, double uy, double uz, const Params &P)
-{
-    const double ps = ph * ph;
-    const double pb = rho / 3.0 + P.aconst * (-0.5 * ps + 3.0 / 4.0 * ps * ps) - P.kconst * ph * lap;
-    const double q2 = 2.0 / 3.0, q1 = -1.0 / 3.0;
-    const double uxs = ux * ux, uys = uy * uy, uzs = uz * uz;
-    const double a2x = q2 * uxs, a1x = q1 * uxs, a2y = q2 * uys, a1y = q1 * uys, a2z = q2 * uzs, a1z = q1 * uzs;
-    const double gxs = gx * gx, gys = gy * gy, gzs = gz * gz;
-    const double wa = 5.0 / 12.0, wb = -1.0 / 3.0, wc = -1.0 / 24.0, wd = 1.0 / 12.0, we = 1.0 / 4.0;
-    const double K = P.kconst;
-    const double w6 = 1.0 / 6.0, w12 = 1.0 / 12.0;
-    const double h = 1.5 * rho;
-    const double tau = P.tau_gas + (ph + 1.0) / 2.0 * P.dtau;
-    const double omega = 1.0 / tau;
-    const double pref = 1.0 - 0.5 * omega;
-    const double pw6 = pref * w6, pw12 = pref * w12;
-    const double mo = -omega;
-    const double t0 = P.fz * (-uz), mp = 1.0 - uz, mm = -1.0 - uz;
-    double sum = 0.0, sum_force = 0.0;
-#define LBM3_FP(pw, cx, cy, cz, cu)                                                                                   \
-    ((pw) * (P.fx * (((cx) - ux) + 3.0 * (cx) * (cu)) + P.fy * (((cy) - uy) + 3.0 * (cy) * (cu)) +                     \
-             P.fz * (((cz) - uz) + 3.0 * (cz) * (cu))))
-#define LBM3_FPAIR(k, kopp, w, c, Q, KG, fpk, fpo)                                                                   \
-    {                                                                                                                 \
-        const double rc = rho * (c), hq = h * (Q);                                                                    \
-        const double fe_k = (w) * ((pb + rc) + hq) + (KG), fe_o = (w) * ((pb - rc) + hq) + (KG);                      \
-        const double fp_k = (fpk), fp_o = (fpo);                                                                      \
-        sum += fe_k; sum += fe_o;                                                                                     \
-        sum_force += fp_k; sum_force += fp_o;                                                                         \
-        emit.template operator()<k>(F[k] + (mo * (F[k] - fe_k) + fp_k));                                              \
-        emit.template operator()<kopp>(F[kopp] + (mo * (F[kopp] - fe_o) + fp_o));                                     \
-    }
-#define LBM3_FQUAD(kp, km, kmo, kpo, cp, cm, B, cross, Gd, e, fp_p, fp_m, fp_mo, fp_po)                               \
-    {                                                                                                                 \
-        const double Qp = (B) + (cross), Qm = (B) - (cross);                                                          \
-        const double Kp = K * ((Gd) + (e)), Km = K * ((Gd) - (e));                                                    \
-        const double rcp = rho * (cp), rcm = rho * (cm), hqp = h * Qp, hqm = h * Qm;                                  \
-        const double fe_p = w12 * ((pb + rcp) + hqp) + Kp, fe_po = w12 * ((pb - rcp) + hqp) + Kp;                     \
-        const double fe_m = w12 * ((pb + rcm) + hqm) + Km, fe_mo = w12 * ((pb - rcm) + hqm) + Km;                     \
-        const double f_p = (fp_p), f_m = (fp_m), f_mo = (fp_mo), f_po = (fp_po);                                      \
-        sum += fe_p; sum += fe_m; sum += fe_mo; sum += fe_po;                                                         \
-        sum_force += f_p; sum_force += f_m; sum_force += f_mo; sum_force += f_po;                                     \
-        emit.template operator()<kp>(F[kp] + (mo * (F[kp] - fe_p) + f_p));                                            \
-        emit.template operator()<km>(F[km] + (mo * (F[km] - fe_m) + f_m));                                            \
-        emit.template operator()<kmo>(F[kmo] + (mo * (F[kmo] - fe_mo) + f_mo));                                       \
-        emit.template operator()<kpo>(F[kpo] + (mo * (F[kpo] - fe_po) + f_po));                                       \
-    }
-    {
-        const double Qx = (a2x + a1y) + a1z, Qy = (a1x + a2y) + a1z, Qz = (a1x + a1y) + a2z;
-        const double Kx = K * ((wa * gxs + wb * gys) + wb * gzs);
-        const double Ky = K * ((wb * gxs + wa * gys) + wb * gzs);
-        const double Kz = K * ((wb * gxs + wb * gys) + wa * gzs);
-        if (FXY) {
-            LBM3_FPAIR(1, 2, w6, ux, Qx, Kx, LBM3_FP(pw6, 1, 0, 0, ux), LBM3_FP(pw6, -1, 0, 0, -ux))
-            LBM3_FPAIR(3, 4, w6, uy, Qy, Ky, LBM3_FP(pw6, 0, 1, 0, uy), LBM3_FP(pw6, 0, -1, 0, -uy))
-            LBM3_FPAIR(5, 6, w6, uz, Qz, Kz, LBM3_FP(pw6, 0, 0, 1, uz), LBM3_FP(pw6, 0, 0, -1, -uz))
-        } else {
-            const double a6 = pw6 * t0, e5 = 3.0 * uz;
-            LBM3_FPAIR(1, 2, w6, ux, Qx, Kx, a6, a6)
-            LBM3_FPAIR(3, 4, w6, uy, Qy, Ky, a6, a6)
-            LBM3_FPAIR(5, 6, w6, uz, Qz, Kz, pw6 * (P.fz * (mp + e5)), pw6 * (P.fz * (mm + e5)))
-        }
-    }
-    const double a12 = pw12 * t0;
-    {
-        const double c7 = ux + uy, c8 = uy - ux;
-        const double Bxy = (a2x + a2y) + a1z, cxy = 2.0 * (ux * uy);
-        const double Gxy = (wc * gxs + wc * gys) + wd * gzs, exy = we * (gx * gy);
-        if (FXY) {
-            LBM3_FQUAD(7, 8, 9, 10, c7, c8, Bxy, cxy, Gxy, exy, LBM3_FP(pw12, 1, 1, 0, c7), LBM3_FP(pw12, -1, 1, 0, c8),
-                       LBM3_FP(pw12, 1, -1, 0, -c8), LBM3_FP(pw12, -1, -1, 0, -c7))
-        } else {
-            LBM3_FQUAD(7, 8, 9, 10, c7, c8, Bxy, cxy, Gxy, exy, a12, a12, a12, a12)
-        }
-    }
-    {
-        const double c11 = uy + uz, c12 = uz - uy;
-        const double Byz = (a1x + a2y) + a2z, cyz = 2.0 * (uy * uz);
-        const double Gyz = (wd * gxs + wc * gys) + wc * gzs, eyz = we * (gy * gz);
-        if (FXY) {
-            LBM3_FQUAD(11, 12, 13, 14, c11, c12, Byz, cyz, Gyz, eyz, LBM3_FP(pw12, 0, 1, 1, c11), LBM3_FP(pw12, 0, -1, 1, c12),
-                       LBM3_FP(pw12, 0, 1, -1, -c12), LBM3_FP(pw12, 0, -1, -1, -c11))
-        } else {
-            const double e11 = 3.0 * c11, e12 = 3.0 * c12;
-            LBM3_FQUAD(11, 12, 13, 14, c11, c12, Byz, cyz, Gyz, eyz, pw12 * (P.fz * (mp + e11)), pw12 * (P.fz * (mp + e12)),
-                       pw12 * (P.fz * (mm + e12)), pw12 * (P.fz * (mm + e11)))
-        }
-    }
-    {
-        const double c15 = ux + uz, c16 = uz - ux;
-        const double Bxz = (a2x + a1y) + a2z, cxz = 2.0 * (ux * uz);
-        const double Gxz = (wc * gxs + wd * gys) + wc * gzs, exz = we * (gx * gz);
-        if (FXY) {
-            LBM3_FQUAD(15, 16, 17, 18, c15, c16, Bxz, cxz, Gxz, exz, LBM3_FP(pw12, 1, 0, 1, c15), LBM3_FP(pw12, -1, 0, 1, c16),
-                       LBM3_FP(pw12, 1, 0, -1, -c16), LBM3_FP(pw12, -1, 0, -1, -c15))
-        } else {
-            const double e15 = 3.0 * c15, e16 = 3.0 * c16;
-            LBM3_FQUAD(15, 16, 17, 18, c15, c16, Bxz, cxz, Gxz, exz, pw12 * (P.fz * (mp + e15)), pw12 * (P.fz * (mp + e16)),
-                       pw12 * (P.fz * (mm + e16)), pw12 * (P.fz * (mm + e15)))
-        }
-    }
-#undef LBM3_FP
-#undef LBM3_FPAIR
-#undef LBM3_FQUAD
-    {
-        const double fe0 = rho - sum, fp0 = -sum_force;
-        emit.template operator()<0>(F[0] + (mo * (F[0] - fe0) + fp0));
-    }
-}
-
-// g populations: lattice.hpp:427,453-455,462,467,487.  emit: template <int K> void operator()(double g_new)
-template <class Emit>
-LBM_HD void collide_g_part(const double *G, Emit emit, double ph, double lap, double ux, double uy, double uz, const Params &P)
-{
-    const double ps = ph * ph;
-    const double mu = P.gammaconst * (P.aconst * (-ph + ps * ph) - P.kconst * lap);
-    const double q2 = 2.0 / 3.0, q1 = -1.0 / 3.0;
-    const double uxs = ux * ux, uys = uy * uy, uzs = uz * uz;
-    const double a2x = q2 * uxs, a1x = q1 * uxs, a2y = q2 * uys, a1y = q1 * uys, a2z = q2 * uzs, a1z = q1 * uzs;
-    const double w6 = 1.0 / 6.0, w12 = 1.0 / 12.0;
-    const double hp = 1.5 * ph;
-    const double mop = -P.omega_phi;
-    double sum_phase = 0.0;
-#define LBM3_GPAIR(k, kopp, w, c, Q)                                                                                 \
-    {                                                                                                                 \
-        const double pc = ph * (c), hpq = hp * (Q);                                                                   \
-        const double ge_k = (w) * ((mu + pc) + hpq), ge_o = (w) * ((mu - pc) + hpq);                                  \
-        sum_phase += ge_k; sum_phase += ge_o;                                                                         \
-        emit.template operator()<k>(G[k] + mop * (G[k] - ge_k));                                                      \
-        emit.template operator()<kopp>(G[kopp] + mop * (G[kopp] - ge_o));                                             \
-    }
-#define LBM3_GQUAD(kp, km, kmo, kpo, cp, cm, B, cross)                                                               \
-    {                                                                                                                 \
-        const double Qp = (B) + (cross), Qm = (B) - (cross);                                                          \
-        const double pcp = ph * (cp), pcm = ph * (cm), hpqp = hp * Qp, hpqm = hp * Qm;                                \
-        const double ge_p = w12 * ((mu + pcp) + hpqp), ge_po = w12 * ((mu - pcp) + hpqp);                             \
-        const double ge_m = w12 * ((mu + pcm) + hpqm), ge_mo = w12 * ((mu - pcm) + hpqm);                             \
-        sum_phase += ge_p; sum_phase += ge_m; sum_phase += ge_mo; sum_phase += ge_po;                                 \
-        emit.template operator()<kp>(G[kp] + mop * (G[kp] - ge_p));                                                   \
-        emit.template operator()<km>(G[km] + mop * (G[km] - ge_m));                                                   \
-        emit.template operator()<kmo>(G[kmo] + mop * (G[kmo] - ge_mo));                                               \
-        emit.template operator()<kpo>(G[kpo] + mop * (G[kpo] - ge_po));                                               \
-    }
-    LBM3_GPAIR(1, 2, w6, ux, (a2x + a1y) + a1z)
-    LBM3_GPAIR(3, 4, w6, uy, (a1x + a2y) + a1z)
-    LBM3_GPAIR(5, 6, w6, uz, (a1x + a1y) + a2z)
-    LBM3_GQUAD(7, 8, 9, 10, ux + uy, uy - ux, (a2x + a2y) + a1z, 2.0 * (ux * uy))
-    LBM3_GQUAD(11, 12, 13, 14, uy + uz, uz - uy, (a1x + a2y) + a2z, 2.0 * (uy * uz))
-    LBM3_GQUAD(15, 16, 17, 18, ux + uz, uz - ux, (a2x + a1y) + a2z, 2.0 * (ux * uz))
-#undef LBM3_GPAIR
-#undef LBM3_GQUAD
-    {
-        const double ge0 = ph - sum_phase;
-        emit.template operator()<0>(G[0] + mop * (G[0] - ge0));
-    }
-}
-
 // Equilibrium used by Lattice::init (lattice.hpp:259-275).  Not the same
 // expression as in collide(): init squares through (c*c - 1/3)*u*u, whose
 // constants and association differ in the last bit.  Runs once; kept literal.

@@ -317,105 +317,6 @@ LBM_HD void collide_push_thread_streamed(const Geom &g, const Params &P, const p
     collide_push_node_streamed<FXY, WRITE>(g, P, F, [gp, pl](int k) { return gp[(long long)k * pl]; }, PH, fout, gout, o, zs, ix, iy);
 }
 
-// ---- the node update split over an f thread and a g thread ------------------
-// Single-set push functors (same folding of mirror / bounce-back as push_border).
-struct PushOneInterior {
-    const Geom &g;
-    pop_t *po;          // out array + pop_index(zs, 0, idx)
-    template <int K>
-    LBM_HD void operator()(double v) const
-    {
-        constexpr int CX[19] = LBM3_CX, CY[19] = LBM3_CY, CZ[19] = LBM3_CZ;
-        po[(long long)(CZ[K] * 19 + K) * g.pl + (CY[K] * g.nx + CX[K])] = v;
-    }
-};
-LBM_HD void push_border_one(const Geom &g, pop_t *out, int zs, int ix, int iy, int k, double v)
-{
-    const int CX[19] = LBM3_CX, CY[19] = LBM3_CY, CZ[19] = LBM3_CZ;
-    const int OPP[19] = {0, 2, 1, 4, 3, 6, 5, 10, 9, 8, 7, 14, 13, 12, 11, 18, 17, 16, 15};
-    const int SYMX[19] = {0, 2, 1, 3, 4, 5, 6, 8, 7, 10, 9, 11, 12, 13, 14, 16, 15, 18, 17};
-    const int SYMY[19] = {0, 1, 2, 4, 3, 5, 6, 9, 10, 7, 8, 12, 11, 14, 13, 15, 16, 17, 18};
-    int px = ix + CX[k], py = iy + CY[k], pz = zs + CZ[k], kk = k;
-    if (px == g.nx - 1 || py == g.ny - 1) {
-        px = ix; py = iy; pz = zs; kk = OPP[k];
-    } else {
-        if (px == 0) { px = 1; kk = SYMX[kk]; }
-        if (py == 0) { py = 1; kk = SYMY[kk]; }
-    }
-    out[pop_index(g, pz, kk, (long long)py * g.nx + px)] = v;
-}
-struct PushOneBorder {
-    const Geom &g;
-    pop_t *out;
-    int zs, ix, iy;
-    template <int K>
-    LBM_HD void operator()(double v) const { push_border_one(g, out, zs, ix, iy, K, v); }
-};
-
-// f thread of a bulk node, after the exchange: F in registers, phase data received from the g thread
-template <bool FXY, bool WRITE>
-LBM_HD void f_thread_finish(const Geom &g, const Params &P, const double *F, double ph, double gx, double gy, double gz,
-                            double lap, double rho, double ux, double uy, double uz, pop_t *fout, const FieldsOut &o, int zs,
-                            int ix, int iy)
-{
-    const int NX = g.nx, NY = g.ny;
-    const long long idx = (long long)iy * NX + ix;
-    const bool own = zs >= 2 && zs < g.nz + 2;
-    if (WRITE && own) {
-        if (iy == 1) mirror_fields<2>(F, P, o, (long long)(zs - 2) * g.pl + ix);
-        if (ix == 1) mirror_fields<1>(F, P, o, (long long)(zs - 2) * g.pl + (long long)iy * NX);
-        if (ix == 1 && iy == 1) mirror_fields<3>(F, P, o, (long long)(zs - 2) * g.pl);
-        const long long at = (long long)(zs - 2) * g.pl + idx;
-        o.rho[at] = rho; o.ux[at] = ux; o.uy[at] = uy; o.uz[at] = uz;
-    }
-    const bool border = ix == 1 || iy == 1 || ix == NX - 2 || iy == NY - 2;
-    if (!border)
-        collide_f_part<FXY>(F, PushOneInterior{g, fout + pop_index(g, zs, 0, idx)}, ph, gx, gy, gz, lap, rho, ux, uy, uz, P);
-    else
-        collide_f_part<FXY>(F, PushOneBorder{g, fout, zs, ix, iy}, ph, gx, gy, gz, lap, rho, ux, uy, uz, P);
-}
-
-// g thread of a bulk node, after the exchange: G in registers, velocity received from the f thread
-LBM_HD void g_thread_finish(const Geom &g, const Params &P, const double *G, double ph, double lap, double ux, double uy,
-                            double uz, pop_t *gout, int zs, int ix, int iy)
-{
-    const int NX = g.nx, NY = g.ny;
-    const long long idx = (long long)iy * NX + ix;
-    const bool border = ix == 1 || iy == 1 || ix == NX - 2 || iy == NY - 2;
-    if (!border)
-        collide_g_part(G, PushOneInterior{g, gout + pop_index(g, zs, 0, idx)}, ph, lap, ux, uy, uz, P);
-    else
-        collide_g_part(G, PushOneBorder{g, gout, zs, ix, iy}, ph, lap, ux, uy, uz, P);
-}
-
-// both halves on one thread (CPU unit test: pins the split against collide())
-template <bool FXY, bool WRITE>
-LBM_HD void collide_push_thread_split(const Geom &g, const Params &P, const pop_t *fin, const pop_t *gin, const double *phi,
-                                      pop_t *fout, pop_t *gout, const FieldsOut &o, int zs, int ix, int iy)
-{
-    const int NX = g.nx, NY = g.ny;
-    if (ix < 1 || ix > NX - 2 || iy < 1 || iy > NY - 2) {
-        if (WRITE && zs >= 2 && zs < g.nz + 2 && ix < NX && iy < NY && (ix == NX - 1 || iy == NY - 1)) {
-            const long long at = (long long)(zs - 2) * g.pl + (long long)iy * NX + ix;
-            o.rho[at] = P.rho_wall; o.ux[at] = 0.0; o.uy[at] = 0.0; o.uz[at] = 0.0;
-        }
-        return;
-    }
-    const long long idx = (long long)iy * NX + ix;
-    double F[19], G[19], PH[19];
-    const int CX[19] = LBM3_CX, CY[19] = LBM3_CY, CZ[19] = LBM3_CZ;
-    for (int k = 0; k < 19; k++) {
-        F[k] = fin[pop_index(g, zs, k, idx)];
-        G[k] = gin[pop_index(g, zs, k, idx)];
-        PH[k] = phi[(long long)(zs + CZ[k]) * g.pl + idx + CY[k] * NX + CX[k]];
-    }
-    double gx, gy, gz, lap, rho, ux, uy, uz;
-    stencils(PH, gx, gy, gz, lap);                       // g thread
-    moments_shifted<FXY>(F, P, rho, ux, uy, uz);         // f thread
-    f_thread_finish<FXY, WRITE>(g, P, F, PH[0], gx, gy, gz, lap, rho, ux, uy, uz, fout, o, zs, ix, iy);
-    g_thread_finish(g, P, G, PH[0], lap, ux, uy, uz, gout, zs, ix, iy);
-}
-
 // ---- initialisation -------------------------------------------------------
 // updateSymmetric + updateWall on the user's fields, one plane per call site
 // thread-row; reference lattice.hpp:705-760 including the loops that stop one

@@ -16,7 +16,7 @@ struct Emu {
     bool fxy;
     std::vector<double> f[2], gq[2], phi, rho, ux, uy, uz;
     int cur = 0;
-    int streamed = 0;        // 0: collide(), 1: collide_streamed(), 2: f/g split, 3: interior(PART 3)+rim rows
+    int streamed = 0;        // 0: collide(), 1: collide_streamed(), 3: interior(PART 3)+rim rows
 };
 
 extern "C" {
@@ -128,16 +128,6 @@ void emu3_step(Emu *e, int n)
                         } else {
                             if (w) collide_push_thread_rows<false, true>(g, e->P, e->f[a].data(), e->gq[a].data(), e->phi.data(), e->f[b].data(), e->gq[b].data(), o, zs, ix, iy);
                             else collide_push_thread_rows<false, false>(g, e->P, e->f[a].data(), e->gq[a].data(), e->phi.data(), e->f[b].data(), e->gq[b].data(), o, zs, ix, iy);
-                        }
-                        continue;
-                    }
-                    if (e->streamed == 2) {
-                        if (e->fxy) {
-                            if (w) collide_push_thread_split<true, true>(g, e->P, e->f[a].data(), e->gq[a].data(), e->phi.data(), e->f[b].data(), e->gq[b].data(), o, zs, ix, iy);
-                            else collide_push_thread_split<true, false>(g, e->P, e->f[a].data(), e->gq[a].data(), e->phi.data(), e->f[b].data(), e->gq[b].data(), o, zs, ix, iy);
-                        } else {
-                            if (w) collide_push_thread_split<false, true>(g, e->P, e->f[a].data(), e->gq[a].data(), e->phi.data(), e->f[b].data(), e->gq[b].data(), o, zs, ix, iy);
-                            else collide_push_thread_split<false, false>(g, e->P, e->f[a].data(), e->gq[a].data(), e->phi.data(), e->f[b].data(), e->gq[b].data(), o, zs, ix, iy);
                         }
                         continue;
                     }
