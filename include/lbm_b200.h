@@ -143,7 +143,9 @@ lbm_status lbm_set_geometry(lbm_ctx *ctx, const int *mask, size_t n);
 lbm_status lbm_init(lbm_ctx *ctx);
 
 /* Test / restart hooks with no reference counterpart other than the arrays being
- * public: load or read back raw populations. set: 0 = f, 1 = g.  n = nodes*Q. */
+ * public: load or read back raw populations. set: 0 = f, 1 = g.  n = nodes*Q.
+ * With slab_count > 1, lbm_set_populations refreshes the ghost planes through the attached communicator
+ * (LBM_ESTATE without lbm_comm_attach: a caller that moves the halos itself restarts through lbm_set_field + lbm_slab_*). */
 lbm_status lbm_set_populations(lbm_ctx *ctx, int set, const double *host_aos, size_t n);
 lbm_status lbm_get_populations(lbm_ctx *ctx, int set, double *host_aos, size_t n);
 
