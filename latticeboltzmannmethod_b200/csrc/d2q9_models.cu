@@ -339,9 +339,9 @@ template <int VARIANT, bool ODD, bool WRITE>
 __global__ void __launch_bounds__(kThreads) k_mrt_step_aa(lbm2::MrtParams P, double *f, const double *__restrict__ force,
                                                            double *__restrict__ rho, double *__restrict__ ux, double *__restrict__ uy)
 {
-    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < (long long)P.nx * P.ny)
-        lbm2::mrt_thread_aa<VARIANT, ODD>(P, f, force, rho, ux, uy, (int)(i / P.ny), (int)(i % P.ny), WRITE);
+    const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;          // nx*ny < 2^31 (checked at create)
+    if (i < (unsigned)(P.nx * P.ny))
+        lbm2::mrt_thread_aa<VARIANT, ODD>(P, f, force, rho, ux, uy, (int)(i / (unsigned)P.ny), (int)(i % (unsigned)P.ny), WRITE);
 }
 // the streamed populations in the reference's AoS order out of the AA array, whichever half of the cycle comes next
 __global__ void __launch_bounds__(kThreads) k_mrt_aa_to_aos9(lbm2::MrtParams P, const double *f, int odd_next, double *aos)

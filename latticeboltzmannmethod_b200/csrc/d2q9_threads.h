@@ -257,6 +257,7 @@ LBM_HD void b2_push(const B2Params &P, const double (&F)[9], const double (&G)[9
     const int NX = P.nx, NY = P.ny;
     const long long n = (long long)NX * NY, i = (long long)ix * NY + iy;
     const int CX[9] = LBM2_CX, CY[9] = LBM2_CY, OPP[9] = LBM2_OPP;
+    const int xs[3] = {ix == 0 ? NX - 1 : ix - 1, ix, ix == NX - 1 ? 0 : ix + 1};   // periodic in x, by comparison
 #pragma unroll
     for (int k = 0; k < 9; k++) {
         const int ty = iy + CY[k];
@@ -264,7 +265,7 @@ LBM_HD void b2_push(const B2Params &P, const double (&F)[9], const double (&G)[9
             f2[OPP[k] * n + i] = F[k];
             g2[OPP[k] * n + i] = G[k];
         } else {
-            const long long t = (long long)((ix + CX[k] + NX) % NX) * NY + ty;
+            const long long t = (long long)xs[1 + CX[k]] * NY + ty;
             f2[k * n + t] = F[k];
             g2[k * n + t] = G[k];
         }
@@ -280,12 +281,12 @@ LBM_HD void b2_collide_thread(const B2Params &P, const double *f, const double *
     const long long n = (long long)NX * NY, i = (long long)ix * NY + iy;
     const int CX[9] = LBM2_CX, CY[9] = LBM2_CY;
     double F[9], G[9], ph9[9];
+    const int xs[3] = {ix == 0 ? NX - 1 : ix - 1, ix, ix == NX - 1 ? 0 : ix + 1};   // periodic in x; 1 <= iy <= NY-2 needs no wrap
 #pragma unroll
     for (int k = 0; k < 9; k++) {
         F[k] = f[k * n + i];
         G[k] = g[k * n + i];
-        const int x2 = (ix + CX[k] + NX) % NX, y2 = (iy + CY[k] + NY) % NY;
-        ph9[k] = phase[(long long)x2 * NY + y2];
+        ph9[k] = phase[(long long)xs[1 + CX[k]] * NY + (iy + CY[k])];
     }
     double d, ux, uy;
     b2_collide_core(P, F, G, ph9, d, ux, uy);
@@ -442,11 +443,10 @@ LBM_HD void mrt_thread_v(const MrtParams &P, const double *f, const double *forc
     double rho, ux, uy;
     mrt_collide_v<VARIANT>(P, fl, forcex_of_ix, ix, rho, ux, uy);
     if (write_fields) { rho_o[i] = rho; ux_o[i] = ux; uy_o[i] = uy; }
+    const int xs[3] = {ix == 0 ? NX - 1 : ix - 1, ix, ix == NX - 1 ? 0 : ix + 1};
+    const int ys[3] = {iy == 0 ? NY - 1 : iy - 1, iy, iy == NY - 1 ? 0 : iy + 1};
 #pragma unroll
-    for (int k = 0; k < 9; k++) {
-        const long long t = (long long)((ix + CX[k] + NX) % NX) * NY + (iy + CY[k] + NY) % NY;
-        f2[k * n + t] = fl[k];
-    }
+    for (int k = 0; k < 9; k++) f2[k * n + (xs[1 + CX[k]] * NY + ys[1 + CY[k]])] = fl[k];
 }
 
 // The same step with IN-PLACE "AA-pattern" streaming (Bailey et al. 2009) on ONE population array: an even step reads
@@ -462,11 +462,15 @@ LBM_HD void mrt_thread_aa(const MrtParams &P, double *f, const double *forcex_of
     const int NX = P.nx, NY = P.ny;
     const long long n = (long long)NX * NY, i = (long long)ix * NY + iy;
     const int CX[9] = LBM2_CX, CY[9] = LBM2_CY, OPP[9] = LBM2_OPP;
-    long long up[9], down[9];      // neighbour against / along direction k
+    // periodic neighbours by comparison (an integer remainder per direction would cost more than the collision's
+    // address arithmetic); nx*ny < 2^31 is checked at create
+    const int xs[3] = {ix == 0 ? NX - 1 : ix - 1, ix, ix == NX - 1 ? 0 : ix + 1};
+    const int ys[3] = {iy == 0 ? NY - 1 : iy - 1, iy, iy == NY - 1 ? 0 : iy + 1};
+    int up[9], down[9];      // neighbour against / along direction k
 #pragma unroll
     for (int k = 0; k < 9; k++) {
-        up[k] = (long long)((ix - CX[k] + NX) % NX) * NY + (iy - CY[k] + NY) % NY;
-        down[k] = (long long)((ix + CX[k] + NX) % NX) * NY + (iy + CY[k] + NY) % NY;
+        up[k] = xs[1 - CX[k]] * NY + ys[1 - CY[k]];
+        down[k] = xs[1 + CX[k]] * NY + ys[1 + CY[k]];
     }
     double fl[9];
 #pragma unroll
@@ -712,7 +716,7 @@ LBM_HD void bs_collide_thread(const BsParams &P, const double *f, const double *
     const double W[9] = LBM2_W;
     const double WXX[9] = LBM_BS_WXX, WYY[9] = LBM_BS_WYY, WXY[9] = LBM_BS_WXY;
     const double GX[9] = LBM_BS_GX, GY[9] = LBM_BS_GY, LAP[9] = LBM_BS_LAP;
-    const int ix = (int)(i % P.nx), iy = (int)(i / P.nx);
+    const int ix = (int)((unsigned)i % (unsigned)P.nx), iy = (int)((unsigned)i / (unsigned)P.nx);   // nx*ny < 2^31 (checked at create)
     // periodic neighbours: (iX+cx+NX)%NX, (iY+cy+NY)%NY
     const int xs[3] = {ix == 0 ? P.nx - 1 : ix - 1, ix, ix == P.nx - 1 ? 0 : ix + 1};
     const int ys[3] = {iy == 0 ? P.ny - 1 : iy - 1, iy, iy == P.ny - 1 ? 0 : iy + 1};
