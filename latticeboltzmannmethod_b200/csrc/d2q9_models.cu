@@ -109,14 +109,14 @@ __global__ void __launch_bounds__(kThreads) k_b2_init(lbm2::B2Params P, const do
 __global__ void __launch_bounds__(kThreads) k_b2_phase(lbm2::B2Params P, const double *g, double *phase)
 {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < (long long)P.nx * P.ny) lbm2::b2_phase_thread(P, g, phase, (int)(i / P.ny), (int)(i % P.ny));
+    if (i < (long long)P.nx * P.ny) lbm2::b2_phase_thread(P, g, phase, (int)((unsigned)i / (unsigned)P.ny), (int)((unsigned)i % (unsigned)P.ny));
 }
 template <bool WRITE, int NT = kThreads>
 __global__ void __launch_bounds__(NT) k_b2_collide(lbm2::B2Params P, const double *f, const double *g, const double *phase,
                                                           double *f2, double *g2, double *rho, double *ux, double *uy)
 {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < (long long)P.nx * P.ny) lbm2::b2_collide_thread(P, f, g, phase, f2, g2, rho, ux, uy, (int)(i / P.ny), (int)(i % P.ny), WRITE);
+    if (i < (long long)P.nx * P.ny) lbm2::b2_collide_thread(P, f, g, phase, f2, g2, rho, ux, uy, (int)((unsigned)i / (unsigned)P.ny), (int)((unsigned)i % (unsigned)P.ny), WRITE);
 }
 // One launch per binary-liquid step, same scheme as k_sc_fused: a tile of TS columns (iX) x 32 rows (iY, the fast
 // index), the phase field of the tile and of the ring around it summed from g into shared memory (wall rows take
@@ -203,7 +203,7 @@ __global__ void __launch_bounds__(kThreads) k_b2_phase_repair(lbm2::B2Params P, 
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(sticky, 1u);
     const long long n = (long long)P.nx * P.ny;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
-        lbm2::b2_phase_thread(P, g, phase, (int)(i / P.ny), (int)(i % P.ny));
+        lbm2::b2_phase_thread(P, g, phase, (int)((unsigned)i / (unsigned)P.ny), (int)((unsigned)i % (unsigned)P.ny));
 }
 template <bool WRITE>
 __global__ void __launch_bounds__(128, 4) k_b2_one(lbm2::B2Params P, const double *__restrict__ f, const double *__restrict__ g,
@@ -331,7 +331,7 @@ __global__ void __launch_bounds__(kThreads) k_mrt_step(lbm2::MrtParams P, const 
 {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < (long long)P.nx * P.ny)
-        lbm2::mrt_thread_v<VARIANT>(P, f, force, f2, rho, ux, uy, (int)(i / P.ny), (int)(i % P.ny), WRITE);
+        lbm2::mrt_thread_v<VARIANT>(P, f, force, f2, rho, ux, uy, (int)((unsigned)i / (unsigned)P.ny), (int)((unsigned)i % (unsigned)P.ny), WRITE);
 }
 // in-place AA-pattern form of the MRT step: ONE population array (the default; kernel_variant 1 = two arrays).
 // Measured at 8192^2: 1.80 / 1.68 ms (GS / Hermite) against 1.82 / 1.85 ms for the two-array push, 4.8 GB less memory.
