@@ -87,7 +87,10 @@ typedef struct {
     int kernel_variant;        /* 0 = default (fastest measured).  Other values select alternative kernels of the same
                                   model, kept for cross-checks and held to the same parity tests.  D3Q19: 0 one-pass
                                   step, 5 two-pass (phase kernel + collide kernels), 1 two-pass with the plain
-                                  whole-plane kernel; Shan-Chen 1 = density pass + collide, 2/3/5 = other tiles of the
+                                  whole-plane kernel, 2 in-place (AA-pattern) streaming on ONE population array -- half
+                                  the population memory (replaces the second array and exchangeMatrices,
+                                  lattice.hpp:842-855), two launches per step, one slab per context (slab_count 1),
+                                  driven by lbm_step only; Shan-Chen 1 = density pass + collide, 2/3/5 = other tiles of the
                                   fused kernel; binary D2Q9 1 = 256-thread blocks, 2-4 = fused tile kernel, 5 = one-pass step (the D3Q19
                                   scheme; slower here); MRT 0 = in-place AA-pattern streaming on ONE population array, 1 = two arrays with push
                                   streaming; curved
@@ -179,6 +182,8 @@ lbm_status lbm_diagnostics(lbm_ctx *ctx, double *mass, double momentum[3], doubl
 void *lbm_get_stream(lbm_ctx *ctx);                /* cudaStream_t the step runs on */
 lbm_status lbm_set_stream(lbm_ctx *ctx, void *cuda_stream);
 unsigned long long lbm_launch_count(const lbm_ctx *ctx); /* kernels launched by this context so far */
+unsigned long long lbm_device_bytes(const lbm_ctx *ctx); /* device memory the context's model holds right now (the sum of
+                                                      its allocations: populations, fields, scratch) */
 int lbm_population_bytes(const lbm_ctx *ctx);      /* storage size of one population value: 8, or 4 in liblbm_b200_f32.so;
                                                       the element size of the F/G halo messages of lbm_slab_halo */
 /* Debugging aid with no reference counterpart: with LBM_GUARD=1 in the environment at lbm_create, every device buffer

@@ -81,6 +81,7 @@ def load_library(precision="f64"):
         "lbm_set_stream": (ci, [vp, vp]),
         "lbm_launch_count": (C.c_ulonglong, [vp]),
         "lbm_population_bytes": (ci, [vp]),
+        "lbm_device_bytes": (C.c_ulonglong, [vp]),
         "lbm_phase_fallbacks": (C.c_ulonglong, [vp]),
         "lbm_guard_check": (C.c_ulonglong, [vp]),
         "lbm_profile": (ci, [vp, ci]),
@@ -106,7 +107,7 @@ def load_library(precision="f64"):
 
 
 EXPORTS = ["lbm_config_default", "lbm_create", "lbm_destroy", "lbm_last_error", "lbm_slab_extent", "lbm_local_nodes",
-           "lbm_set_field", "lbm_get_field", "lbm_get_field_async", "lbm_population_bytes", "lbm_phase_fallbacks", "lbm_guard_check", "lbm_set_geometry", "lbm_init", "lbm_set_populations", "lbm_get_populations", "lbm_step",
+           "lbm_set_field", "lbm_get_field", "lbm_get_field_async", "lbm_population_bytes", "lbm_device_bytes", "lbm_phase_fallbacks", "lbm_guard_check", "lbm_set_geometry", "lbm_init", "lbm_set_populations", "lbm_get_populations", "lbm_step",
            "lbm_sync", "lbm_diagnostics", "lbm_get_stream", "lbm_set_stream", "lbm_launch_count", "lbm_profile",
            "lbm_profile_report", "lbm_host_alloc",
            "lbm_host_free", "lbm_comm_unique_id", "lbm_comm_attach", "lbm_slab_halo", "lbm_slab_init_fields",
@@ -232,6 +233,11 @@ class Context:
     @property
     def population_bytes(self):
         return int(self.L.lbm_population_bytes(self.h))
+
+    @property
+    def device_bytes(self):
+        """Device memory the context's model holds (populations, fields, scratch)."""
+        return int(self.L.lbm_device_bytes(self.h))
 
     def guard_check(self):
         """Guard bytes overwritten so far (contexts created with LBM_GUARD=1 in the environment; else 0)."""

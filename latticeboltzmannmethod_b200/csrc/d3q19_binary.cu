@@ -137,6 +137,124 @@ __global__ void __launch_bounds__(kThreads) k_phase_finish(Geom g, Params P, con
     }
 }
 
+// ---- in-place (AA-pattern) streaming, kernel_variant 2: one population array, owned planes only, z periodic ----
+// blockIdx.y = owned plane; the per-thread work is d3q19_threads.h's aa_* functions
+__device__ __forceinline__ lbm3::AaPlanes aa_planes(const Geom &g, int zs)
+{
+    const long long pp = 19 * g.pl;
+    const int zm = zs == 2 ? g.nz + 1 : zs - 1, zp = zs == g.nz + 1 ? 2 : zs + 1;
+    return lbm3::AaPlanes{zm * pp, zs * pp, zp * pp};
+}
+template <bool ODD>
+__global__ void __launch_bounds__(kThreads) k_aa_phase(Geom g, Params P, const pop_t *gq, double *phi)
+{
+    const unsigned idx = blockIdx.x * kThreads + threadIdx.x;
+    if (idx >= (unsigned)(g.nx * g.ny)) return;
+    const int zs = 2 + blockIdx.y;
+    lbm3::aa_phase_thread<ODD>(g, P, gq, phi, zs, aa_planes(g, zs), (int)(idx % (unsigned)g.nx), (int)(idx / (unsigned)g.nx));
+}
+template <bool FXY, bool WRITE, int COLL, bool ODD>
+__global__ void __launch_bounds__(128, 3) k_aa_collide(Geom g, Params P, pop_t *f, pop_t *gq, const double *__restrict__ phi,
+                                                        FieldsOut o)
+{
+    const unsigned idx = blockIdx.x * 128 + threadIdx.x;
+    if (idx >= (unsigned)(g.nx * g.ny)) return;
+    const int zs = 2 + blockIdx.y;
+    lbm3::aa_collide_thread<FXY, WRITE, COLL, ODD>(g, P, f, gq, phi, o, zs, aa_planes(g, zs), (int)(idx % (unsigned)g.nx),
+                                                   (int)(idx / (unsigned)g.nx));
+}
+// The BGK step in place with the collision in its streamed form (collide_streamed, as in k_step_one): every thread
+// parks its own 19 g values in its own column of shared memory with asynchronous copies issued before anything else
+// -- they are needed only at the end of the collision -- and every post-collision pair leaves for its place as soon
+// as it exists.  No thread reads another thread's column: no barrier.  A direction group of collide_streamed is
+// closed under reversal and fetches its g values before it emits, and all f values are in registers before the
+// first store, so no place is overwritten before it has been read.
+__device__ __forceinline__ void aa_cp_async(pop_t *smem, const pop_t *gmem)
+{
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    if (sizeof(pop_t) == 8) asm volatile("cp.async.ca.shared.global [%0], [%1], 8;\n" ::"r"(s), "l"(gmem) : "memory");
+    else asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(s), "l"(gmem) : "memory");
+}
+template <bool ODD>
+struct AaEmit {
+    const Geom &g;
+    const lbm3::AaPlanes &z;
+    pop_t *f, *gq;
+    int ix, iy;
+    template <int K>
+    __device__ __forceinline__ void operator()(double fv, double gv) const
+    {
+        const long long t = lbm3::aa_slot<ODD, K>(g, z, ix, iy);
+        f[t] = (pop_t)fv;
+        gq[t] = (pop_t)gv;
+    }
+};
+template <bool FXY, bool WRITE, bool ODD>
+__global__ void __launch_bounds__(128, 4) k_aa_core(Geom g, Params P, pop_t *f, pop_t *gq, const double *__restrict__ phi,
+                                                     FieldsOut o)
+{
+    __shared__ pop_t gs_all[19 * 128];
+    const int NX = g.nx, NY = g.ny;
+    const unsigned idx = blockIdx.x * 128 + threadIdx.x;
+    if (idx >= (unsigned)(NX * NY)) return;
+    const int zs = 2 + blockIdx.y;
+    const int ix = (int)(idx % (unsigned)NX), iy = (int)(idx / (unsigned)NX);
+    if (ix < 1 || ix > NX - 2 || iy < 1 || iy > NY - 2) {
+        if (WRITE && (ix == NX - 1 || iy == NY - 1)) {   // wall node fields, lattice.hpp:75-106
+            const long long at = (long long)(zs - 2) * g.pl + idx;
+            o.rho[at] = P.rho_wall; o.ux[at] = 0.0; o.uy[at] = 0.0; o.uz[at] = 0.0;
+        }
+        return;
+    }
+    const lbm3::AaPlanes z = aa_planes(g, zs);
+    pop_t *gs = gs_all + threadIdx.x;
+    lbm3::aa_each([&](auto m) {
+        constexpr int M = decltype(m)::value;
+        constexpr int OPP[19] = {0, 2, 1, 4, 3, 6, 5, 10, 9, 8, 7, 14, 13, 12, 11, 18, 17, 16, 15};
+        aa_cp_async(gs + OPP[M] * 128, gq + lbm3::aa_slot<ODD, M>(g, z, ix, iy));
+    });
+    asm volatile("cp.async.commit_group;\n" ::: "memory");
+    double F[19], PH[19];
+    lbm3::aa_load<ODD>(g, z, f, ix, iy, F);
+    {
+        constexpr int CX[19] = LBM3_CX, CY[19] = LBM3_CY, CZ[19] = LBM3_CZ;
+        const double *pp = phi + (long long)zs * g.pl + idx;
+        const int pl32 = (int)g.pl;
+#pragma unroll
+        for (int k = 0; k < 19; k++) PH[k] = __ldg(pp + (CZ[k] * pl32 + CY[k] * NX + CX[k]));
+    }
+    double gx, gy, gz, lap;
+    lbm3::stencils(PH, gx, gy, gz, lap);
+    if (WRITE) {
+        if (iy == 1) lbm3::mirror_fields<2>(F, P, o, (long long)(zs - 2) * g.pl + ix);
+        if (ix == 1) lbm3::mirror_fields<1>(F, P, o, (long long)(zs - 2) * g.pl + (long long)iy * NX);
+        if (ix == 1 && iy == 1) lbm3::mirror_fields<3>(F, P, o, (long long)(zs - 2) * g.pl);
+    }
+    asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+    auto getG = [gs](int k) { return (double)gs[k * 128]; };
+    // the stores go to the places the loads came from; with the pitch hidden from the optimiser the 38 store
+    // addresses are formed when they are needed instead of being kept in registers from the loads on (spills)
+    Geom gst = g;
+    {
+        int pitch = (int)g.pl;
+        asm volatile("" : "+r"(pitch));
+        gst.pl = pitch;
+    }
+    double rho, ux, uy, uz;
+    lbm3::collide_streamed<FXY>(F, getG, AaEmit<ODD>{gst, z, f, gq, ix, iy}, PH[0], gx, gy, gz, lap, P, rho, ux, uy, uz);
+    if (WRITE) {
+        const long long at = (long long)(zs - 2) * g.pl + idx;
+        o.rho[at] = rho; o.ux[at] = ux; o.uy[at] = uy; o.uz[at] = uz;
+    }
+}
+__global__ void __launch_bounds__(kThreads) k_aa_swap(Geom g, pop_t *f, pop_t *gq)
+{
+    const unsigned idx = blockIdx.x * kThreads + threadIdx.x;
+    if (idx >= (unsigned)(g.nx * g.ny)) return;
+    const int zs = 2 + blockIdx.y;
+    lbm3::aa_swap_thread(g, f, gq, aa_planes(g, zs), (int)(idx % (unsigned)g.nx), (int)(idx / (unsigned)g.nx));
+}
+
 __global__ void k_init_fields(Geom g, Params P, double *phi, double *rho)
 {
     const int z = blockIdx.x * blockDim.x + threadIdx.x;
@@ -225,6 +343,9 @@ public:
     // kernel_variant: 0 one-pass step (collide + next step's phase field in one launch, d3q19_step.cuh); 5 two-pass
     // (k_phase, then the collide kernels); 1 two-pass with the plain whole-plane collide kernel (the cross-check).
     // The TRT extension exists in the array form of the collision only and always takes the two-pass path.
+    // 2: in-place (AA-pattern) streaming on ONE population array -- half the population memory; two launches per step
+    // (phase field, then collide in place); one slab per context (z periodic inside it), any collision operator.
+    bool aa() const { return cfg_.kernel_variant == 2; }
     int coll() const { return mrt_ ? 2 : (P_.trt_magic > 0.0 ? 1 : 0); }
     bool one_pass() const { return cfg_.kernel_variant == 0 && coll() == 0; }
 
@@ -233,8 +354,10 @@ public:
         if (cfg_.nx < 4 || cfg_.ny < 4) return rt_.fail(LBM_EINVAL, "D3Q19: nx and ny must be at least 4");
         if (cfg_.slab_count < 1 || cfg_.slab_rank < 0 || cfg_.slab_rank >= cfg_.slab_count)
             return rt_.fail(LBM_EINVAL, "bad slab_rank/slab_count");
-        if (cfg_.kernel_variant != 0 && cfg_.kernel_variant != 1 && cfg_.kernel_variant != 5)
-            return rt_.fail(LBM_EINVAL, "D3Q19: kernel_variant must be 0 (one-pass), 5 (two-pass, interior + rim) or 1 (two-pass, plain)");
+        if (cfg_.kernel_variant != 0 && cfg_.kernel_variant != 1 && cfg_.kernel_variant != 5 && cfg_.kernel_variant != 2)
+            return rt_.fail(LBM_EINVAL, "D3Q19: kernel_variant must be 0 (one-pass), 5 (two-pass, interior + rim), 1 (two-pass, plain) or 2 (in place, one array)");
+        if (aa() && cfg_.slab_count != 1)
+            return rt_.fail(LBM_EINVAL, "D3Q19 kernel_variant 2 (in-place streaming) runs on one slab per context: use slab_count 1");
         // solver.hpp:25-30
         const int zstep = cfg_.nz / cfg_.slab_count;
         z_begin_ = cfg_.slab_rank * zstep;
@@ -261,12 +384,15 @@ public:
         fxy_ = P_.fx != 0.0 || P_.fy != 0.0;
 
         const size_t pop_bytes = (size_t)(g_.nz + 4) * 19 * g_.pl * sizeof(pop_t);
-        for (int b = 0; b < 2; b++) {
+        if (aa() && 20 * g_.pl >= (1ll << 31))
+            return rt_.fail(LBM_EINVAL, "D3Q19 in-place streaming: a plane must hold fewer than 107 million nodes");
+        for (int b = 0; b < (aa() ? 1 : 2); b++) {
             LBM_CUDA(rt_, rt_.dev_alloc(&f_[b], pop_bytes));
             LBM_CUDA(rt_, rt_.dev_alloc(&gq_[b], pop_bytes));
             LBM_CUDA(rt_, cudaMemsetAsync(f_[b], 0, pop_bytes, rt_.stream));
             LBM_CUDA(rt_, cudaMemsetAsync(gq_[b], 0, pop_bytes, rt_.stream));
         }
+        if (aa()) { f_[1] = f_[0]; gq_[1] = gq_[0]; }   // one array: "front" and "back" are the same memory
         // two phase-field buffers: the one-pass kernel writes the field of step t+1 while step t reads its own
         const size_t phi_bytes = (size_t)(g_.nz + 4) * g_.pl * sizeof(double);
         for (int b = 0; b < (cfg_.kernel_variant == 0 ? 2 : 1); b++) {
@@ -316,7 +442,10 @@ public:
         }
         for (auto &ge : graph_exec_) if (ge) cudaGraphExecDestroy(ge);
         if (side_) { cudaStreamDestroy(side_); cudaEventDestroy(ev_fork_); cudaEventDestroy(ev_join_); }
-        for (int b = 0; b < 2; b++) { rt_.dev_free(f_[b]); rt_.dev_free(gq_[b]); rt_.dev_free(phib_[b]); }
+        for (int b = 0; b < 2; b++) {
+            if (b == 0 || f_[1] != f_[0]) { rt_.dev_free(f_[b]); rt_.dev_free(gq_[b]); }
+            rt_.dev_free(phib_[b]);
+        }
         rt_.dev_free(rho_); rt_.dev_free(ux_); rt_.dev_free(uy_); rt_.dev_free(uz_); rt_.dev_free(diag_); rt_.dev_free(ctrl_); rt_.dev_free(stage_);
     }
 
@@ -398,6 +527,50 @@ public:
         rt_.about_to_launch();
         k_phase<<<plane_grid(count), kThreads, 0, rt_.stream>>>(g_, P_, gpop, phi, zs0);
         return rt_.launched("k_phase");
+    }
+
+    // ---- in-place streaming (kernel_variant 2) ----
+    dim3 owned_grid(int threads) const { return dim3((unsigned)(((long long)g_.nx * g_.ny + threads - 1) / threads), g_.nz); }
+    // phase field of the owned planes out of either half of the cycle, then its two ghost planes (z periodic)
+    lbm_status aa_phase()
+    {
+        rt_.about_to_launch();
+        if (aa_odd_) k_aa_phase<true><<<owned_grid(kThreads), kThreads, 0, rt_.stream>>>(g_, P_, gq_[0], phib_[0]);
+        else k_aa_phase<false><<<owned_grid(kThreads), kThreads, 0, rt_.stream>>>(g_, P_, gq_[0], phib_[0]);
+        LBM_TRY(rt_.launched("k_aa_phase"));
+        return exchange(true);
+    }
+    lbm_status aa_step(int write_fields)
+    {
+        LBM_TRY(aa_phase());
+        const FieldsOut o = fields_out();
+        const dim3 grid = owned_grid(128);
+        rt_.about_to_launch();
+        with_flavour(write_fields, [&](auto fxy, auto wr, auto c) {
+            constexpr bool FXY = decltype(fxy)::value, WR = decltype(wr)::value;
+            constexpr int COLL = decltype(c)::value;
+            if (COLL == 0) {   // BGK: the streamed form; the TRT and MRT extensions exist in the array form only
+                if (aa_odd_) k_aa_core<FXY, WR, true><<<grid, 128, 0, rt_.stream>>>(g_, P_, f_[0], gq_[0], phib_[0], o);
+                else k_aa_core<FXY, WR, false><<<grid, 128, 0, rt_.stream>>>(g_, P_, f_[0], gq_[0], phib_[0], o);
+            } else {
+                if (aa_odd_) k_aa_collide<FXY, WR, COLL == 0 ? 1 : COLL, true><<<grid, 128, 0, rt_.stream>>>(g_, P_, f_[0], gq_[0], phib_[0], o);
+                else k_aa_collide<FXY, WR, COLL == 0 ? 1 : COLL, false><<<grid, 128, 0, rt_.stream>>>(g_, P_, f_[0], gq_[0], phib_[0], o);
+            }
+        });
+        LBM_TRY(rt_.launched(coll() == 0 ? "k_aa_core" : "k_aa_collide"));
+        aa_odd_ = !aa_odd_;
+        return LBM_OK;
+    }
+    // everything that reads or writes populations from outside a step wants the streamed populations: after an odd
+    // number of steps the pairs of places swap contents once (in place; the next step is then an even one again)
+    lbm_status aa_normalize()
+    {
+        if (!aa_odd_) return LBM_OK;
+        rt_.about_to_launch();
+        k_aa_swap<<<owned_grid(kThreads), kThreads, 0, rt_.stream>>>(g_, f_[0], gq_[0]);
+        LBM_TRY(rt_.launched("k_aa_swap"));
+        aa_odd_ = false;
+        return LBM_OK;
     }
 
     // ---- slab phases ----
@@ -528,6 +701,7 @@ public:
 
     lbm_status slab_collide(int write_fields) override
     {
+        if (aa()) return rt_.fail(LBM_EINVAL, "kernel_variant 2 (in-place streaming) is driven by lbm_step, not by the lbm_slab_* protocol");
         const int nz = g_.nz;
         if (one_pass()) {
             LBM_TRY(ensure_phi());
@@ -553,6 +727,7 @@ public:
     // planes, whose g populations the exchange has just delivered
     lbm_status slab_finish() override
     {
+        if (aa()) return rt_.fail(LBM_EINVAL, "kernel_variant 2 (in-place streaming) is driven by lbm_step, not by the lbm_slab_* protocol");
         cur_ = 1 - cur_;
         if (lag_pending_) {
             lag_pending_ = false;
@@ -668,6 +843,15 @@ public:
     lbm_status init() override
     {
         LBM_TRY(need_comm());
+        if (aa()) {   // one array, no ghost planes of populations
+            LBM_TRY(slab_init_fields());
+            LBM_TRY(exchange(true));
+            LBM_TRY(slab_init_pops());
+            aa_odd_ = false;
+            LBM_TRY(aa_phase());
+            k_after_init<<<plane_grid(g_.nz), kThreads, 0, rt_.stream>>>(g_, P_, f_[0], fields_out());
+            return rt_.launched("k_after_init");
+        }
         LBM_TRY(slab_init_fields());
         LBM_TRY(exchange(true));
         LBM_TRY(slab_init_pops());
@@ -761,6 +945,10 @@ public:
     lbm_status step(int nsteps) override
     {
         LBM_TRY(need_comm());
+        if (aa()) {
+            for (int t = 0; t < nsteps; t++) LBM_TRY(aa_step(t == nsteps - 1));
+            return LBM_OK;
+        }
         const bool overlap = comm_ && cfg_.slab_count > 1 && cfg_.kernel_variant != 1 && g_.nz >= 8;
         int t = 0;
         // small slabs: everything but the first and the last steps in replayed pairs
@@ -790,6 +978,7 @@ public:
     {
         LBM_TRY(need_comm());
         LBM_TRY(ensure_stage());
+        LBM_TRY(aa_normalize());
         const size_t per_plane = (size_t)g_.nx * g_.ny * 19;
         pop_t *dst = set == 0 ? f_[cur_] : gq_[cur_];
         for (int z0 = 0; z0 < g_.nz; z0 += stage_planes_) {
@@ -799,6 +988,7 @@ public:
             LBM_TRY(rt_.launched("k_scatter_aos"));
         }
         LBM_CUDA(rt_, cudaStreamSynchronize(rt_.stream));
+        if (aa()) return LBM_OK;   // no ghost planes of populations
         // refresh the ghost planes of the front buffers: slab_halo() addresses the back buffers, so
         // flip, exchange, flip back
         cur_ = 1 - cur_;
@@ -810,6 +1000,7 @@ public:
     lbm_status get_populations(int set, double *host) override
     {
         LBM_TRY(ensure_stage());
+        LBM_TRY(aa_normalize());
         const size_t per_plane = (size_t)g_.nx * g_.ny * 19;
         for (int z0 = 0; z0 < g_.nz; z0 += stage_planes_) {
             const int n = std::min(stage_planes_, g_.nz - z0);
@@ -823,6 +1014,7 @@ public:
 
     lbm_status diagnostics(double *mass, double *mom, double *phase_mass, int *has_nan) override
     {
+        LBM_TRY(aa_normalize());
         DiagLayout L;
         const size_t pp = 19 * (size_t)g_.pl;
         L.f = f_[cur_] + 2 * pp;
@@ -851,6 +1043,7 @@ private:
     double *phib_[2] = {nullptr, nullptr};
     int pf_ = 0, po_ = 0;
     bool phi_valid_ = false, lag_pending_ = false;
+    bool aa_odd_ = false;   // kernel_variant 2: the array holds post-collision values in the opposite slots (odd half of the cycle)
     cudaGraphExec_t graph_exec_[8] = {};   // one replayable pair of steps per (cur_, pf_, po_)
     unsigned long long graph_launches_[8] = {};
     bool graphs_off_ = false;

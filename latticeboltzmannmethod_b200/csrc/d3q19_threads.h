@@ -19,6 +19,8 @@
 #ifndef LBM_D3Q19_THREADS_H
 #define LBM_D3Q19_THREADS_H
 
+#include <type_traits>
+
 #include "d3q19_node.h"
 #include "lbm_pop.h"
 
@@ -315,6 +317,141 @@ LBM_HD void collide_push_thread_streamed(const Geom &g, const Params &P, const p
     const pop_t *gp = gin + pop_index(g, zs, 0, idx);
     const long long pl = g.pl;
     collide_push_node_streamed<FXY, WRITE>(g, P, F, [gp, pl](int k) { return gp[(long long)k * pl]; }, PH, fout, gout, o, zs, ix, iy);
+}
+
+// ---- in-place (AA-pattern) streaming on ONE population array (kernel_variant 2) --------------
+// Replaces the second population array and exchangeMatrices (lattice.hpp:842-855).
+//
+// The folded push above is a bijection on (bulk node, direction) with one more property: a value pushed back from
+// where it landed, in the direction opposite to the slot it landed in, arrives at the node it came from -- in the
+// opposite slot (plain push, bounce-back and both mirror lines alike).  Hence, with loc(x, m) the place the push of
+// direction m from node x writes:
+//   even step (array holds the streamed populations, slot k of node x = f_k(x)):
+//       F[k] = A[x, k];            collide;   A[x, opp(m)] = F*[m]          -- nothing leaves the node
+//   odd step  (array holds post-collision values in the opposite slot of their own node):
+//       F[opp(m)] = A[loc(x, m)];  collide;   A[loc(x, m)] = F*[m]          -- lands where the two-array push puts it
+// Every thread loads and stores the same 19 places, no two threads share one: no second array, no race.  With
+// slot(x, m) = (x, opp(m)) in an even and loc(x, m) in an odd step both read F[opp(m)] = A[slot(x, m)] and write
+// A[slot(x, m)] = F*[m].  z is periodic inside the one slab this variant runs on: the planes below and above come as
+// explicit offsets, no ghost planes of populations are needed.
+struct AaPlanes {
+    long long zm, z0, zp;   // element offsets of plane z-1, z, z+1 (19 * pitch each) from the start of the array
+};
+
+// offset of the place the folded push of direction K from bulk node (ix, iy) writes (same rules as push_border)
+template <int K>
+LBM_HD long long aa_loc(const Geom &g, const AaPlanes &z, int ix, int iy)
+{
+    constexpr int CX[19] = LBM3_CX, CY[19] = LBM3_CY, CZ[19] = LBM3_CZ;
+    constexpr int OPP[19] = {0, 2, 1, 4, 3, 6, 5, 10, 9, 8, 7, 14, 13, 12, 11, 18, 17, 16, 15};
+    constexpr int SYMX[19] = {0, 2, 1, 3, 4, 5, 6, 8, 7, 10, 9, 11, 12, 13, 14, 16, 15, 18, 17};
+    constexpr int SYMY[19] = {0, 1, 2, 4, 3, 5, 6, 9, 10, 7, 8, 12, 11, 14, 13, 15, 16, 17, 18};
+    constexpr int cx = CX[K], cy = CY[K], cz = CZ[K];
+    constexpr int KX = SYMX[K], KY = SYMY[K], KXY = SYMY[SYMX[K]], KO = OPP[K];
+    const int idx = iy * g.nx + ix;
+    const int pl = (int)g.pl;
+    const bool wall = (cx == 1 && ix == g.nx - 2) || (cy == 1 && iy == g.ny - 2);
+    const bool mx = cx == -1 && ix == 1, my = cy == -1 && iy == 1;
+    const int kk = mx ? (my ? KXY : KX) : (my ? KY : K);
+    const int d = (my ? 0 : cy * g.nx) + (mx ? 0 : cx);
+    const long long zb = cz > 0 ? z.zp : (cz < 0 ? z.zm : z.z0);
+    return wall ? z.z0 + (KO * pl + idx) : zb + (kk * pl + idx + d);
+}
+template <bool ODD, int K>
+LBM_HD long long aa_slot(const Geom &g, const AaPlanes &z, int ix, int iy)
+{
+    constexpr int OPP[19] = {0, 2, 1, 4, 3, 6, 5, 10, 9, 8, 7, 14, 13, 12, 11, 18, 17, 16, 15};
+    if (ODD) return aa_loc<K>(g, z, ix, iy);
+    return z.z0 + (OPP[K] * (int)g.pl + iy * g.nx + ix);
+}
+// fn(integral_constant<int, K>) for K = 0 .. 18, unrolled at compile time
+template <int K = 0, class Fn>
+LBM_HD void aa_each(Fn &&fn)
+{
+    fn(std::integral_constant<int, K>{});
+    if constexpr (K < 18) aa_each<K + 1>(fn);
+}
+// the streamed populations of bulk node (ix, iy) in direction order, out of either half of the cycle
+template <bool ODD>
+LBM_HD void aa_load(const Geom &g, const AaPlanes &z, const pop_t *a, int ix, int iy, double *V)
+{
+    constexpr int OPP[19] = {0, 2, 1, 4, 3, 6, 5, 10, 9, 8, 7, 14, 13, 12, 11, 18, 17, 16, 15};
+    aa_each([&](auto m) {
+        constexpr int M = decltype(m)::value;
+        V[OPP[M]] = a[aa_slot<ODD, M>(g, z, ix, iy)];
+    });
+}
+
+// phase field of one bulk node (+ the mirror / wall nodes it is the inner neighbour of) from the g array in either half
+template <bool ODD>
+LBM_HD void aa_phase_thread(const Geom &g, const Params &P, const pop_t *gq, double *phi, int zs, const AaPlanes &z, int ix, int iy)
+{
+    if (ix < 1 || ix > g.nx - 2 || iy < 1 || iy > g.ny - 2) return;
+    double G[19];
+    aa_load<ODD>(g, z, gq, ix, iy, G);
+    phase_node(g, P, G, phi, zs, ix, iy);
+}
+
+// one node of one step, in place (same reference lines as collide_push_thread)
+template <bool FXY, bool WRITE, int COLL, bool ODD>
+LBM_HD void aa_collide_thread(const Geom &g, const Params &P, pop_t *f, pop_t *gq, const double *phi, const FieldsOut &o,
+                              int zs, const AaPlanes &z, int ix, int iy)
+{
+    const int NX = g.nx, NY = g.ny;
+    if (ix < 1 || ix > NX - 2 || iy < 1 || iy > NY - 2) {
+        if (WRITE && ix < NX && iy < NY && (ix == NX - 1 || iy == NY - 1)) {   // wall node fields, lattice.hpp:75-106
+            const long long at = (long long)(zs - 2) * g.pl + (long long)iy * NX + ix;
+            o.rho[at] = P.rho_wall; o.ux[at] = 0.0; o.uy[at] = 0.0; o.uz[at] = 0.0;
+        }
+        return;
+    }
+    const long long idx = (long long)iy * NX + ix;
+    double F[19], G[19], PH[19];
+    aa_load<ODD>(g, z, f, ix, iy, F);
+    aa_load<ODD>(g, z, gq, ix, iy, G);
+    {
+        constexpr int CX[19] = LBM3_CX, CY[19] = LBM3_CY, CZ[19] = LBM3_CZ;
+#pragma unroll
+        for (int k = 0; k < 19; k++) PH[k] = phi[(long long)(zs + CZ[k]) * g.pl + idx + CY[k] * NX + CX[k]];
+    }
+    double gx, gy, gz, lap;
+    stencils(PH, gx, gy, gz, lap);
+    if (WRITE) {
+        if (iy == 1) mirror_fields<2>(F, P, o, (long long)(zs - 2) * g.pl + ix);
+        if (ix == 1) mirror_fields<1>(F, P, o, (long long)(zs - 2) * g.pl + (long long)iy * NX);
+        if (ix == 1 && iy == 1) mirror_fields<3>(F, P, o, (long long)(zs - 2) * g.pl);
+    }
+    double rho, ux, uy, uz;
+    collide<FXY, COLL>(F, G, PH[0], gx, gy, gz, lap, P, rho, ux, uy, uz);
+    if (WRITE) {
+        const long long at = (long long)(zs - 2) * g.pl + idx;
+        o.rho[at] = rho; o.ux[at] = ux; o.uy[at] = uy; o.uz[at] = uz;
+    }
+    aa_each([&](auto m) {
+        constexpr int M = decltype(m)::value;
+        const long long t = aa_slot<ODD, M>(g, z, ix, iy);
+        f[t] = (pop_t)F[M];
+        gq[t] = (pop_t)G[M];
+    });
+}
+
+// Turns an array of the odd half (post-collision values in the opposite slots) into the streamed populations and
+// back, in place: the streamed value of (x, k) sits at loc(x, opp(k)), and loc(., opp(.)) is an involution on the
+// places, so the two places of every pair swap contents.  The thread of the lower address does the swap.
+LBM_HD void aa_swap_thread(const Geom &g, pop_t *f, pop_t *gq, const AaPlanes &z, int ix, int iy)
+{
+    if (ix < 1 || ix > g.nx - 2 || iy < 1 || iy > g.ny - 2) return;
+    aa_each([&](auto m) {
+        constexpr int M = decltype(m)::value;
+        const long long own = aa_slot<false, M>(g, z, ix, iy);   // (x, opp(M))
+        const long long other = aa_slot<true, M>(g, z, ix, iy);  // loc(x, M): holds the streamed value of (x, opp(M))
+        if (own < other) {
+            const pop_t a = f[own], b = f[other];
+            f[own] = b; f[other] = a;
+            const pop_t c = gq[own], d = gq[other];
+            gq[own] = d; gq[other] = c;
+        }
+    });
 }
 
 // ---- initialisation -------------------------------------------------------

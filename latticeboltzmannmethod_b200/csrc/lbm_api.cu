@@ -235,6 +235,13 @@ lbm_status lbm_set_stream(lbm_ctx *ctx, void *stream)
 }
 
 unsigned long long lbm_launch_count(const lbm_ctx *ctx) { return ctx ? ctx->rt.launches : 0; }
+unsigned long long lbm_device_bytes(const lbm_ctx *ctx)
+{
+    unsigned long long n = 0;
+    if (ctx)
+        for (const auto &kv : ctx->rt.allocs) n += kv.second.bytes;
+    return n;
+}
 int lbm_population_bytes(const lbm_ctx *ctx) { return ctx && ctx->model ? ctx->model->pop_bytes() : 0; }
 unsigned long long lbm_guard_check(lbm_ctx *ctx)
 {

@@ -16,7 +16,8 @@ struct Emu {
     bool fxy;
     std::vector<double> f[2], gq[2], phi, rho, ux, uy, uz;
     int cur = 0;
-    int streamed = 0;        // 0: collide(), 1: collide_streamed(), 3: interior(PART 3)+rim rows
+    int streamed = 0;        // 0: collide(), 1: collide_streamed(), 3: interior(PART 3)+rim rows, 4: in-place (AA) on f[cur] alone
+    bool odd = false;        // mode 4: the array holds post-collision values in the opposite slots
 };
 
 extern "C" {
@@ -108,10 +109,59 @@ void emu3_init(Emu *e)
         for (int iy = 0; iy < g.ny; iy++)
             for (int ix = 0; ix < g.nx; ix++) after_init_thread(g, e->P, e->f[e->cur].data(), o, z, ix, iy);
 }
+}  // extern "C"
+static AaPlanes aa_planes(const Geom &g, int zs)
+{
+    const long long pp = 19 * g.pl;
+    const int zm = zs == 2 ? g.nz + 1 : zs - 1, zp = zs == g.nz + 1 ? 2 : zs + 1;
+    return AaPlanes{zm * pp, zs * pp, zp * pp};
+}
+template <bool ODD>
+static void aa_step(Emu *e, bool w)
+{
+    const Geom &g = e->g;
+    FieldsOut o{e->rho.data(), e->ux.data(), e->uy.data(), e->uz.data()};
+    double *f = e->f[e->cur].data(), *gq = e->gq[e->cur].data(), *phi = e->phi.data();
+    for (int zs = 2; zs < g.nz + 2; zs++)
+        for (int iy = 0; iy < g.ny; iy++)
+            for (int ix = 0; ix < g.nx; ix++) aa_phase_thread<ODD>(g, e->P, gq, phi, zs, aa_planes(g, zs), ix, iy);
+    memcpy(phi + 1 * g.pl, phi + (size_t)(g.nz + 1) * g.pl, g.pl * sizeof(double));
+    memcpy(phi + (size_t)(g.nz + 2) * g.pl, phi + 2 * g.pl, g.pl * sizeof(double));
+    for (int zs = 2; zs < g.nz + 2; zs++)
+        for (int iy = 0; iy < g.ny; iy++)
+            for (int ix = 0; ix < g.nx; ix++) {
+                const AaPlanes z = aa_planes(g, zs);
+                if (e->fxy) {
+                    if (w) aa_collide_thread<true, true, 0, ODD>(g, e->P, f, gq, phi, o, zs, z, ix, iy);
+                    else aa_collide_thread<true, false, 0, ODD>(g, e->P, f, gq, phi, o, zs, z, ix, iy);
+                } else {
+                    if (w) aa_collide_thread<false, true, 0, ODD>(g, e->P, f, gq, phi, o, zs, z, ix, iy);
+                    else aa_collide_thread<false, false, 0, ODD>(g, e->P, f, gq, phi, o, zs, z, ix, iy);
+                }
+            }
+}
+static void aa_normalize(Emu *e)
+{
+    if (!e->odd) return;
+    const Geom &g = e->g;
+    for (int zs = 2; zs < g.nz + 2; zs++)
+        for (int iy = 0; iy < g.ny; iy++)
+            for (int ix = 0; ix < g.nx; ix++) aa_swap_thread(g, e->f[e->cur].data(), e->gq[e->cur].data(), aa_planes(g, zs), ix, iy);
+    e->odd = false;
+}
+extern "C" {
 void emu3_step(Emu *e, int n)
 {
     const Geom &g = e->g;
     FieldsOut o{e->rho.data(), e->ux.data(), e->uy.data(), e->uz.data()};
+    if (e->streamed == 4) {
+        for (int t = 0; t < n; t++) {
+            if (e->odd) aa_step<true>(e, t == n - 1);
+            else aa_step<false>(e, t == n - 1);
+            e->odd = !e->odd;
+        }
+        return;
+    }
     for (int t = 0; t < n; t++) {
         const int a = e->cur, b = 1 - a;
         const bool w = t == n - 1;
@@ -155,6 +205,7 @@ void emu3_step(Emu *e, int n)
 }
 void emu3_get_pops(Emu *e, double *f, double *g)
 {
+    aa_normalize(e);
     for (int z = 0; z < e->g.nz; z++)
         for (int iy = 0; iy < e->g.ny; iy++)
             for (int ix = 0; ix < e->g.nx; ix++) {

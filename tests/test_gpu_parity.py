@@ -51,7 +51,7 @@ def _random_fields(nx, ny, nz, seed=5):
             0.01 * rng.standard_normal(n), 0.01 * rng.standard_normal(n), 0.01 * rng.standard_normal(n)]
 
 
-@pytest.mark.parametrize("variant", [0, 5, 1])
+@pytest.mark.parametrize("variant", [0, 5, 1, 2])
 @pytest.mark.parametrize("shape,params,rand", [((27, 27, 52), ol.PARAMS_QUARTER, False), ((9, 7, 5), ol.PARAMS_QUARTER, True),
                                                ((12, 10, 6), GENERAL, True), ((4, 4, 2), GENERAL, True),
                                                ((92, 52, 12), ol.PARAMS_FULL, False), ((35, 18, 9), GENERAL, True)])
@@ -71,11 +71,12 @@ def test_d3q19_vs_oracle(shape, params, rand, variant):
     o.close()
 
 
-@pytest.mark.parametrize("variant", [0, 5])
+@pytest.mark.parametrize("variant", [0, 5, 2])
 @pytest.mark.parametrize("shape,seed", [((200, 150, 40), 3), ((131, 77, 19), 4), ((640, 33, 12), 5)])
 def test_d3q19_default_paths_equal_the_plain_kernel_on_larger_grids(shape, seed, variant):
     """Grids large enough for several strips, many plane-steps and a lag shorter than the slab: the one-pass step
-    (kernel_variant 0) and the two-pass step with the staged collide kernel (5) must leave exactly the state of the
+    (kernel_variant 0), the two-pass step with the staged collide kernel (5) and the in-place step on one population
+    array (2) must leave exactly the state of the
     plain whole-plane kernel (1: array form of the collision, no staging, no strips -- itself equal to the oracle on
     the small grids above), and the one-pass step must never have had to fall back to the separate phase kernel."""
     nx, ny, nz = shape
@@ -118,7 +119,56 @@ def test_d3q19_one_pass_fallback_path_gives_the_same_result(monkeypatch):
     b.close()
 
 
-@pytest.mark.parametrize("variant", [0, 5, 1])
+def test_d3q19_in_place_streaming_halves_the_population_memory_and_survives_outside_access():
+    """kernel_variant 2 (AA-pattern streaming on one array): the populations take half the device memory of the
+    two-array forms; reading populations, diagnostics and restoring populations in EITHER half of the cycle (after an
+    odd or an even number of steps) neither disturbs the run nor sees anything but the streamed populations."""
+    nx, ny, nz = 64, 48, 24
+    flds = _random_fields(nx, ny, nz, 11)
+    a = _ctx3(nx, ny, nz, GENERAL, flds, 2)
+    b = _ctx3(nx, ny, nz, GENERAL, flds, 1)
+    pops = 2 * 19 * 8 * (nz + 4) * ((nx * ny + 15) // 16 * 16)       # f and g, one array each, incl. the unused ghost planes
+    assert b.device_bytes - a.device_bytes == pops
+    assert a.device_bytes < 0.6 * b.device_bytes
+    saved = None
+    for s in (1, 1, 3, 2, 1):                                       # cumulative 1, 2, 5, 7, 8: both halves of the cycle
+        a.step(s)
+        b.step(s)
+        da, db = a.diagnostics(), b.diagnostics()
+        for k in ("mass", "phase_mass"):
+            assert da[k] == db[k], (s, k)
+        assert np.array_equal(da["momentum"], db["momentum"]) and not da["has_nan"]
+        for q in (0, 1):
+            assert ndiff(a.get_populations(q), b.get_populations(q)) == 0, (s, q)
+        for k in F3:
+            assert ndiff(a.get_field(k), b.get_field(k)) == 0, (s, k)
+        if saved is None:
+            saved = [a.get_populations(0).copy(), a.get_populations(1).copy()]   # the state after step 1 (odd half)
+    # restart from the saved populations while the array is in the odd half again
+    a.step(1)
+    b.step(1)
+    a.set_populations(0, saved[0]); a.set_populations(1, saved[1])
+    b.set_populations(0, saved[0]); b.set_populations(1, saved[1])
+    for s in (1, 4):
+        a.step(s)
+        b.step(s)
+        for q in (0, 1):
+            assert ndiff(a.get_populations(q), b.get_populations(q)) == 0, ("restart", s, q)
+    a.close()
+    b.close()
+
+
+def test_d3q19_in_place_streaming_refuses_more_than_one_slab():
+    api = _api()
+    cfg = api.microchannel_config("quarter", 12, 10, 8)
+    cfg.kernel_variant = 2
+    cfg.slab_count, cfg.slab_rank = 2, 0
+    with pytest.raises(Exception) as e:
+        api.Context(cfg)
+    assert "slab" in str(e.value)
+
+
+@pytest.mark.parametrize("variant", [0, 5, 1, 2])
 def test_d3q19_quarterchannel_golden(variant):
     """The reference's own QuarterChannel run, all 1001 steps, against values dumped from the unmodified reference."""
     m = gl.meta("quarter_t1000")

@@ -44,7 +44,7 @@ GENERAL = [0.04, 0.04, 1.0, 0.05, 0.0, 0.5, 1.0, 2.5, 0.7, 1e-5, -2e-5, 3e-5]
     ((12, 10, 6), GENERAL, 3, (1, 3, 10), True),
     ((4, 4, 2), GENERAL, 1, (1, 3), True),
 ])
-@pytest.mark.parametrize("streamed", [0, 1, 3])
+@pytest.mark.parametrize("streamed", [0, 1, 3, 4])
 def test_d3q19_threads_match_oracle(emu_libs, shape, params, width, steps, rand, streamed):
     nx, ny, nz = shape
     n = nx * ny * nz
@@ -56,7 +56,7 @@ def test_d3q19_threads_match_oracle(emu_libs, shape, params, width, steps, rand,
     p = np.asarray(params, dtype=np.float64)
     e = L.emu3_create(nx, ny, nz, _p(p))
     L.emu3_set_fields(e, *[_p(a) for a in flds])
-    L.emu3_use_streamed(e, streamed)   # 0 collide(), 1 collide_streamed(), 3 interior (PART 3) + rim rows
+    L.emu3_use_streamed(e, streamed)   # 0 collide(), 1 collide_streamed(), 3 interior (PART 3) + rim rows, 4 in-place (AA) on one array
     L.emu3_init(e)
 
     def compare(tag):

@@ -103,7 +103,7 @@ def test_mrt_collision_adds_exactly_the_force_to_the_momentum(emu_libs, rates, t
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("variant", [0, 5])
+@pytest.mark.parametrize("variant", [0, 5, 2])
 @pytest.mark.parametrize("shape,params,rates", [((12, 10, 8), CONST_TAU, DHUMIERES), ((27, 27, 20), TWO_TAU, DHUMIERES),
                                                 ((9, 7, 5), TWO_TAU, [-1.0, 1.7, -1.0, 0.3, 1.9])])
 def test_gpu_mrt_equals_oracle_restatement(shape, params, rates, variant):

@@ -87,7 +87,8 @@ def test_trt_collision_adds_exactly_the_force_to_the_momentum(emu_libs, magic, t
 @pytest.mark.gpu
 @pytest.mark.parametrize("shape,params,magic", [((12, 10, 8), CONST_TAU, 0.64), ((27, 27, 20), TWO_TAU, 3.0 / 16.0),
                                                 ((9, 7, 5), TWO_TAU, 0.25)])
-def test_gpu_trt_equals_oracle_restatement(shape, params, magic):
+@pytest.mark.parametrize("variant", [0, 2])
+def test_gpu_trt_equals_oracle_restatement(shape, params, magic, variant):
     from latticeboltzmannmethod_b200 import api
     nx, ny, nz = shape
     flds = _fields(nx, ny, nz)
@@ -95,6 +96,7 @@ def test_gpu_trt_equals_oracle_restatement(shape, params, magic):
     (cfg.aconst, cfg.kconst, cfg.gammaconst, cfg.wall_gradient, _pw, cfg.rho_wall, cfg.tau_phi, cfg.tau_liq, cfg.tau_gas) = params[:9]
     cfg.force[0], cfg.force[1], cfg.force[2] = params[9:12]
     cfg.trt_magic = magic
+    cfg.kernel_variant = variant        # 0: two-pass with the register kernel, 2: in place on one population array
     ctx = api.Context(cfg)
     for name, a in zip(F3, flds):
         ctx.set_field(name, a)
