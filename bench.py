@@ -33,7 +33,7 @@ def parse():
     ap.add_argument("--nx", type=int, default=512)
     ap.add_argument("--ny", type=int, default=512)
     ap.add_argument("--nz-per-gpu", type=int, default=512)
-    ap.add_argument("--variant", type=int, default=0, help="kernel_variant (0 default: one-pass step; 5 two-pass with interior + rim kernels; 1 two-pass, plain kernel)")
+    ap.add_argument("--variant", type=int, default=0, help="kernel_variant (0 default: one-pass step; 5 two-pass with interior + rim kernels; 1 two-pass, plain kernel; 2 / 6 in-place streaming on one population array, one pass / two passes)")
     ap.add_argument("--e2e-steps", type=int, default=100, help="lattice steps per end-to-end segment (QuarterChannel NUMOUTPUT)")
     ap.add_argument("--precision", default="f64", choices=["f64", "f32"], help="f32: liblbm_b200_f32.so, populations stored as float (not the parity build; the headline is f64)")
     ap.add_argument("--no-e2e", action="store_true")
@@ -542,7 +542,8 @@ def ours(args, rank, world, local_rank):
                            "kernel_variant": args.variant, "l2": "inputs (%.1f GB of populations per GPU) exceed the 126 MB L2" % (nloc * b_alg / 2 / 1e9),
                            "parallelism": "z-slab x%d" % world},
                 "mlups_per_gpu": value / world, "roofline": roof, "cpu_baseline": cb, "e2e": e2e, "clocks": clk,
-                "gpu_launches": launches, "phase_fallbacks": fallbacks}
+                "gpu_launches": launches, "phase_fallbacks": fallbacks,
+                "device_bytes_per_gpu": ctx.device_bytes}
         if parity is not None:
             line["parity"] = parity
         if secondary is not None:

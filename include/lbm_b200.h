@@ -87,10 +87,11 @@ typedef struct {
     int kernel_variant;        /* 0 = default (fastest measured).  Other values select alternative kernels of the same
                                   model, kept for cross-checks and held to the same parity tests.  D3Q19: 0 one-pass
                                   step, 5 two-pass (phase kernel + collide kernels), 1 two-pass with the plain
-                                  whole-plane kernel, 2 in-place (AA-pattern) streaming on ONE population array -- half
-                                  the population memory (replaces the second array and exchangeMatrices,
-                                  lattice.hpp:842-855), two launches per step, one slab per context (slab_count 1),
-                                  driven by lbm_step only; Shan-Chen 1 = density pass + collide, 2/3/5 = other tiles of the
+                                  whole-plane kernel, 2 and 6 in-place (AA-pattern) streaming on ONE population array --
+                                  half the population memory (replaces the second array and exchangeMatrices,
+                                  lattice.hpp:842-855), one slab per context (slab_count 1), driven by lbm_step only;
+                                  2 one pass (the phase field runs ahead of the collision inside one launch), 6 two
+                                  passes; Shan-Chen 1 = density pass + collide, 2/3/5 = other tiles of the
                                   fused kernel; binary D2Q9 1 = 256-thread blocks, 2-4 = fused tile kernel, 5 = one-pass step (the D3Q19
                                   scheme; slower here); MRT 0 = in-place AA-pattern streaming on ONE population array, 1 = two arrays with push
                                   streaming; curved

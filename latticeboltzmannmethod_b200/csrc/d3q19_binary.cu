@@ -10,6 +10,7 @@
 
 #include <mutex>
 
+#include "d3q19_inplace.cuh"
 #include "d3q19_step.cuh"
 #include "d3q19_threads.h"
 #include "lbm_internal.h"
@@ -18,6 +19,12 @@ namespace lbm {
 namespace {
 
 using lbm3::FieldsOut;
+using lbm3::k_aa_collide;
+using lbm3::k_aa_core;
+using lbm3::k_aa_one;
+using lbm3::k_aa_phase;
+using lbm3::k_aa_repair;
+using lbm3::k_aa_swap;
 using lbm3::Geom;
 using lbm3::Params;
 
@@ -137,124 +144,6 @@ __global__ void __launch_bounds__(kThreads) k_phase_finish(Geom g, Params P, con
     }
 }
 
-// ---- in-place (AA-pattern) streaming, kernel_variant 2: one population array, owned planes only, z periodic ----
-// blockIdx.y = owned plane; the per-thread work is d3q19_threads.h's aa_* functions
-__device__ __forceinline__ lbm3::AaPlanes aa_planes(const Geom &g, int zs)
-{
-    const long long pp = 19 * g.pl;
-    const int zm = zs == 2 ? g.nz + 1 : zs - 1, zp = zs == g.nz + 1 ? 2 : zs + 1;
-    return lbm3::AaPlanes{zm * pp, zs * pp, zp * pp};
-}
-template <bool ODD>
-__global__ void __launch_bounds__(kThreads) k_aa_phase(Geom g, Params P, const pop_t *gq, double *phi)
-{
-    const unsigned idx = blockIdx.x * kThreads + threadIdx.x;
-    if (idx >= (unsigned)(g.nx * g.ny)) return;
-    const int zs = 2 + blockIdx.y;
-    lbm3::aa_phase_thread<ODD>(g, P, gq, phi, zs, aa_planes(g, zs), (int)(idx % (unsigned)g.nx), (int)(idx / (unsigned)g.nx));
-}
-template <bool FXY, bool WRITE, int COLL, bool ODD>
-__global__ void __launch_bounds__(128, 3) k_aa_collide(Geom g, Params P, pop_t *f, pop_t *gq, const double *__restrict__ phi,
-                                                        FieldsOut o)
-{
-    const unsigned idx = blockIdx.x * 128 + threadIdx.x;
-    if (idx >= (unsigned)(g.nx * g.ny)) return;
-    const int zs = 2 + blockIdx.y;
-    lbm3::aa_collide_thread<FXY, WRITE, COLL, ODD>(g, P, f, gq, phi, o, zs, aa_planes(g, zs), (int)(idx % (unsigned)g.nx),
-                                                   (int)(idx / (unsigned)g.nx));
-}
-// The BGK step in place with the collision in its streamed form (collide_streamed, as in k_step_one): every thread
-// parks its own 19 g values in its own column of shared memory with asynchronous copies issued before anything else
-// -- they are needed only at the end of the collision -- and every post-collision pair leaves for its place as soon
-// as it exists.  No thread reads another thread's column: no barrier.  A direction group of collide_streamed is
-// closed under reversal and fetches its g values before it emits, and all f values are in registers before the
-// first store, so no place is overwritten before it has been read.
-__device__ __forceinline__ void aa_cp_async(pop_t *smem, const pop_t *gmem)
-{
-    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
-    if (sizeof(pop_t) == 8) asm volatile("cp.async.ca.shared.global [%0], [%1], 8;\n" ::"r"(s), "l"(gmem) : "memory");
-    else asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(s), "l"(gmem) : "memory");
-}
-template <bool ODD>
-struct AaEmit {
-    const Geom &g;
-    const lbm3::AaPlanes &z;
-    pop_t *f, *gq;
-    int ix, iy;
-    template <int K>
-    __device__ __forceinline__ void operator()(double fv, double gv) const
-    {
-        const long long t = lbm3::aa_slot<ODD, K>(g, z, ix, iy);
-        f[t] = (pop_t)fv;
-        gq[t] = (pop_t)gv;
-    }
-};
-template <bool FXY, bool WRITE, bool ODD>
-__global__ void __launch_bounds__(128, 4) k_aa_core(Geom g, Params P, pop_t *f, pop_t *gq, const double *__restrict__ phi,
-                                                     FieldsOut o)
-{
-    __shared__ pop_t gs_all[19 * 128];
-    const int NX = g.nx, NY = g.ny;
-    const unsigned idx = blockIdx.x * 128 + threadIdx.x;
-    if (idx >= (unsigned)(NX * NY)) return;
-    const int zs = 2 + blockIdx.y;
-    const int ix = (int)(idx % (unsigned)NX), iy = (int)(idx / (unsigned)NX);
-    if (ix < 1 || ix > NX - 2 || iy < 1 || iy > NY - 2) {
-        if (WRITE && (ix == NX - 1 || iy == NY - 1)) {   // wall node fields, lattice.hpp:75-106
-            const long long at = (long long)(zs - 2) * g.pl + idx;
-            o.rho[at] = P.rho_wall; o.ux[at] = 0.0; o.uy[at] = 0.0; o.uz[at] = 0.0;
-        }
-        return;
-    }
-    const lbm3::AaPlanes z = aa_planes(g, zs);
-    pop_t *gs = gs_all + threadIdx.x;
-    lbm3::aa_each([&](auto m) {
-        constexpr int M = decltype(m)::value;
-        constexpr int OPP[19] = {0, 2, 1, 4, 3, 6, 5, 10, 9, 8, 7, 14, 13, 12, 11, 18, 17, 16, 15};
-        aa_cp_async(gs + OPP[M] * 128, gq + lbm3::aa_slot<ODD, M>(g, z, ix, iy));
-    });
-    asm volatile("cp.async.commit_group;\n" ::: "memory");
-    double F[19], PH[19];
-    lbm3::aa_load<ODD>(g, z, f, ix, iy, F);
-    {
-        constexpr int CX[19] = LBM3_CX, CY[19] = LBM3_CY, CZ[19] = LBM3_CZ;
-        const double *pp = phi + (long long)zs * g.pl + idx;
-        const int pl32 = (int)g.pl;
-#pragma unroll
-        for (int k = 0; k < 19; k++) PH[k] = __ldg(pp + (CZ[k] * pl32 + CY[k] * NX + CX[k]));
-    }
-    double gx, gy, gz, lap;
-    lbm3::stencils(PH, gx, gy, gz, lap);
-    if (WRITE) {
-        if (iy == 1) lbm3::mirror_fields<2>(F, P, o, (long long)(zs - 2) * g.pl + ix);
-        if (ix == 1) lbm3::mirror_fields<1>(F, P, o, (long long)(zs - 2) * g.pl + (long long)iy * NX);
-        if (ix == 1 && iy == 1) lbm3::mirror_fields<3>(F, P, o, (long long)(zs - 2) * g.pl);
-    }
-    asm volatile("cp.async.wait_group 0;\n" ::: "memory");
-    auto getG = [gs](int k) { return (double)gs[k * 128]; };
-    // the stores go to the places the loads came from; with the pitch hidden from the optimiser the 38 store
-    // addresses are formed when they are needed instead of being kept in registers from the loads on (spills)
-    Geom gst = g;
-    {
-        int pitch = (int)g.pl;
-        asm volatile("" : "+r"(pitch));
-        gst.pl = pitch;
-    }
-    double rho, ux, uy, uz;
-    lbm3::collide_streamed<FXY>(F, getG, AaEmit<ODD>{gst, z, f, gq, ix, iy}, PH[0], gx, gy, gz, lap, P, rho, ux, uy, uz);
-    if (WRITE) {
-        const long long at = (long long)(zs - 2) * g.pl + idx;
-        o.rho[at] = rho; o.ux[at] = ux; o.uy[at] = uy; o.uz[at] = uz;
-    }
-}
-__global__ void __launch_bounds__(kThreads) k_aa_swap(Geom g, pop_t *f, pop_t *gq)
-{
-    const unsigned idx = blockIdx.x * kThreads + threadIdx.x;
-    if (idx >= (unsigned)(g.nx * g.ny)) return;
-    const int zs = 2 + blockIdx.y;
-    lbm3::aa_swap_thread(g, f, gq, aa_planes(g, zs), (int)(idx % (unsigned)g.nx), (int)(idx / (unsigned)g.nx));
-}
-
 __global__ void k_init_fields(Geom g, Params P, double *phi, double *rho)
 {
     const int z = blockIdx.x * blockDim.x + threadIdx.x;
@@ -343,9 +232,12 @@ public:
     // kernel_variant: 0 one-pass step (collide + next step's phase field in one launch, d3q19_step.cuh); 5 two-pass
     // (k_phase, then the collide kernels); 1 two-pass with the plain whole-plane collide kernel (the cross-check).
     // The TRT extension exists in the array form of the collision only and always takes the two-pass path.
-    // 2: in-place (AA-pattern) streaming on ONE population array -- half the population memory; two launches per step
-    // (phase field, then collide in place); one slab per context (z periodic inside it), any collision operator.
-    bool aa() const { return cfg_.kernel_variant == 2; }
+    // 2 and 6: in-place (AA-pattern) streaming on ONE population array (d3q19_inplace.cuh) -- half the population
+    // memory; one slab per context (z periodic inside it), any collision operator.  2: one pass (the phase field of
+    // the step runs ahead of the collision inside the same launch; BGK -- the extensions take the two-pass form);
+    // 6: two passes (phase field, then collide in place).
+    bool aa() const { return cfg_.kernel_variant == 2 || cfg_.kernel_variant == 6; }
+    bool aa_one() const { return cfg_.kernel_variant == 2 && coll() == 0; }
     int coll() const { return mrt_ ? 2 : (P_.trt_magic > 0.0 ? 1 : 0); }
     bool one_pass() const { return cfg_.kernel_variant == 0 && coll() == 0; }
 
@@ -354,10 +246,10 @@ public:
         if (cfg_.nx < 4 || cfg_.ny < 4) return rt_.fail(LBM_EINVAL, "D3Q19: nx and ny must be at least 4");
         if (cfg_.slab_count < 1 || cfg_.slab_rank < 0 || cfg_.slab_rank >= cfg_.slab_count)
             return rt_.fail(LBM_EINVAL, "bad slab_rank/slab_count");
-        if (cfg_.kernel_variant != 0 && cfg_.kernel_variant != 1 && cfg_.kernel_variant != 5 && cfg_.kernel_variant != 2)
-            return rt_.fail(LBM_EINVAL, "D3Q19: kernel_variant must be 0 (one-pass), 5 (two-pass, interior + rim), 1 (two-pass, plain) or 2 (in place, one array)");
+        if (cfg_.kernel_variant != 0 && cfg_.kernel_variant != 1 && cfg_.kernel_variant != 5 && !aa())
+            return rt_.fail(LBM_EINVAL, "D3Q19: kernel_variant must be 0 (one-pass), 5 (two-pass, interior + rim), 1 (two-pass, plain), 2 (in place on one array, one pass) or 6 (in place, two passes)");
         if (aa() && cfg_.slab_count != 1)
-            return rt_.fail(LBM_EINVAL, "D3Q19 kernel_variant 2 (in-place streaming) runs on one slab per context: use slab_count 1");
+            return rt_.fail(LBM_EINVAL, "D3Q19 kernel_variant 2 / 6 (in-place streaming) runs on one slab per context: use slab_count 1");
         // solver.hpp:25-30
         const int zstep = cfg_.nz / cfg_.slab_count;
         z_begin_ = cfg_.slab_rank * zstep;
@@ -406,15 +298,17 @@ public:
             LBM_CUDA(rt_, cudaMemsetAsync(*p, 0, fld_bytes, rt_.stream));
         }
         LBM_CUDA(rt_, rt_.dev_alloc(&diag_, (size_t)(diagnostics_scratch_blocks() + 1) * 6 * sizeof(double)));
-        if (one_pass()) {
-            // strip / lag geometry of the one-pass kernel (d3q19_step.cuh).  A strip is `sb_` blocks of 128 in-plane
-            // nodes; the phase part trails the collide part by `lag_` plane-steps = kLagWindows times the number of
-            // blocks the GPU holds at once (measured at 512^3: 1.0 -> 16.4, 1.25 -> 16.2, 1.5 -> 15.3, 1.75 -> 15.4,
-            // 2 -> 15.5, 3 -> 16.3 ms: shorter and blocks wait for their producers, longer and L2 loses the g* rows).
+        if (one_pass() || aa_one()) {
+            // strip / lag geometry of the one-pass kernels (d3q19_step.cuh, d3q19_inplace.cuh).  A strip is `sb_` blocks
+            // of 128 in-plane nodes; one part of a block trails the other by `lag_` plane-steps = kLagWindows times the
+            // number of blocks the GPU holds at once (measured at 512^3 with k_step_one: 1.0 -> 16.4, 1.25 -> 16.2,
+            // 1.5 -> 15.3, 1.75 -> 15.4, 2 -> 15.5, 3 -> 16.3 ms: shorter and blocks wait for their producers, longer
+            // and L2 loses the g rows).
             if (g_.pl * 40 >= (1ll << 31) || g_.nz + 4 + 64 > 65535)
                 return rt_.fail(LBM_EINVAL, "D3Q19 one-pass step: a plane must hold fewer than 53 million nodes and a slab fewer than 65 000 planes (use kernel_variant 1)");
             int sms = 148;
             cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, rt_.device);
+            sms_ = sms;
             double lag_windows = 1.5;
             if (const char *e = getenv("LBM_TUNE_LAGK")) lag_windows = atof(e);     // measurement knobs, not part of the ABI
             if (const char *e = getenv("LBM_TUNE_POL")) pol_ = atoi(e);
@@ -425,7 +319,10 @@ public:
             if (nblk_ + dshift_ <= sb_) sb_ = nblk_ + dshift_;   // one strip
             nstrips_ = (nblk_ + dshift_ + sb_ - 1) / sb_;
             lag_ = 2 + (int)(lag_windows * (sms * 4) / sb_);
+            // control words: [0] give-up flag, [32 + 32 i] counter of group i, then (in place) one word per segment of
+            // an owned plane for the warps that did not collide, [last] number of steps that fell back
             ctrl_words_ = ((size_t)nstrips_ * (g_.nz + 4 + lag_) + 2) * lbm3::LAG_PAD + 64;
+            if (aa_one()) ctrl_words_ += (size_t)nblk_ * g_.nz;
             LBM_CUDA(rt_, rt_.dev_alloc(&ctrl_, ctrl_words_ * sizeof(unsigned)));
             LBM_CUDA(rt_, cudaMemsetAsync(ctrl_, 0, ctrl_words_ * sizeof(unsigned), rt_.stream));
         }
@@ -540,8 +437,40 @@ public:
         LBM_TRY(rt_.launched("k_aa_phase"));
         return exchange(true);
     }
+    // one pass (d3q19_inplace.cuh): phase parts run L plane-steps ahead of the collisions of the same launch
+    lbm_status aa_step_one(int write_fields)
+    {
+        lbm3::AaPlan A{};
+        A.sb = sb_; A.nstrips = nstrips_; A.L = lag_ + 1; A.dshift = dshift_; A.nblk = nblk_;
+        A.pz = g_.nz + A.L;
+        A.full = (unsigned)sb_;
+        A.spin_limit = spin_limit_;
+        const size_t counters = (size_t)nstrips_ * g_.nz * lbm3::LAG_PAD, masks = (size_t)nblk_ * g_.nz;
+        if (32 + counters + masks + 1 > ctrl_words_) return rt_.fail(LBM_ESTATE, "in-place one-pass kernel: control words too small");
+        LBM_CUDA(rt_, cudaMemsetAsync(ctrl_, 0, (32 + counters + masks) * sizeof(unsigned), rt_.stream));
+        unsigned *done = ctrl_ + 32, *skipped = ctrl_ + 32 + counters, *sticky = ctrl_ + ctrl_words_ - 1;
+        const FieldsOut o = fields_out();
+        const dim3 grid(sb_, A.pz, nstrips_);
+        rt_.about_to_launch();
+        with_flavour(write_fields, [&](auto fxy, auto wr, auto) {
+            constexpr bool FXY = decltype(fxy)::value, WR = decltype(wr)::value;
+            if (aa_odd_) k_aa_one<FXY, WR, true><<<grid, 128, 0, rt_.stream>>>(g_, P_, f_[0], gq_[0], phib_[0], o, done, ctrl_, skipped, A);
+            else k_aa_one<FXY, WR, false><<<grid, 128, 0, rt_.stream>>>(g_, P_, f_[0], gq_[0], phib_[0], o, done, ctrl_, skipped, A);
+        });
+        LBM_TRY(rt_.launched("k_aa_one"));
+        rt_.about_to_launch();
+        with_flavour(write_fields, [&](auto fxy, auto wr, auto) {
+            constexpr bool FXY = decltype(fxy)::value, WR = decltype(wr)::value;
+            if (aa_odd_) k_aa_repair<FXY, WR, true><<<sms_ * 3, 128, 0, rt_.stream>>>(g_, P_, f_[0], gq_[0], phib_[0], o, ctrl_, skipped, sticky, nblk_);
+            else k_aa_repair<FXY, WR, false><<<sms_ * 3, 128, 0, rt_.stream>>>(g_, P_, f_[0], gq_[0], phib_[0], o, ctrl_, skipped, sticky, nblk_);
+        });
+        LBM_TRY(rt_.launched("k_aa_repair"));
+        aa_odd_ = !aa_odd_;
+        return LBM_OK;
+    }
     lbm_status aa_step(int write_fields)
     {
+        if (aa_one()) return aa_step_one(write_fields);
         LBM_TRY(aa_phase());
         const FieldsOut o = fields_out();
         const dim3 grid = owned_grid(128);
@@ -701,7 +630,7 @@ public:
 
     lbm_status slab_collide(int write_fields) override
     {
-        if (aa()) return rt_.fail(LBM_EINVAL, "kernel_variant 2 (in-place streaming) is driven by lbm_step, not by the lbm_slab_* protocol");
+        if (aa()) return rt_.fail(LBM_EINVAL, "kernel_variant 2 / 6 (in-place streaming) is driven by lbm_step, not by the lbm_slab_* protocol");
         const int nz = g_.nz;
         if (one_pass()) {
             LBM_TRY(ensure_phi());
@@ -727,7 +656,7 @@ public:
     // planes, whose g populations the exchange has just delivered
     lbm_status slab_finish() override
     {
-        if (aa()) return rt_.fail(LBM_EINVAL, "kernel_variant 2 (in-place streaming) is driven by lbm_step, not by the lbm_slab_* protocol");
+        if (aa()) return rt_.fail(LBM_EINVAL, "kernel_variant 2 / 6 (in-place streaming) is driven by lbm_step, not by the lbm_slab_* protocol");
         cur_ = 1 - cur_;
         if (lag_pending_) {
             lag_pending_ = false;
@@ -1051,7 +980,7 @@ private:
     int pend_p0_ = 0, pend_p1_ = 0;      // owned planes whose phase field the pending one-pass step has written
     double *rho_ = nullptr, *ux_ = nullptr, *uy_ = nullptr, *uz_ = nullptr, *diag_ = nullptr;
     // one-pass kernel: strip geometry and its control words ([0] give-up flag, [1..] group counters, last: fallback count)
-    int nblk_ = 0, dshift_ = 0, sb_ = 0, nstrips_ = 0, lag_ = 0;
+    int nblk_ = 0, dshift_ = 0, sb_ = 0, nstrips_ = 0, lag_ = 0, sms_ = 148;
     int pol_ = 1;     // L2 residency hints on (15.28 vs 15.63 ms at 512^3)
     unsigned spin_limit_ = 4000;   // polls of 200 ns before a warp of the one-pass kernel gives up (~1 ms)
     unsigned *ctrl_ = nullptr;
