@@ -433,6 +433,7 @@ def ours(args, rank, world, local_rank):
     ms = ev0.elapsed_time(ev1)
     launches = ctx.launch_count - launches0
     fallbacks = ctx.phase_fallbacks
+    device_bytes = ctx.device_bytes
     # per-kernel split: a second, untimed-for-the-headline pass with one CUDA event pair around every launch
     psteps = min(args.steps, 20)
     ctx.profile(True)
@@ -543,7 +544,7 @@ def ours(args, rank, world, local_rank):
                            "parallelism": "z-slab x%d" % world},
                 "mlups_per_gpu": value / world, "roofline": roof, "cpu_baseline": cb, "e2e": e2e, "clocks": clk,
                 "gpu_launches": launches, "phase_fallbacks": fallbacks,
-                "device_bytes_per_gpu": ctx.device_bytes}
+                "device_bytes_per_gpu": device_bytes}
         if parity is not None:
             line["parity"] = parity
         if secondary is not None:
