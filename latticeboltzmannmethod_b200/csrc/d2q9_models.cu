@@ -92,6 +92,110 @@ __global__ void __launch_bounds__(TX *TY, MINB) k_sc_fused(lbm2::ScParams P, con
         f2[k * n + (long long)y2 * nx + x2] = F[k];
     }
 }
+// kernel_variant 6: one launch per Shan-Chen step by MARCHING (the scheme of k_b2_march below): a block owns 128
+// consecutive columns (iX, the fast index) and walks over `yc` consecutive rows.  psi = 1 - exp(-rho) lives only in
+// shared memory, as a ring of four rows of 128 + 2 values: before row y is collided the block has evaluated psi of
+// row y + 1 from the populations it is about to collide anyway.  Against the tile form (k_sc_fused) the ring of
+// neighbours whose populations are re-read -- 76 nodes for a 32 x 4 tile of 128 -- shrinks to 2/yc + 2/128 of a node
+// per node, and so do the redundant exp evaluations.  Populations travel through shared memory in a three-row pipeline
+// of 8-byte asynchronous copies, every thread its own column; the ring needs the one barrier per row.
+__device__ __forceinline__ void sc_cp_async8(double *smem, const double *gmem)
+{
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;\n" ::"r"(s), "l"(gmem) : "memory");
+}
+template <bool WRITE>
+__global__ void __launch_bounds__(128, 6) k_sc_march(lbm2::ScParams P, const double *f, double *f2, double *rho, double *u1, double *u2, int yc)
+{
+    __shared__ double fb[3 * 9 * 128];     // populations of the rows in flight
+    __shared__ double hb[3 * 9 * 2];       // ... of the columns just outside the block's 128 (threads 0 and 127)
+    __shared__ double ring[4 * 130];       // psi of rows y-1 .. y+1 (+ the one being written)
+    const int nx = P.nx, ny = P.ny;
+    const long long n = (long long)nx * ny;
+    const int t = threadIdx.x;
+    const int x0 = blockIdx.x * 128, y0 = blockIdx.y * yc;
+    const int cnt = min(128, nx - x0);                       // columns of this block
+    const int nrow = min(yc, ny - y0);                       // rows it collides: y0 .. y0 + nrow - 1
+    const int ix = x0 + t;
+    const bool active = t < cnt;
+    // periodic neighbours of the block's column range: thread 0 the one before, thread 127 the one after
+    const bool halo = t == 0 || t == 127;
+    const int hx = t == 0 ? (x0 == 0 ? nx - 1 : x0 - 1) : (x0 + cnt == nx ? 0 : x0 + cnt);
+    const int hcol = t == 0 ? 0 : 1, hring = t == 0 ? 0 : cnt + 1;
+
+    auto request = [&](int r) {      // row r relative to y0; -1 and nrow are the periodic neighbours
+        if (r <= nrow) {
+            int y = y0 + r;
+            y = y < 0 ? y + ny : (y >= ny ? y - ny : y);
+            const int bi = (r + 1) % 3;
+            const long long base = (long long)y * nx;
+            if (active) {
+#pragma unroll
+                for (int k = 0; k < 9; k++) sc_cp_async8(fb + (bi * 9 + k) * 128 + t, f + k * n + base + ix);
+            }
+            if (halo) {
+#pragma unroll
+                for (int k = 0; k < 9; k++) sc_cp_async8(hb + (bi * 9 + k) * 2 + hcol, f + k * n + base + hx);
+            }
+        }
+        asm volatile("cp.async.commit_group;\n" ::: "memory");
+    };
+    auto psi_of = [&](int r) {       // shanchen.cpp:124-132 and psi of :152-157, for this thread's node(s) of row r
+        const int bi = (r + 1) % 3, ri = (r + 1) & 3;
+        if (active) {
+            double d = 0;
+#pragma unroll
+            for (int k = 0; k < 9; k++) d += fb[(bi * 9 + k) * 128 + t];
+            ring[ri * 130 + t + 1] = 1.0 - lbm_exp(-d);
+        }
+        if (halo) {
+            double d = 0;
+#pragma unroll
+            for (int k = 0; k < 9; k++) d += hb[(bi * 9 + k) * 2 + hcol];
+            ring[ri * 130 + hring] = 1.0 - lbm_exp(-d);
+        }
+    };
+
+    request(-1);
+    request(0);
+    request(1);
+    asm volatile("cp.async.wait_group 2;\n" ::: "memory");
+    psi_of(-1);
+    asm volatile("cp.async.wait_group 1;\n" ::: "memory");
+    psi_of(0);
+    const int xm = ix == 0 ? nx - 1 : ix - 1, xp = ix == nx - 1 ? 0 : ix + 1;
+    for (int r = 0; r < nrow; r++) {
+        asm volatile("cp.async.wait_group 0;\n" ::: "memory");   // row r + 1 has landed
+        psi_of(r + 1);
+        __syncthreads();
+        const int bi = (r + 1) % 3, iy = y0 + r;
+        double F[9];
+        if (active) {
+#pragma unroll
+            for (int k = 0; k < 9; k++) F[k] = fb[(bi * 9 + k) * 128 + t];
+        }
+        request(r + 2);                                          // into the buffer of row r - 1
+        if (active) {
+            const int CX[9] = LBM2_CX, CY[9] = LBM2_CY;
+            double dense = 0, ps[9];
+#pragma unroll
+            for (int k = 0; k < 9; k++) dense += F[k];
+#pragma unroll
+            for (int k = 0; k < 9; k++) ps[k] = ring[((r + 1 + CY[k]) & 3) * 130 + t + 1 + CX[k]];
+            double v1, v2;
+            lbm2::sc_collide_core(P, F, dense, ps[0], ps, v1, v2);
+            const long long i = (long long)iy * nx + ix;
+            if (WRITE) { rho[i] = dense; u1[i] = v1; u2[i] = v2; }
+            const int ym = iy == 0 ? ny - 1 : iy - 1, yp = iy == ny - 1 ? 0 : iy + 1;
+#pragma unroll
+            for (int k = 0; k < 9; k++) {
+                const int x2 = CX[k] > 0 ? xp : (CX[k] < 0 ? xm : ix), y2 = CY[k] > 0 ? yp : (CY[k] < 0 ? ym : iy);
+                f2[k * n + (long long)y2 * nx + x2] = F[k];
+            }
+        }
+    }
+    asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+}
 // ---- binary kernels (node index i = iX*NY+iY, iY fastest) ----
 __global__ void __launch_bounds__(kThreads) k_b2_wallphase(lbm2::B2Params P, double *phase)
 {
@@ -318,6 +422,116 @@ __global__ void __launch_bounds__(128, 4) k_b2_one(lbm2::B2Params P, const doubl
     __syncthreads();
     if (threadIdx.x == 0) asm volatile("red.release.gpu.global.add.u32 [%0], %1;\n" ::"l"(done + (size_t)(b / L.sb) * 32), "r"(1u) : "memory");
 }
+// kernel_variant 0 (the default): one pass per binary-liquid step by MARCHING.  A block owns 128 consecutive rows (iY, the fast
+// index) and walks over `xc` consecutive columns (iX).  The phase field lives only in shared memory, as a ring of four
+// columns of 128 + 2 values; before column x is collided the block has summed the phase values of column x + 1 from
+// the g populations it is about to collide anyway, so HBM sees every population once in and once out and the phase
+// pass (88 B per update on top of 288) is gone -- without any ordering between blocks.  What it costs instead: the g
+// values of the two columns either side of a block's range and of the two rows either side of its 128 are read by the
+// neighbouring blocks as well (2/xc + 2/128 of g).  All populations travel through shared memory in a three-column
+// pipeline of 8-byte asynchronous copies (every thread its own column: only the ring needs the one barrier per column).
+__device__ __forceinline__ void b2_cp_async8(double *smem, const double *gmem)
+{
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;\n" ::"r"(s), "l"(gmem) : "memory");
+}
+constexpr int kB2MarchSmem = ((3 * 9 + 3 * 9) * 128 + 3 * 9 * 2 + 4 * 130) * (int)sizeof(double);
+template <bool WRITE>
+__global__ void __launch_bounds__(128, 3) k_b2_march(lbm2::B2Params P, const double *f, const double *g, double *f2, double *g2,
+                                                     double *phase, double *rho, double *uxo, double *uyo, int xc)
+{
+    extern __shared__ __align__(16) double b2m_smem[];
+    double *fb = b2m_smem;                 // [3][9][128] f of the columns in flight
+    double *gb = fb + 3 * 9 * 128;         // [3][9][128] g
+    double *hb = gb + 3 * 9 * 128;         // [3][9][2]   g of the rows just outside the block's 128 (threads 0 and 127)
+    double *ring = hb + 3 * 9 * 2;         // [4][130]    phase field of columns x-1 .. x+1 (+ one being written)
+    const int NX = P.nx, NY = P.ny;
+    const long long n = (long long)NX * NY;
+    const int t = threadIdx.x;
+    const int y0 = blockIdx.x * 128, x0 = blockIdx.y * xc;
+    const int ncol = min(xc, NX - x0);                       // columns this block collides: x0 .. x0 + ncol - 1
+    const int iy = y0 + t;
+    const bool in_y = iy < NY, active = iy >= 1 && iy <= NY - 2;
+    const int sy = min(max(iy, 1), NY - 2);                  // wall rows take their neighbour row's sum (binary.cpp:245-249)
+    int hy = -1;
+    if (t == 0 && y0 > 0) hy = y0 - 1;
+    if (t == 127 && y0 + 128 < NY) hy = y0 + 128;
+    const int hsy = min(max(hy, 1), NY - 2), hcol = t == 0 ? 0 : 1;
+
+    // column r (relative to x0; -1 and ncol are the neighbours, of which only g is needed)
+    auto request = [&](int r) {
+        if (r <= ncol) {
+            int x = x0 + r;
+            x = x < 0 ? x + NX : (x >= NX ? x - NX : x);
+            const int bi = (r + 1) % 3;
+            const long long base = (long long)x * NY;
+            if (in_y) {
+#pragma unroll
+                for (int k = 0; k < 9; k++) b2_cp_async8(gb + (bi * 9 + k) * 128 + t, g + k * n + base + sy);
+                if (active && r >= 0 && r < ncol) {
+#pragma unroll
+                    for (int k = 0; k < 9; k++) b2_cp_async8(fb + (bi * 9 + k) * 128 + t, f + k * n + base + iy);
+                }
+            }
+            if (hy >= 0) {
+#pragma unroll
+                for (int k = 0; k < 9; k++) b2_cp_async8(hb + (bi * 9 + k) * 2 + hcol, g + k * n + base + hsy);
+            }
+        }
+        asm volatile("cp.async.commit_group;\n" ::: "memory");
+    };
+    // this thread's phase values of column r into the ring (its copies have landed); binary.cpp:239-250, ascending k
+    auto phase_of = [&](int r) {
+        const int bi = (r + 1) % 3, ri = (r + 1) & 3;
+        if (in_y) {
+            double s = 0.0;
+#pragma unroll
+            for (int k = 0; k < 9; k++) s += gb[(bi * 9 + k) * 128 + t];
+            ring[ri * 130 + t + 1] = sy == iy ? s : s - P.wall_gradient;
+        }
+        if (hy >= 0) {
+            double s = 0.0;
+#pragma unroll
+            for (int k = 0; k < 9; k++) s += hb[(bi * 9 + k) * 2 + hcol];
+            ring[ri * 130 + (t == 0 ? 0 : 129)] = hsy == hy ? s : s - P.wall_gradient;
+        }
+    };
+
+    request(-1);
+    request(0);
+    request(1);
+    asm volatile("cp.async.wait_group 2;\n" ::: "memory");
+    phase_of(-1);
+    asm volatile("cp.async.wait_group 1;\n" ::: "memory");
+    phase_of(0);
+    for (int r = 0; r < ncol; r++) {
+        asm volatile("cp.async.wait_group 0;\n" ::: "memory");   // column r + 1 has landed
+        phase_of(r + 1);
+        __syncthreads();
+        const int bi = (r + 1) % 3, ix = x0 + r;
+        double F[9], G[9], ph9[9];
+        if (active) {
+#pragma unroll
+            for (int k = 0; k < 9; k++) {
+                F[k] = fb[(bi * 9 + k) * 128 + t];
+                G[k] = gb[(bi * 9 + k) * 128 + t];
+            }
+        }
+        request(r + 2);                                          // into the buffers of column r - 1
+        const long long i = (long long)ix * NY + iy;
+        if (WRITE && in_y) phase[i] = ring[((r + 1) & 3) * 130 + t + 1];   // wall rows included
+        if (active) {
+            const int CX[9] = LBM2_CX, CY[9] = LBM2_CY;
+#pragma unroll
+            for (int k = 0; k < 9; k++) ph9[k] = ring[((r + 1 + CX[k]) & 3) * 130 + t + 1 + CY[k]];
+            double d, vx, vy;
+            lbm2::b2_collide_core(P, F, G, ph9, d, vx, vy);
+            if (WRITE) { rho[i] = d; uxo[i] = vx; uyo[i] = vy; }
+            lbm2::b2_push(P, F, G, f2, g2, ix, iy);
+        }
+    }
+    asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+}
 // ---- MRT kernels ----
 __global__ void __launch_bounds__(kThreads) k_mrt_init(lbm2::MrtParams P, const double *rho, const double *ux, const double *uy, double *f)
 {
@@ -524,6 +738,19 @@ public:
         // kernel_variant 1: the two-kernel form (density pass + collide); otherwise the fused tile kernel:
         // 0 = 32x4 tile capped at 64 registers, 8 blocks/SM (fastest measured: 2.12 ms at 8192^2); 2 = 32x16;
         // 3 = 32x8 at 64 registers (2.27 ms); 5 = 32x8 uncapped, 3 blocks/SM (2.58 ms)
+        if (cfg_.kernel_variant == 6) {     // marching kernel
+            int yc = 64;
+            if (const char *e = getenv("LBM_TUNE_XC")) yc = std::max(1, atoi(e));   // measurement knob
+            const dim3 grid((cfg_.nx + 127) / 128, (cfg_.ny + yc - 1) / yc);
+            for (int t = 0; t < nsteps; t++) {
+                auto kern = t == nsteps - 1 ? k_sc_march<true> : k_sc_march<false>;
+                rt_.about_to_launch();
+                kern<<<grid, 128, 0, rt_.stream>>>(P_, f_[cur_], f_[1 - cur_], fields_[LBM_RHO], fields_[LBM_UX], fields_[LBM_UY], yc);
+                LBM_TRY(rt_.launched("k_sc_march"));
+                cur_ = 1 - cur_;
+            }
+            return LBM_OK;
+        }
         if (cfg_.kernel_variant != 1) {
             for (int t = 0; t < nsteps; t++) {
                 const bool w = t == nsteps - 1;
@@ -653,11 +880,31 @@ public:
         }
         return LBM_OK;
     }
+    lbm_status step_march(int nsteps)
+    {
+        int xc = 64;
+        if (const char *e = getenv("LBM_TUNE_XC")) xc = std::max(1, atoi(e));   // measurement knob
+        const dim3 grid((cfg_.ny + 127) / 128, (cfg_.nx + xc - 1) / xc);
+        for (int t = 0; t < nsteps; t++) {
+            const bool w = t == nsteps - 1;
+            auto kern = w ? k_b2_march<true> : k_b2_march<false>;
+            LBM_CUDA(rt_, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kB2MarchSmem));
+            rt_.about_to_launch();
+            kern<<<grid, 128, kB2MarchSmem, rt_.stream>>>(P_, f_[cur_], g_[cur_], f_[1 - cur_], g_[1 - cur_], fields_[LBM_PHASE],
+                                                          fields_[LBM_RHO], fields_[LBM_UX], fields_[LBM_UY], xc);
+            LBM_TRY(rt_.launched("k_b2_march"));
+            cur_ = 1 - cur_;
+        }
+        return LBM_OK;
+    }
     lbm_status step(int nsteps) override
     {
         if (one_pass_) return step_one_pass(nsteps);
-        // kernel_variant 0 (default) and 1 (and 5 on grids the one-pass kernel does not take): phase pass + collide, the
-        // fastest measured (4.13 ms at 8192^2; the one-pass kernel, variant 5: 4.68 ms -- it moves 303 instead of 376 B per
+        // kernel_variant 0 (default): the marching kernel, one pass with the phase field in shared memory: 3.42 ms at
+        // 8192^2 = 0.86 of the measured HBM peak (columns per block 32 / 64 / 128 / 256: 3.41 / 3.42 / 3.45 / 3.47 ms)
+        if (cfg_.kernel_variant == 0) return step_march(nsteps);
+        // kernel_variant 6 and 1 (and 5 on grids the one-pass kernel does not take): phase pass + collide, round 1's
+        // default (3.94 ms at 8192^2; the lagging one-pass kernel, variant 5: 4.68 ms -- it moves 303 instead of 376 B per
         // update, but this collision is short enough that the phase part's extra instructions cost more than its bytes;
         // a staged, streamed form of the collide kernel at 5 / 6 / 8 blocks per SM: 4.29 / 4.19 / 4.79 ms -- the register
         // form already moves its 288 B per update at 5.9 TB/s, occupancy is not what limits it).  The fused

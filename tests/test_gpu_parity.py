@@ -242,7 +242,7 @@ def test_d3q19_population_roundtrip_and_diagnostics():
 
 
 # ---------------- 2-D programs ----------------
-@pytest.mark.parametrize("variant", [0, 1, 2, 3, 5])
+@pytest.mark.parametrize("variant", [0, 1, 2, 3, 5, 6])
 def test_shanchen_vs_oracle_and_golden(variant):
     """variant 0/2/3/5: the fused tile kernel (32x4, 32x16, 32x8 at 64 registers, 32x8); 1: density pass + collide."""
     api = _api()
@@ -276,7 +276,7 @@ def test_shanchen_vs_oracle_and_golden(variant):
     ctx.close()
 
 
-@pytest.mark.parametrize("variant", [0, 1, 2, 3, 5])
+@pytest.mark.parametrize("variant", [0, 1, 2, 3, 5, 6])
 @pytest.mark.parametrize("nx,ny", [(45, 37), (64, 8), (33, 100)])
 def test_shanchen_odd_sizes_vs_oracle(nx, ny, variant):
     """Grids that are no multiple of the tile: partial tiles wrap onto the periodic neighbours."""
@@ -300,7 +300,7 @@ def test_shanchen_odd_sizes_vs_oracle(nx, ny, variant):
     o.close()
 
 
-@pytest.mark.parametrize("variant", [0, 5, 1, 2, 3, 4])
+@pytest.mark.parametrize("variant", [0, 5, 1, 2, 3, 4, 6])
 def test_binary2d_vs_oracle_and_golden(variant):
     """variant 0/1: phase pass + collide (128- / 256-thread blocks); 5: the one-pass step (collide + next step's phase
     field in one launch); 2/3/4: the fused tile kernel (8x32, 4x32 at 96 registers, 4x32)."""
@@ -336,14 +336,17 @@ def test_binary2d_vs_oracle_and_golden(variant):
     ctx.close()
 
 
+@pytest.mark.parametrize("one_pass", [5, 6])
 @pytest.mark.parametrize("nx,ny", [(300, 130), (64, 1000), (1500, 40), (258, 257)])
-def test_binary2d_one_pass_equals_two_pass_on_larger_grids(nx, ny):
-    """Grids with many blocks, tall columns (pushes reach several blocks), the periodic seam in the flush zone, a restart
-    from loaded populations in between: the one-pass step must leave exactly the state of phase pass + collide."""
+def test_binary2d_one_pass_equals_two_pass_on_larger_grids(nx, ny, one_pass):
+    """Grids with many blocks, tall columns (pushes reach several blocks; several 128-row blocks and several column
+    ranges for the marching kernel), the periodic seam, a restart from loaded populations in between: the one-pass
+    steps (5: phase field of the next step summed behind the collision, 6: marching with the phase field in shared
+    memory) must leave exactly the state of phase pass + collide."""
     api = _api()
     ph0 = np.random.default_rng(3).uniform(-1, 1, nx * ny)
     ctxs = []
-    for variant in (5, 0):
+    for variant in (one_pass, 0):
         cfg = api.binary2d_config(nx, ny)
         cfg.kernel_variant = variant
         c = api.Context(cfg)
@@ -367,7 +370,7 @@ def test_binary2d_one_pass_equals_two_pass_on_larger_grids(nx, ny):
     b.close()
 
 
-@pytest.mark.parametrize("variant", [0, 5, 2, 3, 4])
+@pytest.mark.parametrize("variant", [0, 5, 2, 3, 4, 6])
 @pytest.mark.parametrize("nx,ny", [(37, 23), (4, 70), (65, 34), (9, 33)])
 def test_binary2d_random_odd_size(nx, ny, variant):
     api = _api()
