@@ -92,8 +92,9 @@ typedef struct {
                                   lattice.hpp:842-855), one slab per context (slab_count 1), driven by lbm_step only;
                                   2 one pass (the phase field runs ahead of the collision inside one launch), 6 two
                                   passes; Shan-Chen 1 = density pass + collide, 2/3/5 = other tiles of the
-                                  fused kernel; binary D2Q9 1 = 256-thread blocks, 2-4 = fused tile kernel, 5 = one-pass step (the D3Q19
-                                  scheme; slower here); MRT 0 = in-place AA-pattern streaming on ONE population array, 1 = two arrays with push
+                                  fused kernel; binary D2Q9 0 = marching kernel (one pass, the phase field in a shared-memory ring),
+                                  6 / 1 = phase pass + collide with 128- / 256-thread blocks, 2-4 = fused tile kernel,
+                                  5 = one-pass step in the manner of the D3Q19 default (slower here); MRT 0 = in-place AA-pattern streaming on ONE population array, 1 = two arrays with push
                                   streaming; curved
                                   solid 1/2 = other block shapes.  Results never depend on it. */
     double trt_magic;          /* LBM_BINARY_D3Q19 only, EXTENSION with no counterpart in the reference: 0 (default) keeps

@@ -92,110 +92,6 @@ __global__ void __launch_bounds__(TX *TY, MINB) k_sc_fused(lbm2::ScParams P, con
         f2[k * n + (long long)y2 * nx + x2] = F[k];
     }
 }
-// kernel_variant 6: one launch per Shan-Chen step by MARCHING (the scheme of k_b2_march below): a block owns 128
-// consecutive columns (iX, the fast index) and walks over `yc` consecutive rows.  psi = 1 - exp(-rho) lives only in
-// shared memory, as a ring of four rows of 128 + 2 values: before row y is collided the block has evaluated psi of
-// row y + 1 from the populations it is about to collide anyway.  Against the tile form (k_sc_fused) the ring of
-// neighbours whose populations are re-read -- 76 nodes for a 32 x 4 tile of 128 -- shrinks to 2/yc + 2/128 of a node
-// per node, and so do the redundant exp evaluations.  Populations travel through shared memory in a three-row pipeline
-// of 8-byte asynchronous copies, every thread its own column; the ring needs the one barrier per row.
-__device__ __forceinline__ void sc_cp_async8(double *smem, const double *gmem)
-{
-    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;\n" ::"r"(s), "l"(gmem) : "memory");
-}
-template <bool WRITE>
-__global__ void __launch_bounds__(128, 6) k_sc_march(lbm2::ScParams P, const double *f, double *f2, double *rho, double *u1, double *u2, int yc)
-{
-    __shared__ double fb[3 * 9 * 128];     // populations of the rows in flight
-    __shared__ double hb[3 * 9 * 2];       // ... of the columns just outside the block's 128 (threads 0 and 127)
-    __shared__ double ring[4 * 130];       // psi of rows y-1 .. y+1 (+ the one being written)
-    const int nx = P.nx, ny = P.ny;
-    const long long n = (long long)nx * ny;
-    const int t = threadIdx.x;
-    const int x0 = blockIdx.x * 128, y0 = blockIdx.y * yc;
-    const int cnt = min(128, nx - x0);                       // columns of this block
-    const int nrow = min(yc, ny - y0);                       // rows it collides: y0 .. y0 + nrow - 1
-    const int ix = x0 + t;
-    const bool active = t < cnt;
-    // periodic neighbours of the block's column range: thread 0 the one before, thread 127 the one after
-    const bool halo = t == 0 || t == 127;
-    const int hx = t == 0 ? (x0 == 0 ? nx - 1 : x0 - 1) : (x0 + cnt == nx ? 0 : x0 + cnt);
-    const int hcol = t == 0 ? 0 : 1, hring = t == 0 ? 0 : cnt + 1;
-
-    auto request = [&](int r) {      // row r relative to y0; -1 and nrow are the periodic neighbours
-        if (r <= nrow) {
-            int y = y0 + r;
-            y = y < 0 ? y + ny : (y >= ny ? y - ny : y);
-            const int bi = (r + 1) % 3;
-            const long long base = (long long)y * nx;
-            if (active) {
-#pragma unroll
-                for (int k = 0; k < 9; k++) sc_cp_async8(fb + (bi * 9 + k) * 128 + t, f + k * n + base + ix);
-            }
-            if (halo) {
-#pragma unroll
-                for (int k = 0; k < 9; k++) sc_cp_async8(hb + (bi * 9 + k) * 2 + hcol, f + k * n + base + hx);
-            }
-        }
-        asm volatile("cp.async.commit_group;\n" ::: "memory");
-    };
-    auto psi_of = [&](int r) {       // shanchen.cpp:124-132 and psi of :152-157, for this thread's node(s) of row r
-        const int bi = (r + 1) % 3, ri = (r + 1) & 3;
-        if (active) {
-            double d = 0;
-#pragma unroll
-            for (int k = 0; k < 9; k++) d += fb[(bi * 9 + k) * 128 + t];
-            ring[ri * 130 + t + 1] = 1.0 - lbm_exp(-d);
-        }
-        if (halo) {
-            double d = 0;
-#pragma unroll
-            for (int k = 0; k < 9; k++) d += hb[(bi * 9 + k) * 2 + hcol];
-            ring[ri * 130 + hring] = 1.0 - lbm_exp(-d);
-        }
-    };
-
-    request(-1);
-    request(0);
-    request(1);
-    asm volatile("cp.async.wait_group 2;\n" ::: "memory");
-    psi_of(-1);
-    asm volatile("cp.async.wait_group 1;\n" ::: "memory");
-    psi_of(0);
-    const int xm = ix == 0 ? nx - 1 : ix - 1, xp = ix == nx - 1 ? 0 : ix + 1;
-    for (int r = 0; r < nrow; r++) {
-        asm volatile("cp.async.wait_group 0;\n" ::: "memory");   // row r + 1 has landed
-        psi_of(r + 1);
-        __syncthreads();
-        const int bi = (r + 1) % 3, iy = y0 + r;
-        double F[9];
-        if (active) {
-#pragma unroll
-            for (int k = 0; k < 9; k++) F[k] = fb[(bi * 9 + k) * 128 + t];
-        }
-        request(r + 2);                                          // into the buffer of row r - 1
-        if (active) {
-            const int CX[9] = LBM2_CX, CY[9] = LBM2_CY;
-            double dense = 0, ps[9];
-#pragma unroll
-            for (int k = 0; k < 9; k++) dense += F[k];
-#pragma unroll
-            for (int k = 0; k < 9; k++) ps[k] = ring[((r + 1 + CY[k]) & 3) * 130 + t + 1 + CX[k]];
-            double v1, v2;
-            lbm2::sc_collide_core(P, F, dense, ps[0], ps, v1, v2);
-            const long long i = (long long)iy * nx + ix;
-            if (WRITE) { rho[i] = dense; u1[i] = v1; u2[i] = v2; }
-            const int ym = iy == 0 ? ny - 1 : iy - 1, yp = iy == ny - 1 ? 0 : iy + 1;
-#pragma unroll
-            for (int k = 0; k < 9; k++) {
-                const int x2 = CX[k] > 0 ? xp : (CX[k] < 0 ? xm : ix), y2 = CY[k] > 0 ? yp : (CY[k] < 0 ? ym : iy);
-                f2[k * n + (long long)y2 * nx + x2] = F[k];
-            }
-        }
-    }
-    asm volatile("cp.async.wait_group 0;\n" ::: "memory");
-}
 // ---- binary kernels (node index i = iX*NY+iY, iY fastest) ----
 __global__ void __launch_bounds__(kThreads) k_b2_wallphase(lbm2::B2Params P, double *phase)
 {
@@ -737,20 +633,9 @@ public:
     {
         // kernel_variant 1: the two-kernel form (density pass + collide); otherwise the fused tile kernel:
         // 0 = 32x4 tile capped at 64 registers, 8 blocks/SM (fastest measured: 2.12 ms at 8192^2); 2 = 32x16;
-        // 3 = 32x8 at 64 registers (2.27 ms); 5 = 32x8 uncapped, 3 blocks/SM (2.58 ms)
-        if (cfg_.kernel_variant == 6) {     // marching kernel
-            int yc = 64;
-            if (const char *e = getenv("LBM_TUNE_XC")) yc = std::max(1, atoi(e));   // measurement knob
-            const dim3 grid((cfg_.nx + 127) / 128, (cfg_.ny + yc - 1) / yc);
-            for (int t = 0; t < nsteps; t++) {
-                auto kern = t == nsteps - 1 ? k_sc_march<true> : k_sc_march<false>;
-                rt_.about_to_launch();
-                kern<<<grid, 128, 0, rt_.stream>>>(P_, f_[cur_], f_[1 - cur_], fields_[LBM_RHO], fields_[LBM_UX], fields_[LBM_UY], yc);
-                LBM_TRY(rt_.launched("k_sc_march"));
-                cur_ = 1 - cur_;
-            }
-            return LBM_OK;
-        }
+        // 3 = 32x8 at 64 registers (2.27 ms); 5 = 32x8 uncapped, 3 blocks/SM (2.58 ms).  A marching kernel (128 columns
+        // per block walking over 64 rows, psi in a shared-memory ring -- the scheme that took the binary model from
+        // 3.94 to 3.42 ms) equalled the oracle and ran in 2.03 ms against 1.98 ms for the tile kernel: not kept.
         if (cfg_.kernel_variant != 1) {
             for (int t = 0; t < nsteps; t++) {
                 const bool w = t == nsteps - 1;
@@ -1174,6 +1059,9 @@ public:
             k_bs_phase<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, g_[cur_], links_, fields_[LBM_PHASE]);
             LBM_TRY(rt_.launched("k_bs_phase"));
             rt_.about_to_launch();
+            // (A marching kernel in the manner of k_b2_march -- sums of g in a shared-memory ring of rows y-2 .. y+2, the
+            // phase value of a bounce-back neighbour looked up through its link word -- ran in 4.16 ms against 3.96 ms
+            // for these two passes: the per-neighbour link loads and look-ups cost more than the phase pass.  Not kept.)
             // kernel_variant 0 (default): 128 threads x 4 blocks/SM (128 registers), 4.27 ms at 8192^2; 1: 128 threads x 3
             // (168 registers, no spills), 4.75 ms; 2: 256 threads x 2 (128 registers), 4.45 ms
             const bool w = t == nsteps - 1;

@@ -704,45 +704,30 @@ LBM_HD void bs_phase_thread(const BsParams &P, const double *g, const unsigned s
     phi[i] = dir ? phase_temp - P.wall_gradient : phase_temp;
 }
 
-// collide_bulk (:260-356) of one fluid node, then update_bounce_back + stream folded into the push
-LBM_HD void bs_collide_thread(const BsParams &P, const double *f, const double *g, const double *phi, const unsigned short *links,
-                              double *f2, double *g2, double *rho_o, double *ux_o, double *uy_o, long long i,
-                              bool write_fields = true)
+// collide_bulk (:260-356) of one fluid node whose populations fl, gl and the nine phase values of its stencil (ph9[0]
+// the node's own) are in registers; fl and gl hold the post-collision values on return
+LBM_HD void bs_collide_node(const BsParams &P, double (&fl)[9], double (&gl)[9], const double (&ph9)[9], double &dense_temp,
+                            double &ux_temp, double &uy_temp)
 {
-    const unsigned link = links[i];
-    if (!(link & 1u)) return;
-    const long long n = (long long)P.nx * P.ny;
-    const int CX[9] = LBM2_CX, CY[9] = LBM2_CY, OPP[9] = LBM2_OPP;
+    const int CX[9] = LBM2_CX, CY[9] = LBM2_CY;
     const double W[9] = LBM2_W;
     const double WXX[9] = LBM_BS_WXX, WYY[9] = LBM_BS_WYY, WXY[9] = LBM_BS_WXY;
     const double GX[9] = LBM_BS_GX, GY[9] = LBM_BS_GY, LAP[9] = LBM_BS_LAP;
-    const int ix = (int)((unsigned)i % (unsigned)P.nx), iy = (int)((unsigned)i / (unsigned)P.nx);   // nx*ny < 2^31 (checked at create)
-    // periodic neighbours: (iX+cx+NX)%NX, (iY+cy+NY)%NY
-    const int xs[3] = {ix == 0 ? P.nx - 1 : ix - 1, ix, ix == P.nx - 1 ? 0 : ix + 1};
-    const int ys[3] = {iy == 0 ? P.ny - 1 : iy - 1, iy, iy == P.ny - 1 ? 0 : iy + 1};
-    int nb[9];      // nx*ny < 2^31 (checked at create)
-#pragma unroll
-    for (int k = 0; k < 9; k++) nb[k] = ys[CY[k] + 1] * P.nx + xs[CX[k] + 1];
-
-    double fl[9], gl[9];
-    double dense_temp = 0.0, ux_temp = 0.0, uy_temp = 0.0;
-    const double phase_temp = phi[i];
+    dense_temp = 0.0; ux_temp = 0.0; uy_temp = 0.0;
+    const double phase_temp = ph9[0];
 #pragma unroll
     for (int k = 0; k < 9; k++) {
-        fl[k] = f[k * n + i];
-        gl[k] = g[k * n + i];
         dense_temp += fl[k];
         ux_temp += fl[k] * CX[k];
         uy_temp += fl[k] * CY[k];
     }
     ux_temp = (ux_temp + 0.5 * P.force_x) / dense_temp;
     uy_temp = (uy_temp + 0.5 * P.force_y) / dense_temp;
-    if (write_fields) { rho_o[i] = dense_temp; ux_o[i] = ux_temp; uy_o[i] = uy_temp; }
 
     double laplace_temp = 0.0, gradx_temp = 0.0, grady_temp = 0.0;
 #pragma unroll
     for (int k = 0; k < 9; k++) {
-        const double ph = phi[nb[k]];
+        const double ph = ph9[k];
         laplace_temp += LAP[k] * ph;
         gradx_temp += GX[k] * ph;
         grady_temp += GY[k] * ph;
@@ -772,16 +757,55 @@ LBM_HD void bs_collide_thread(const BsParams &P, const double *f, const double *
     const double omega_rho = 1.0 / tau_rho;
 #pragma unroll
     for (int k = 0; k < 9; k++) {
-        const double fo = fl[k] * (1.0 - omega_rho) + omega_rho * feqeq[k];
-        const double go = gl[k] * (1.0 - P.omega_phi) + P.omega_phi * geqeq[k];
+        fl[k] = fl[k] * (1.0 - omega_rho) + omega_rho * feqeq[k];
+        gl[k] = gl[k] * (1.0 - P.omega_phi) + P.omega_phi * geqeq[k];
+    }
+}
+// update_bounce_back + stream folded into the push: a population sent towards a bounce-back node comes straight back
+// into the node's own opposite slot (:358-372, :617-637); nb[k] = index of the periodic neighbour in direction k
+LBM_HD void bs_push(const BsParams &P, unsigned link, const double (&fl)[9], const double (&gl)[9], const int (&nb)[9], double *f2,
+                    double *g2, long long i)
+{
+    const long long n = (long long)P.nx * P.ny;
+    const int OPP[9] = LBM2_OPP;
+#pragma unroll
+    for (int k = 0; k < 9; k++) {
         if (link & (1u << k)) {      // bit 0 (the fluid flag) sends the rest population to slot OPP[0] = 0 of the node itself
-            f2[OPP[k] * n + i] = fo;
-            g2[OPP[k] * n + i] = go;
+            f2[OPP[k] * n + i] = fl[k];
+            g2[OPP[k] * n + i] = gl[k];
         } else {
-            f2[k * n + nb[k]] = fo;
-            g2[k * n + nb[k]] = go;
+            f2[k * n + nb[k]] = fl[k];
+            g2[k * n + nb[k]] = gl[k];
         }
     }
+}
+
+// the two-kernel form: the phase field comes from bs_phase_thread's array
+LBM_HD void bs_collide_thread(const BsParams &P, const double *f, const double *g, const double *phi, const unsigned short *links,
+                              double *f2, double *g2, double *rho_o, double *ux_o, double *uy_o, long long i,
+                              bool write_fields = true)
+{
+    const unsigned link = links[i];
+    if (!(link & 1u)) return;
+    const long long n = (long long)P.nx * P.ny;
+    const int CX[9] = LBM2_CX, CY[9] = LBM2_CY;
+    const int ix = (int)((unsigned)i % (unsigned)P.nx), iy = (int)((unsigned)i / (unsigned)P.nx);   // nx*ny < 2^31 (checked at create)
+    // periodic neighbours: (iX+cx+NX)%NX, (iY+cy+NY)%NY
+    const int xs[3] = {ix == 0 ? P.nx - 1 : ix - 1, ix, ix == P.nx - 1 ? 0 : ix + 1};
+    const int ys[3] = {iy == 0 ? P.ny - 1 : iy - 1, iy, iy == P.ny - 1 ? 0 : iy + 1};
+    int nb[9];      // nx*ny < 2^31 (checked at create)
+    double fl[9], gl[9], ph9[9];
+#pragma unroll
+    for (int k = 0; k < 9; k++) {
+        nb[k] = ys[CY[k] + 1] * P.nx + xs[CX[k] + 1];
+        fl[k] = f[k * n + i];
+        gl[k] = g[k * n + i];
+        ph9[k] = phi[nb[k]];
+    }
+    double dense_temp, ux_temp, uy_temp;
+    bs_collide_node(P, fl, gl, ph9, dense_temp, ux_temp, uy_temp);
+    if (write_fields) { rho_o[i] = dense_temp; ux_o[i] = ux_temp; uy_o[i] = uy_temp; }
+    bs_push(P, link, fl, gl, nb, f2, g2, i);
 }
 
 }  // namespace lbm2
