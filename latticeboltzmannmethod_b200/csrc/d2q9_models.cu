@@ -635,7 +635,7 @@ public:
         // 0 = 32x4 tile capped at 64 registers, 8 blocks/SM (fastest measured: 2.12 ms at 8192^2); 2 = 32x16;
         // 3 = 32x8 at 64 registers (2.27 ms); 5 = 32x8 uncapped, 3 blocks/SM (2.58 ms).  A marching kernel (128 columns
         // per block walking over 64 rows, psi in a shared-memory ring -- the scheme that took the binary model from
-        // 3.94 to 3.42 ms) equalled the oracle and ran in 2.03 ms against 1.98 ms for the tile kernel: not kept.
+        // 3.94 to 3.42 ms) was bit-exact and ran in 2.03 ms against 1.98 ms for the tile kernel: not kept.
         if (cfg_.kernel_variant != 1) {
             for (int t = 0; t < nsteps; t++) {
                 const bool w = t == nsteps - 1;
