@@ -48,6 +48,9 @@ public:
         cfg.wall_gradient = p.get("phase_gradient"); cfg.rho_wall = p.get("rho_wall");
         cfg.tau_phi = p.get("tau_phi"); cfg.tau_liq = p.get("tau_liq"); cfg.tau_gas = p.get("tau_gas");
         cfg.force[0] = p.get("force_x"); cfg.force[1] = p.get("force_y"); cfg.force[2] = p.get("force_z");
+        // LBM_KERNEL_VARIANT: lbm_config.kernel_variant (default 0); e.g. 2 runs the step in place on one population array
+        // (half the population memory; one GPU only)
+        if (const char *v = std::getenv("LBM_KERNEL_VARIANT")) cfg.kernel_variant = std::atoi(v);
         const char *e = std::getenv("LBM_GPUS");
         const int ngpu = e ? std::atoi(e) : 1;
         if (ngpu < 1 || NZ / ngpu < 2) throw std::runtime_error("LBM_GPUS: need at least 2 z planes per GPU");

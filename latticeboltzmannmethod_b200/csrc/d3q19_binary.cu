@@ -516,6 +516,7 @@ public:
     }
     lbm_status slab_after_init() override
     {
+        if (aa()) return rt_.fail(LBM_EINVAL, "kernel_variant 2 / 6 (in-place streaming) is driven by lbm_init / lbm_step, not by the lbm_slab_* protocol");
         pf_ = po_;
         LBM_TRY(phase_planes(gq_[cur_], phib_[pf_], 0, g_.nz + 4));
         phi_valid_ = true;

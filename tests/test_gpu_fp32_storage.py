@@ -84,3 +84,29 @@ def test_fp32_storage_roundtrip_and_limits():
         api.Context(cfg, "f32")
     with pytest.raises(api.LbmError):                                         # D2Q9 models live in the fp64 library
         api.Context(api.shanchen_config(), "f32")
+
+
+@pytest.mark.parametrize("variant", [2, 6, 5, 0])
+def test_fp32_storage_kernel_variants_agree_bit_for_bit(variant):
+    """Within the fp32-storage build every kernel variant rounds the same values at the same stores, so the in-place
+    forms on one population array (2: one pass, 6: two passes; 4-byte asynchronous copies there) and the two-array
+    forms (5, 0) must leave exactly the state of the plain two-array kernel (1)."""
+    api = _api()
+    nx, ny, nz = 70, 37, 12
+    runs = []
+    for v in (variant, 1):
+        cfg = api.microchannel_config("quarter", nx, ny, nz)
+        cfg.kernel_variant = v
+        ctx = api.Context(cfg, "f32")
+        for name, a in zip(FIELDS, api.microchannel_initial_fields(nx, ny, nz, 5)):
+            ctx.set_field(name, a)
+        ctx.init()
+        out = []
+        for s in (1, 2, 6):
+            ctx.step(s)
+            out.append([ctx.get_field(k) for k in FIELDS] + [ctx.get_populations(0), ctx.get_populations(1)])
+        ctx.close()
+        runs.append(out)
+    for a, b in zip(*runs):
+        for x, y in zip(a, b):
+            assert np.array_equal(x, y)

@@ -176,6 +176,26 @@ def test_microchannel_checkpoint_restart(tmp_path):
         assert np.array_equal(a[k], b[k]), k
 
 
+def test_microchannel_in_place_writes_the_same_files(tmp_path):
+    """LBM_KERNEL_VARIANT=2: the drop-in QuarterChannel program on ONE population array (in-place streaming): stdout,
+    every .vts and the checkpoint (taken after an odd number of steps) byte-identical to the default run; a restart
+    from that checkpoint continues identically as well."""
+    two, one = tmp_path / "two_arrays", tmp_path / "one_array"
+    os.mkdir(two)
+    os.mkdir(one)
+    env = {"LBM_NUMTIME": "141", "LBM_CHECKPOINT": "ck"}
+    out2 = _run("microchannel_quarter", [], str(two), env=env)
+    out1 = _run("microchannel_quarter", [], str(one), env=dict(env, LBM_KERNEL_VARIANT="2"))
+    assert out1 == out2
+    files = sorted(os.listdir(two))
+    assert files == sorted(os.listdir(one)) and "ck.pop" in files
+    for f in files:
+        assert open(two / f, "rb").read() == open(one / f, "rb").read(), f
+    _run("microchannel_quarter", [], str(one), env={"LBM_NUMTIME": "201", "LBM_RESTART": "ck", "LBM_KERNEL_VARIANT": "2"})
+    _run("microchannel_quarter", [], str(two), env={"LBM_NUMTIME": "201", "LBM_RESTART": "ck"})
+    assert open(two / "phase00200.vts", "rb").read() == open(one / "phase00200.vts", "rb").read()
+
+
 def _ngpu():
     try:
         import torch
