@@ -295,7 +295,7 @@ def multi_gpu_parity(api, dist, torch, np, args, rank, world, local_rank):
         for i, w in enumerate(want):
             got = np.concatenate([p[i] for p in parts])
             ndiff += int(np.count_nonzero(~((got == w) | (np.isnan(got) & np.isnan(w)))))
-        res = {"grid": "%dx%dx%d" % (nx, ny, nz), "slabs": world, "steps": steps, "path": "lbm_comm_attach + lbm_init + lbm_step (NCCL, overlapped)",
+        res = {"grid": "%dx%dx%d" % (nx, ny, nz), "slabs": world, "steps": steps, "path": "lbm_comm_attach + lbm_init + lbm_step (NCCL%s)" % (", five directions per face after every in-place sub-step" if args.variant in (2, 6) else ", overlapped"),
                "compared": "rho, phase, ux, uy, uz, f, g against one slab on one GPU", "values": int(sum(w.size for w in want)),
                "ndiff": ndiff, "phase_fallbacks": fb}
     flag = torch.tensor([0 if res is None else res["ndiff"]], dtype=torch.int64, device="cuda")

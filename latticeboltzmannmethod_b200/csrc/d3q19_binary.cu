@@ -21,6 +21,7 @@ namespace {
 using lbm3::FieldsOut;
 using lbm3::k_aa_collide;
 using lbm3::k_aa_core;
+using lbm3::k_aa_merge;
 using lbm3::k_aa_one;
 using lbm3::k_aa_phase;
 using lbm3::k_aa_repair;
@@ -248,14 +249,13 @@ public:
             return rt_.fail(LBM_EINVAL, "bad slab_rank/slab_count");
         if (cfg_.kernel_variant != 0 && cfg_.kernel_variant != 1 && cfg_.kernel_variant != 5 && !aa())
             return rt_.fail(LBM_EINVAL, "D3Q19: kernel_variant must be 0 (one-pass), 5 (two-pass, interior + rim), 1 (two-pass, plain), 2 (in place on one array, one pass) or 6 (in place, two passes)");
-        if (aa() && cfg_.slab_count != 1)
-            return rt_.fail(LBM_EINVAL, "D3Q19 kernel_variant 2 / 6 (in-place streaming) runs on one slab per context: use slab_count 1");
         // solver.hpp:25-30
         const int zstep = cfg_.nz / cfg_.slab_count;
         z_begin_ = cfg_.slab_rank * zstep;
         int z_end = z_begin_ + zstep - 1;
         if (cfg_.slab_rank == cfg_.slab_count - 1) z_end = cfg_.nz - 1;
         g_.nx = cfg_.nx; g_.ny = cfg_.ny; g_.nz = z_end - z_begin_ + 1;
+        g_.zwrap = cfg_.slab_count == 1;   // in-place kernels: z periodic by addressing / ghost planes filled by aa_exchange
         if (g_.nz < 2) return rt_.fail(LBM_EINVAL, "D3Q19: every slab needs at least 2 z planes");
         g_.pl = ((long long)g_.nx * g_.ny + 15) / 16 * 16;
         P_.aconst = cfg_.aconst; P_.kconst = cfg_.kconst; P_.gammaconst = cfg_.gammaconst;
@@ -428,18 +428,74 @@ public:
 
     // ---- in-place streaming (kernel_variant 2) ----
     dim3 owned_grid(int threads) const { return dim3((unsigned)(((long long)g_.nx * g_.ny + threads - 1) / threads), g_.nz); }
-    // phase field of the owned planes out of either half of the cycle, then its two ghost planes (z periodic)
-    lbm_status aa_phase()
+    // phase field out of either half of the cycle -- of all owned planes, or of the first and the last one only --
+    // then its two ghost planes (copies inside one slab, the neighbours' planes between slabs)
+    lbm_status aa_phase(bool ends_only = false)
     {
+        const dim3 grid = ends_only ? dim3(owned_grid(kThreads).x, 2) : owned_grid(kThreads);
+        const int zstep = ends_only ? g_.nz - 1 : 1;
         rt_.about_to_launch();
-        if (aa_odd_) k_aa_phase<true><<<owned_grid(kThreads), kThreads, 0, rt_.stream>>>(g_, P_, gq_[0], phib_[0]);
-        else k_aa_phase<false><<<owned_grid(kThreads), kThreads, 0, rt_.stream>>>(g_, P_, gq_[0], phib_[0]);
+        if (aa_odd_) k_aa_phase<true><<<grid, kThreads, 0, rt_.stream>>>(g_, P_, gq_[0], phib_[0], 2, zstep);
+        else k_aa_phase<false><<<grid, kThreads, 0, rt_.stream>>>(g_, P_, gq_[0], phib_[0], 2, zstep);
         LBM_TRY(rt_.launched("k_aa_phase"));
         return exchange(true);
+    }
+    // Halo exchange of the in-place step between slabs: only the five directions that cross a z face travel, a quarter
+    // of what the two-array step sends.  After an even step (the array holds post-collision values in the opposite
+    // slots) the slots with c_z = -1 of the top owned plane go to the upper neighbour's ghost plane below its slab and
+    // the slots with c_z = +1 of the bottom owned plane to the lower neighbour's ghost plane above: the places its odd
+    // step loads from.  After an odd step the same places hold what this slab pushed across the face and travel on to
+    // the neighbour's first / last owned plane -- through the unused rows of its ghost planes, from where k_aa_merge
+    // moves them into the owned plane except where a slot holds the node's own bounced-back population (a wall next
+    // to the z face: that place is written by the node itself, not from across the face).  Slot numbers and in-plane
+    // positions are the same on both sides (the folded push never changes c_z).  Directions with c_z = -1 are 6, 13, 14,
+    // 17, 18; c_z = +1: 5, 11, 12, 15, 16.
+    lbm_status aa_exchange(bool after_even)
+    {
+        if (cfg_.slab_count == 1) return LBM_OK;
+        LBM_TRY(need_comm());
+        NcclApi *api = nccl_api(&rt_.err);
+        if (!api) return LBM_ENCCL;
+        static const int kDown[3][2] = {{6, 1}, {13, 2}, {17, 2}}, kUp[3][2] = {{5, 1}, {11, 2}, {15, 2}};   // first slot, count
+        const int up = (cfg_.slab_rank + 1) % cfg_.slab_count, down = (cfg_.slab_rank - 1 + cfg_.slab_count) % cfg_.slab_count;
+        const int dtype = sizeof(pop_t) == sizeof(double) ? kNcclFloat64 : kNcclFloat32;
+        const size_t pl = (size_t)g_.pl;
+        const int nz = g_.nz;
+        auto at = [&](pop_t *arr, int zs, int k) { return arr + ((size_t)zs * 19 + k) * pl; };
+        // planes: what goes to the upper / lower neighbour and where its counterpart from below / above arrives
+        const int s_up = after_even ? nz + 1 : nz + 2, s_down = after_even ? 2 : 1;
+        const int r_below = 1, r_above = nz + 2;      // after an odd step: the rows of the ghost planes no place of this slab uses
+        // to the upper neighbour: after an even step my c_z = -1 slots (it loads them as its plane below), after an odd
+        // step the c_z = +1 slots of my ghost plane above (what I pushed up); the lower neighbour mirrors that
+        const int(*to_up)[2] = after_even ? kDown : kUp, (*to_down)[2] = after_even ? kUp : kDown;
+        int rc = api->GroupStart();
+        pop_t *arrs[2] = {f_[0], gq_[0]};
+        for (pop_t *arr : arrs)
+            for (int i = 0; i < 3 && rc == 0; i++) rc = api->Send(at(arr, s_up, to_up[i][0]), to_up[i][1] * pl, dtype, up, comm_, rt_.stream);
+        for (pop_t *arr : arrs)
+            for (int i = 0; i < 3 && rc == 0; i++) rc = api->Send(at(arr, s_down, to_down[i][0]), to_down[i][1] * pl, dtype, down, comm_, rt_.stream);
+        // receives in the order the peer sends: from below comes what the lower neighbour sent up, from above what the
+        // upper one sent down (with two slabs both are the same peer: NCCL matches a pair's messages in order)
+        for (pop_t *arr : arrs)
+            for (int i = 0; i < 3 && rc == 0; i++) rc = api->Recv(at(arr, r_below, to_up[i][0]), to_up[i][1] * pl, dtype, down, comm_, rt_.stream);
+        for (pop_t *arr : arrs)
+            for (int i = 0; i < 3 && rc == 0; i++) rc = api->Recv(at(arr, r_above, to_down[i][0]), to_down[i][1] * pl, dtype, up, comm_, rt_.stream);
+        const int rc2 = api->GroupEnd();
+        if (rc == 0) rc = rc2;
+        if (rc != 0) return rt_.fail(LBM_ENCCL, std::string("NCCL halo exchange (in-place step): ") + (api->GetErrorString ? api->GetErrorString(rc) : "error"));
+        if (!after_even) {
+            rt_.about_to_launch();
+            k_aa_merge<<<owned_grid(kThreads).x, kThreads, 0, rt_.stream>>>(g_, f_[0], gq_[0]);
+            LBM_TRY(rt_.launched("k_aa_merge"));
+        }
+        return LBM_OK;
     }
     // one pass (d3q19_inplace.cuh): phase parts run L plane-steps ahead of the collisions of the same launch
     lbm_status aa_step_one(int write_fields)
     {
+        // between slabs the collision of the first and the last plane needs the neighbours' phase field: those two
+        // planes are summed ahead of the launch and exchanged (the launch sums them again: same values)
+        if (cfg_.slab_count > 1) LBM_TRY(aa_phase(true));
         lbm3::AaPlan A{};
         A.sb = sb_; A.nstrips = nstrips_; A.L = lag_ + 1; A.dshift = dshift_; A.nblk = nblk_;
         A.pz = g_.nz + A.L;
@@ -465,6 +521,7 @@ public:
             else k_aa_repair<FXY, WR, false><<<sms_ * 3, 128, 0, rt_.stream>>>(g_, P_, f_[0], gq_[0], phib_[0], o, ctrl_, skipped, sticky, nblk_);
         });
         LBM_TRY(rt_.launched("k_aa_repair"));
+        LBM_TRY(aa_exchange(!aa_odd_));
         aa_odd_ = !aa_odd_;
         return LBM_OK;
     }
@@ -487,19 +544,34 @@ public:
             }
         });
         LBM_TRY(rt_.launched(coll() == 0 ? "k_aa_core" : "k_aa_collide"));
+        LBM_TRY(aa_exchange(!aa_odd_));
         aa_odd_ = !aa_odd_;
         return LBM_OK;
     }
     // everything that reads or writes populations from outside a step wants the streamed populations: after an odd
     // number of steps the pairs of places swap contents once (in place; the next step is then an even one again)
+    // Between slabs the swap is local as well (the partner places in the ghost planes hold the neighbours' values since
+    // the exchange after the even step), but the slabs have to stay in the same half of the cycle: readers swap, read and
+    // swap back (aa_denormalize), and populations can only be loaded in the even half.
+    lbm_status aa_swap()
+    {
+        rt_.about_to_launch();
+        k_aa_swap<<<owned_grid(kThreads), kThreads, 0, rt_.stream>>>(g_, f_[0], gq_[0]);
+        return rt_.launched("k_aa_swap");
+    }
     lbm_status aa_normalize()
     {
         if (!aa_odd_) return LBM_OK;
-        rt_.about_to_launch();
-        k_aa_swap<<<owned_grid(kThreads), kThreads, 0, rt_.stream>>>(g_, f_[0], gq_[0]);
-        LBM_TRY(rt_.launched("k_aa_swap"));
-        aa_odd_ = false;
+        LBM_TRY(aa_swap());
+        if (cfg_.slab_count == 1) aa_odd_ = false;
+        else aa_swapped_for_read_ = true;
         return LBM_OK;
+    }
+    lbm_status aa_denormalize()
+    {
+        if (!aa_swapped_for_read_) return LBM_OK;
+        aa_swapped_for_read_ = false;
+        return aa_swap();
     }
 
     // ---- slab phases ----
@@ -907,6 +979,8 @@ public:
     lbm_status set_populations(int set, const double *host) override
     {
         LBM_TRY(need_comm());
+        if (aa() && aa_odd_ && cfg_.slab_count > 1)
+            return rt_.fail(LBM_ESTATE, "in-place streaming on several slabs: populations can be loaded after lbm_init or an even number of steps only");
         LBM_TRY(ensure_stage());
         LBM_TRY(aa_normalize());
         const size_t per_plane = (size_t)g_.nx * g_.ny * 19;
@@ -938,6 +1012,7 @@ public:
             LBM_TRY(rt_.launched("k_gather_aos"));
             LBM_CUDA(rt_, cudaMemcpyAsync(host + per_plane * z0, stage_, per_plane * n * sizeof(double), cudaMemcpyDeviceToHost, rt_.stream));
         }
+        LBM_TRY(aa_denormalize());
         LBM_CUDA(rt_, cudaStreamSynchronize(rt_.stream));
         return LBM_OK;
     }
@@ -954,6 +1029,7 @@ public:
         L.planes = g_.nz; L.nx = g_.nx; L.ny = g_.ny; L.q = 19; L.skip_border = 1; L.node_major_x = 1;
         double out[6];
         LBM_TRY(run_diagnostics(rt_, L, diag_, diagnostics_scratch_blocks(), out));
+        LBM_TRY(aa_denormalize());
         if (mass) *mass = out[0];
         if (mom) { mom[0] = out[1]; mom[1] = out[2]; mom[2] = out[3]; }
         if (phase_mass) *phase_mass = out[4];
@@ -973,7 +1049,8 @@ private:
     double *phib_[2] = {nullptr, nullptr};
     int pf_ = 0, po_ = 0;
     bool phi_valid_ = false, lag_pending_ = false;
-    bool aa_odd_ = false;   // kernel_variant 2: the array holds post-collision values in the opposite slots (odd half of the cycle)
+    bool aa_odd_ = false;   // kernel_variant 2 / 6: the array holds post-collision values in the opposite slots (odd half of the cycle)
+    bool aa_swapped_for_read_ = false;   // ... and is swapped into streamed order for the duration of a read (several slabs)
     cudaGraphExec_t graph_exec_[8] = {};   // one replayable pair of steps per (cur_, pf_, po_)
     unsigned long long graph_launches_[8] = {};
     bool graphs_off_ = false;

@@ -17,19 +17,22 @@
 
 namespace lbm3 {
 
+// one slab holding the whole grid: z periodic by addressing; a slab of several: the ghost planes 1 and nz+2, which the
+// halo exchange of the in-place step fills and empties (Slab3D::aa_exchange)
 __device__ __forceinline__ AaPlanes aa_planes(const Geom &g, int zs)
 {
     const long long pp = 19 * g.pl;
-    const int zm = zs == 2 ? g.nz + 1 : zs - 1, zp = zs == g.nz + 1 ? 2 : zs + 1;
+    const int zm = g.zwrap && zs == 2 ? g.nz + 1 : zs - 1, zp = g.zwrap && zs == g.nz + 1 ? 2 : zs + 1;
     return AaPlanes{zm * pp, zs * pp, zp * pp};
 }
 
+// planes zs0, zs0 + zstep, ... (blockIdx.y): all owned planes (2, 1), or just the first and the last one (2, nz - 1)
 template <bool ODD>
-__global__ void __launch_bounds__(256) k_aa_phase(Geom g, Params P, const pop_t *gq, double *phi)
+__global__ void __launch_bounds__(256) k_aa_phase(Geom g, Params P, const pop_t *gq, double *phi, int zs0, int zstep)
 {
     const unsigned idx = blockIdx.x * 256 + threadIdx.x;
     if (idx >= (unsigned)(g.nx * g.ny)) return;
-    const int zs = 2 + blockIdx.y;
+    const int zs = zs0 + (int)blockIdx.y * zstep;
     aa_phase_thread<ODD>(g, P, gq, phi, zs, aa_planes(g, zs), (int)(idx % (unsigned)g.nx), (int)(idx / (unsigned)g.nx));
 }
 
@@ -50,7 +53,34 @@ __global__ void __launch_bounds__(256) k_aa_swap(Geom g, pop_t *f, pop_t *gq)
     const unsigned idx = blockIdx.x * 256 + threadIdx.x;
     if (idx >= (unsigned)(g.nx * g.ny)) return;
     const int zs = 2 + blockIdx.y;
-    aa_swap_thread(g, f, gq, aa_planes(g, zs), (int)(idx % (unsigned)g.nx), (int)(idx / (unsigned)g.nx));
+    aa_swap_thread(g, f, gq, aa_planes(g, zs), (int)(idx % (unsigned)g.nx), (int)(idx / (unsigned)g.nx), !g.zwrap && zs == 2,
+                   !g.zwrap && zs == g.nz + 1);
+}
+
+// Second half of the halo exchange after an odd step (Slab3D::aa_exchange): what the neighbours pushed across the two z
+// faces has arrived in the unused rows of the ghost planes (c_z = +1 rows of plane 1, c_z = -1 rows of plane nz+2) and
+// goes into the first / last owned plane -- except where the slot holds the node's own bounced-back population.
+__global__ void __launch_bounds__(256) k_aa_merge(Geom g, pop_t *f, pop_t *gq)
+{
+    const unsigned idx = blockIdx.x * 256 + threadIdx.x;
+    if (idx >= (unsigned)(g.nx * g.ny)) return;
+    const int ix = (int)(idx % (unsigned)g.nx), iy = (int)(idx / (unsigned)g.nx);
+    if (ix < 1 || ix > g.nx - 2 || iy < 1 || iy > g.ny - 2) return;
+    constexpr int UP[5] = {5, 11, 12, 15, 16}, DOWN[5] = {6, 13, 14, 17, 18};
+    const size_t pl = (size_t)g.pl;
+#pragma unroll
+    for (int i = 0; i < 5; i++) {
+        if (aa_crossed_face(g, UP[i], ix, iy)) {          // from below into the first owned plane
+            const size_t src = ((size_t)1 * 19 + UP[i]) * pl + idx, dst = ((size_t)2 * 19 + UP[i]) * pl + idx;
+            f[dst] = f[src];
+            gq[dst] = gq[src];
+        }
+        if (aa_crossed_face(g, DOWN[i], ix, iy)) {        // from above into the last owned plane
+            const size_t src = ((size_t)(g.nz + 2) * 19 + DOWN[i]) * pl + idx, dst = ((size_t)(g.nz + 1) * 19 + DOWN[i]) * pl + idx;
+            f[dst] = f[src];
+            gq[dst] = gq[src];
+        }
+    }
 }
 
 // ---- the BGK step in place with the collision in its streamed form (collide_streamed, as in k_step_one) ----
@@ -173,8 +203,10 @@ __global__ void __launch_bounds__(128, 4) k_aa_core(Geom g, Params P, pop_t *f, 
 //     plane-steps t-L .. t-L+2 are (strip s and, for the first segments, strip s-1: counters as in k_step_one, one
 //     release-add per block, relaxed polls), and whose g values are mostly still in L2 (674 B of DRAM traffic per
 //     lattice update measured at 512^3, 624 if none had left it; the two-pass form moves 780).
-// Plane sequence: nz-1, 0, 1, .., nz-2 for the phase parts (the plane below plane 0 first: z is periodic) and
-// 0 .. nz-1 for the collisions.  The phase part of plane 0 / nz-1 also writes the ghost plane above / below.
+// Plane sequence, one slab holding the whole grid: nz-1, 0, 1, .., nz-2 for the phase parts (the plane below plane 0
+// first: z is periodic) and 0 .. nz-1 for the collisions; the phase part of plane 0 / nz-1 also writes the ghost plane
+// above / below.  A slab of several: 0 .. nz-1 for both; the phase field of the two ghost planes is there before the
+// launch (the neighbours' first / last plane, summed by k_aa_phase and exchanged).
 // A warp whose counters are not full after a bounded wait does NOT collide: it records itself in `skipped`
 // (one word per 128-node segment of an owned plane, one bit per warp) and raises flags[0]; k_aa_repair then collides
 // those segments from the finished phase field.  In place that is all a repair takes -- a node's collision touches
@@ -210,9 +242,10 @@ k_aa_one(Geom g, Params P, pop_t *f, pop_t *gq, double *phi, FieldsOut o, unsign
     unsigned seen = A.full;
     const unsigned *cnt = done;
     if (c_step && lane < 6) {
-        const int q = (c + lane % 3) % nz, sdep = strip - lane / 3;
-        need = sdep >= 0 && (lane < 3 || (int)blockIdx.x < 2 * A.dshift);
-        cnt = done + (size_t)(sdep * nz + q) * LAG_PAD;
+        // plane-step at which the phase field of plane c - 1 + j was summed
+        const int q = g.zwrap ? (c + lane % 3) % nz : c - 1 + lane % 3, sdep = strip - lane / 3;
+        need = sdep >= 0 && q >= 0 && q < nz && (lane < 3 || (int)blockIdx.x < 2 * A.dshift);
+        cnt = done + (size_t)(sdep * nz + (need ? q : 0)) * LAG_PAD;
         if (need) seen = lag_ld_relaxed(cnt);
     }
 
@@ -239,7 +272,7 @@ k_aa_one(Geom g, Params P, pop_t *f, pop_t *gq, double *phi, FieldsOut o, unsign
     // ---- phase part, requests: the g values of plane-sequence element t (nothing in this launch has touched these
     // places yet) into this thread's second column; summed at the very end of the block, when they have long arrived
     const int pidx = bbase + (int)threadIdx.x;
-    const int pz = t == 0 ? nz - 1 : t - 1;
+    const int pz = g.zwrap ? (t == 0 ? nz - 1 : t - 1) : t;
     int px = 0, py = 0;
     bool do_p = t < nz && pidx < nplane;
     if (do_p) {
@@ -284,8 +317,8 @@ k_aa_one(Geom g, Params P, pop_t *f, pop_t *gq, double *phi, FieldsOut o, unsign
 #pragma unroll
         for (int k = 0; k < 19; k++) G2[k] = (double)ps[k * 128];
         phase_node(g, P, G2, phi, pz + 2, px, py);
-        if (pz == 0) phase_node(g, P, G2, phi, nz + 2, px, py);       // ghost plane above the slab
-        if (pz == nz - 1) phase_node(g, P, G2, phi, 1, px, py);       // ghost plane below
+        if (g.zwrap && pz == 0) phase_node(g, P, G2, phi, nz + 2, px, py);       // ghost plane above the slab
+        if (g.zwrap && pz == nz - 1) phase_node(g, P, G2, phi, 1, px, py);       // ghost plane below
     }
 
     // publish the end of this block's phase part: one release-add per block, after a block barrier

@@ -28,6 +28,8 @@ namespace lbm3 {
 
 struct Geom {
     int nx, ny, nz;        // local slab: nz owned planes
+    int zwrap;             // in-place kernels only: 1 = the slab is the whole grid, z is periodic by addressing; 0 = the
+                           // planes below / above the slab are ghost planes filled by the halo exchange
     long long pl;          // plane pitch in doubles (>= nx*ny, multiple of 16)
 };
 
@@ -435,17 +437,32 @@ LBM_HD void aa_collide_thread(const Geom &g, const Params &P, pop_t *f, pop_t *g
     });
 }
 
+// Between slabs: after an odd step the value in slot k (c_z != 0) of bulk node (ix, iy) of a slab's first or last plane
+// has come across the z face -- pushed there by the neighbouring slab, straight or off a mirror line -- unless the
+// in-plane position it would have come from is a wall node: then it is the node's own population, bounced back, and
+// the halo exchange must leave it alone.
+LBM_HD bool aa_crossed_face(const Geom &g, int k, int ix, int iy)
+{
+    const int CX[19] = LBM3_CX, CY[19] = LBM3_CY;
+    return !((CX[k] == -1 && ix == g.nx - 2) || (CY[k] == -1 && iy == g.ny - 2));
+}
+
 // Turns an array of the odd half (post-collision values in the opposite slots) into the streamed populations and
 // back, in place: the streamed value of (x, k) sits at loc(x, opp(k)), and loc(., opp(.)) is an involution on the
 // places, so the two places of every pair swap contents.  The thread of the lower address does the swap.
-LBM_HD void aa_swap_thread(const Geom &g, pop_t *f, pop_t *gq, const AaPlanes &z, int ix, int iy)
+// `ghost_below` / `ghost_above`: the plane below / above is a ghost plane of a slab (its places have no thread of their
+// own in this launch), so this thread swaps with them whatever the addresses.
+LBM_HD void aa_swap_thread(const Geom &g, pop_t *f, pop_t *gq, const AaPlanes &z, int ix, int iy, bool ghost_below = false,
+                           bool ghost_above = false)
 {
     if (ix < 1 || ix > g.nx - 2 || iy < 1 || iy > g.ny - 2) return;
+    const long long pp = 19 * g.pl;
     aa_each([&](auto m) {
         constexpr int M = decltype(m)::value;
         const long long own = aa_slot<false, M>(g, z, ix, iy);   // (x, opp(M))
         const long long other = aa_slot<true, M>(g, z, ix, iy);  // loc(x, M): holds the streamed value of (x, opp(M))
-        if (own < other) {
+        const bool in_ghost = (ghost_below && other >= z.zm && other < z.zm + pp) || (ghost_above && other >= z.zp && other < z.zp + pp);
+        if (own < other || in_ghost) {
             const pop_t a = f[own], b = f[other];
             f[own] = b; f[other] = a;
             const pop_t c = gq[own], d = gq[other];

@@ -24,7 +24,7 @@ extern "C" {
 Emu *emu3_create(int nx, int ny, int nz, const double *p)
 {
     Emu *e = new Emu;
-    e->g.nx = nx; e->g.ny = ny; e->g.nz = nz;
+    e->g.nx = nx; e->g.ny = ny; e->g.nz = nz; e->g.zwrap = 1;
     e->g.pl = ((long long)nx * ny + 15) / 16 * 16;
     e->P.aconst = p[0]; e->P.kconst = p[1]; e->P.gammaconst = p[2]; e->P.phase_gradient = p[3];
     e->P.rho_wall = p[5]; e->P.omega_phi = 1.0 / p[6]; e->P.tau_gas = p[8]; e->P.dtau = p[7] - p[8];
@@ -223,4 +223,124 @@ void emu3_set_pops(Emu *e, const double *f, const double *g)
             }
     self_exchange(e, e->cur);
 }
+}
+
+// ---- the in-place step on several slabs, emulated: the halo protocol of Slab3D::aa_exchange with memcpy as transport ----
+// Splits the (initialised, even-half) state of `whole` into `nslabs` slabs, runs `steps` in-place steps on both, and
+// returns the number of population values (streamed order) that differ between the slabs and the whole grid.
+namespace {
+struct SlabEmu {
+    Geom g;
+    std::vector<double> f, gq, phi;
+    int z0;
+};
+void copy_rows(std::vector<double> &dst, int zd, const std::vector<double> &src, int zs, const Geom &g, bool down_set, bool merge = false)
+{
+    static const int kDown[5] = {6, 13, 14, 17, 18}, kUp[5] = {5, 11, 12, 15, 16};
+    const int *ks = down_set ? kDown : kUp;
+    for (int i = 0; i < 5; i++) {
+        if (!merge) {
+            memcpy(&dst[((size_t)zd * 19 + ks[i]) * g.pl], &src[((size_t)zs * 19 + ks[i]) * g.pl], g.pl * sizeof(double));
+            continue;
+        }
+        for (int iy = 1; iy < g.ny - 1; iy++)     // what the CUDA library does with k_aa_merge
+            for (int ix = 1; ix < g.nx - 1; ix++)
+                if (aa_crossed_face(g, ks[i], ix, iy))
+                    dst[((size_t)zd * 19 + ks[i]) * g.pl + (size_t)iy * g.nx + ix] = src[((size_t)zs * 19 + ks[i]) * g.pl + (size_t)iy * g.nx + ix];
+    }
+}
+template <bool ODD>
+void slab_step(std::vector<SlabEmu> &S, const Params &P, bool fxy)
+{
+    const int n = (int)S.size();
+    for (auto &s : S)
+        for (int zs = 2; zs < s.g.nz + 2; zs++)
+            for (int iy = 0; iy < s.g.ny; iy++)
+                for (int ix = 0; ix < s.g.nx; ix++) {
+                    const long long pp = 19 * s.g.pl;
+                    aa_phase_thread<ODD>(s.g, P, s.gq.data(), s.phi.data(), zs, AaPlanes{(zs - 1) * pp, zs * pp, (zs + 1) * pp}, ix, iy);
+                }
+    for (int r = 0; r < n; r++) {      // phase ghost planes from the ring neighbours
+        SlabEmu &s = S[r], &up = S[(r + 1) % n], &dn = S[(r + n - 1) % n];
+        memcpy(&s.phi[1 * s.g.pl], &dn.phi[(size_t)(dn.g.nz + 1) * s.g.pl], s.g.pl * sizeof(double));
+        memcpy(&s.phi[(size_t)(s.g.nz + 2) * s.g.pl], &up.phi[2 * s.g.pl], s.g.pl * sizeof(double));
+    }
+    FieldsOut o{nullptr, nullptr, nullptr, nullptr};
+    for (auto &s : S)
+        for (int zs = 2; zs < s.g.nz + 2; zs++)
+            for (int iy = 0; iy < s.g.ny; iy++)
+                for (int ix = 0; ix < s.g.nx; ix++) {
+                    const long long pp = 19 * s.g.pl;
+                    const AaPlanes z{(zs - 1) * pp, zs * pp, (zs + 1) * pp};
+                    if (fxy) aa_collide_thread<true, false, 0, ODD>(s.g, P, s.f.data(), s.gq.data(), s.phi.data(), o, zs, z, ix, iy);
+                    else aa_collide_thread<false, false, 0, ODD>(s.g, P, s.f.data(), s.gq.data(), s.phi.data(), o, zs, z, ix, iy);
+                }
+    // population halos.  Snapshot semantics: every slab's outgoing rows are read before anybody's incoming rows land
+    std::vector<SlabEmu> T = S;
+    for (int r = 0; r < n; r++) {
+        SlabEmu &s = S[r];
+        const SlabEmu &up = T[(r + 1) % n], &dn = T[(r + n - 1) % n];
+        const int nz = s.g.nz;
+        for (int a = 0; a < 2; a++) {
+            std::vector<double> &mine = a ? s.gq : s.f;
+            const std::vector<double> &fu = a ? up.gq : up.f, &fd = a ? dn.gq : dn.f;
+            if (!ODD) {   // after an even step: neighbours' boundary planes into my ghost planes
+                copy_rows(mine, 1, fd, dn.g.nz + 1, s.g, true);        // lower neighbour's top plane, c_z = -1 slots
+                copy_rows(mine, nz + 2, fu, 2, s.g, false);            // upper neighbour's bottom plane, c_z = +1 slots
+            } else {      // after an odd step: neighbours' ghost planes into my boundary planes
+                copy_rows(mine, 2, fd, dn.g.nz + 2, s.g, false, true);       // what the lower neighbour pushed up
+                copy_rows(mine, nz + 1, fu, 1, s.g, true, true);             // what the upper neighbour pushed down
+            }
+        }
+    }
+}
+}  // namespace
+extern "C" long long emu3_aa_slabs_vs_whole(Emu *whole, int nslabs, int steps)
+{
+    const Geom &G = whole->g;
+    const size_t pp = 19 * (size_t)G.pl;
+    std::vector<SlabEmu> S(nslabs);
+    const int zstep = G.nz / nslabs;
+    for (int r = 0; r < nslabs; r++) {
+        SlabEmu &s = S[r];
+        s.z0 = r * zstep;
+        s.g = G;
+        s.g.nz = r == nslabs - 1 ? G.nz - s.z0 : zstep;
+        s.g.zwrap = 0;
+        s.f.assign((size_t)(s.g.nz + 4) * pp, 0.0);
+        s.gq.assign((size_t)(s.g.nz + 4) * pp, 0.0);
+        s.phi.assign((size_t)(s.g.nz + 4) * G.pl, 0.0);
+        memcpy(&s.f[2 * pp], &whole->f[whole->cur][(size_t)(s.z0 + 2) * pp], (size_t)s.g.nz * pp * sizeof(double));
+        memcpy(&s.gq[2 * pp], &whole->gq[whole->cur][(size_t)(s.z0 + 2) * pp], (size_t)s.g.nz * pp * sizeof(double));
+    }
+    whole->streamed = 4;
+    bool odd = false;
+    for (int t = 0; t < steps; t++) {
+        if (odd) slab_step<true>(S, whole->P, whole->fxy);
+        else slab_step<false>(S, whole->P, whole->fxy);
+        odd = !odd;
+    }
+    emu3_step(whole, steps);
+    // streamed order on both sides
+    aa_normalize(whole);
+    if (odd)
+        for (auto &s : S)
+            for (int zs = 2; zs < s.g.nz + 2; zs++)
+                for (int iy = 0; iy < G.ny; iy++)
+                    for (int ix = 0; ix < G.nx; ix++) {
+                        const long long q = 19 * s.g.pl;
+                        aa_swap_thread(s.g, s.f.data(), s.gq.data(), AaPlanes{(zs - 1) * q, zs * q, (zs + 1) * q}, ix, iy, zs == 2, zs == s.g.nz + 1);
+                    }
+    long long bad = 0;
+    for (auto &s : S)
+        for (int z = 0; z < s.g.nz; z++)
+            for (int k = 0; k < 19; k++)
+                for (int iy = 1; iy < G.ny - 1; iy++)
+                    for (int ix = 1; ix < G.nx - 1; ix++) {
+                        const size_t a = ((size_t)(z + 2) * 19 + k) * G.pl + (size_t)iy * G.nx + ix;
+                        const size_t b = ((size_t)(s.z0 + z + 2) * 19 + k) * G.pl + (size_t)iy * G.nx + ix;
+                        bad += s.f[a] != whole->f[whole->cur][b];
+                        bad += s.gq[a] != whole->gq[whole->cur][b];
+                    }
+    return bad;
 }

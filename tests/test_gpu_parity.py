@@ -162,16 +162,6 @@ def test_d3q19_in_place_streaming_halves_the_population_memory_and_survives_outs
     b.close()
 
 
-def test_d3q19_in_place_streaming_refuses_more_than_one_slab():
-    api = _api()
-    cfg = api.microchannel_config("quarter", 12, 10, 8)
-    cfg.kernel_variant = 2
-    cfg.slab_count, cfg.slab_rank = 2, 0
-    with pytest.raises(Exception) as e:
-        api.Context(cfg)
-    assert "slab" in str(e.value)
-
-
 @pytest.mark.parametrize("variant", [0, 5, 1, 2, 6])
 def test_d3q19_quarterchannel_golden(variant):
     """The reference's own QuarterChannel run, all 1001 steps, against values dumped from the unmodified reference."""

@@ -79,6 +79,23 @@ def test_d3q19_threads_match_oracle(emu_libs, shape, params, width, steps, rand,
     o.close()
 
 
+@pytest.mark.parametrize("nslabs", [1, 2, 3])
+@pytest.mark.parametrize("steps", [1, 2, 3, 6])
+def test_d3q19_in_place_slab_protocol_matches_one_slab(emu_libs, nslabs, steps):
+    """The halo protocol of the in-place step between slabs (Slab3D::aa_exchange + k_aa_merge: five directions per face,
+    ghost rows after even steps, masked merge into the owned planes after odd ones, ghost-aware swap for reading in the
+    odd half), emulated with memcpy as the transport, against the same steps on one periodic slab."""
+    L = _emu3(emu_libs["d3q19"])
+    L.emu3_aa_slabs_vs_whole.restype = C.c_longlong
+    L.emu3_aa_slabs_vs_whole.argtypes = [C.c_void_p, C.c_int, C.c_int]
+    nx, ny, nz = 12, 10, 9
+    e = L.emu3_create(nx, ny, nz, _p(np.asarray(GENERAL, dtype=np.float64)))
+    L.emu3_set_fields(e, *[_p(a) for a in _fields(nx, ny, nz, 3, True)])
+    L.emu3_init(e)
+    assert L.emu3_aa_slabs_vs_whole(e, nslabs, steps) == 0
+    L.emu3_destroy(e)
+
+
 def _emu2(path):
     L = C.CDLL(path)
     L.emusc_create.restype = C.c_void_p
