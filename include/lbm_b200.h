@@ -89,9 +89,11 @@ typedef struct {
                                   step, 5 two-pass (phase kernel + collide kernels), 1 two-pass with the plain
                                   whole-plane kernel, 2 and 6 in-place (AA-pattern) streaming on ONE population array --
                                   half the population memory (replaces the second array and exchangeMatrices,
-                                  lattice.hpp:842-855), one slab per context (slab_count 1), driven by lbm_step only;
-                                  2 one pass (the phase field runs ahead of the collision inside one launch), 6 two
-                                  passes; Shan-Chen 1 = density pass + collide, 2/3/5 = other tiles of the
+                                  lattice.hpp:842-855); 2 one pass (the phase field runs ahead of the collision inside
+                                  one launch), 6 two passes; on several slabs only the five z-crossing directions travel
+                                  (NCCL inside lbm_step after lbm_comm_attach; the lbm_slab_* protocol is for the
+                                  two-array forms), and populations can be loaded after lbm_init or an even number of
+                                  steps only; Shan-Chen 1 = density pass + collide, 2/3/5 = other tiles of the
                                   fused kernel; binary D2Q9 0 = marching kernel (one pass, the phase field in a shared-memory ring),
                                   6 / 1 = phase pass + collide with 128- / 256-thread blocks, 2-4 = fused tile kernel,
                                   5 = one-pass step in the manner of the D3Q19 default (slower here); MRT 0 = in-place AA-pattern streaming on ONE population array, 1 = two arrays with push

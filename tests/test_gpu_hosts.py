@@ -224,6 +224,13 @@ def test_microchannel_on_several_gpus_writes_the_same_files(gpus, tmp_path):
     assert files == sorted(os.listdir(many)) and "phase00200.vts" in files and "ck.pop" in files
     for f in files:
         assert open(one / f, "rb").read() == open(many / f, "rb").read(), f
+    # the same on ONE population array per GPU (in-place streaming, five directions per face in the halo messages)
+    inplace = tmp_path / "inplace"
+    os.mkdir(inplace)
+    outi = _run("microchannel_quarter", [], str(inplace), env=dict(env, LBM_GPUS=str(gpus), LBM_KERNEL_VARIANT="2"))
+    assert outi == out1
+    for f in files:
+        assert open(one / f, "rb").read() == open(inplace / f, "rb").read(), ("in place", f)
     # continue the N-GPU checkpoint on one GPU and the other way round: same files again
     for src, dst, g in ((many, one, "1"), (one, many, str(gpus))):
         _run("microchannel_quarter", [], str(dst), env={"LBM_NUMTIME": "301", "LBM_RESTART": str(src / "ck"), "LBM_GPUS": g})
