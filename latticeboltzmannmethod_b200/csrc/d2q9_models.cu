@@ -770,10 +770,14 @@ public:
         int xc = 64;
         if (const char *e = getenv("LBM_TUNE_XC")) xc = std::max(1, atoi(e));   // measurement knob
         const dim3 grid((cfg_.ny + 127) / 128, (cfg_.nx + xc - 1) / xc);
+        if (!march_ready_) {    // 60 KB of dynamic shared memory: opt in once
+            LBM_CUDA(rt_, cudaFuncSetAttribute(k_b2_march<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kB2MarchSmem));
+            LBM_CUDA(rt_, cudaFuncSetAttribute(k_b2_march<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kB2MarchSmem));
+            march_ready_ = true;
+        }
         for (int t = 0; t < nsteps; t++) {
             const bool w = t == nsteps - 1;
             auto kern = w ? k_b2_march<true> : k_b2_march<false>;
-            LBM_CUDA(rt_, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kB2MarchSmem));
             rt_.about_to_launch();
             kern<<<grid, 128, kB2MarchSmem, rt_.stream>>>(P_, f_[cur_], g_[cur_], f_[1 - cur_], g_[1 - cur_], fields_[LBM_PHASE],
                                                           fields_[LBM_RHO], fields_[LBM_UX], fields_[LBM_UY], xc);
@@ -841,6 +845,7 @@ public:
 
 private:
     lbm2::B2Params P_{};
+    bool march_ready_ = false;
     bool one_pass_ = false, next_valid_ = false;   // next_valid_: phase_next_ holds the phase field of the front populations
     B2OnePlan one_{};
     unsigned *ctrl_ = nullptr;                     // [0] give-up flag, [32 + 32 i] counter of group i, [last] fallback count
