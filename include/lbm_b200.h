@@ -93,12 +93,11 @@ typedef struct {
                                   one launch), 6 two passes; on several slabs only the five z-crossing directions travel
                                   (NCCL inside lbm_step after lbm_comm_attach; the lbm_slab_* protocol is for the
                                   two-array forms), and populations can be loaded after lbm_init or an even number of
-                                  steps only; Shan-Chen 1 = density pass + collide, 2/3/5 = other tiles of the
-                                  fused kernel; binary D2Q9 0 = marching kernel (one pass, the phase field in a shared-memory ring),
-                                  6 / 1 = phase pass + collide with 128- / 256-thread blocks, 2-4 = fused tile kernel,
-                                  5 = one-pass step in the manner of the D3Q19 default (slower here); MRT 0 = in-place AA-pattern streaming on ONE population array, 1 = two arrays with push
-                                  streaming; curved
-                                  solid 1/2 = other block shapes.  Results never depend on it. */
+                                  steps only; Shan-Chen 0 = fused tile kernel, 1 = density pass + collide; binary D2Q9 0 = marching
+                                  kernel (one pass, the phase field in a shared-memory ring), 1 = phase pass + collide;
+                                  MRT 0 = in-place AA-pattern streaming on ONE population array, 1 = two arrays with
+                                  push streaming; TRT diffusion and curved solid: 0 only.  Any other value: LBM_EINVAL.
+                                  Results never depend on it. */
     double trt_magic;          /* LBM_BINARY_D3Q19 only, EXTENSION with no counterpart in the reference: 0 (default) keeps
                                   the reference's BGK collision; Lambda > 0 relaxes the antisymmetric half of f with
                                   omega- = 1/(Lambda/(tau-1/2) + 1/2) (two-relaxation-time), everything else unchanged.

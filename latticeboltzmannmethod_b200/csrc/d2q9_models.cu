@@ -118,206 +118,6 @@ __global__ void __launch_bounds__(NT) k_b2_collide(lbm2::B2Params P, const doubl
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < (long long)P.nx * P.ny) lbm2::b2_collide_thread(P, f, g, phase, f2, g2, rho, ux, uy, (int)((unsigned)i / (unsigned)P.ny), (int)((unsigned)i % (unsigned)P.ny), WRITE);
 }
-// One launch per binary-liquid step, same scheme as k_sc_fused: a tile of TS columns (iX) x 32 rows (iY, the fast
-// index), the phase field of the tile and of the ring around it summed from g into shared memory (wall rows take
-// their neighbour row's sum minus wall_gradient, binary.cpp:245-249), one barrier, collide out of registers.
-template <int TS, int MINB, bool WRITE>
-__global__ void __launch_bounds__(32 * TS, MINB) k_b2_fused(lbm2::B2Params P, const double *__restrict__ f, const double *__restrict__ g,
-                                                             double *__restrict__ f2, double *__restrict__ g2, double *__restrict__ phase,
-                                                             double *__restrict__ rho, double *__restrict__ ux, double *__restrict__ uy)
-{
-    __shared__ double phi_s[TS + 2][34];
-    const int NX = P.nx, NY = P.ny;
-    const long long n = (long long)NX * NY;
-    const int ly = threadIdx.x & 31, lx = threadIdx.x >> 5;
-    const int y0 = blockIdx.x * 32, x0 = blockIdx.y * TS;
-    // phi of frame position (fx, fy) = node (x0+fx-1 periodic, y0+fy-1); rows outside [0, NY-1] are never read
-    auto frame_phi = [&](int fx, int fy) {
-        const int gy = y0 + fy - 1;
-        if (gy < 0 || gy > NY - 1) return;
-        const int gx = (x0 + fx - 1 + NX) % NX;
-        const int sy = gy == 0 ? 1 : (gy == NY - 1 ? NY - 2 : gy);
-        const long long h = (long long)gx * NY + sy;
-        double s = 0.0;
-#pragma unroll
-        for (int k = 0; k < 9; k++) s += g[k * n + h];
-        phi_s[fx][fy] = sy == gy ? s : s - P.wall_gradient;
-    };
-    const int ix = x0 + lx, iy = y0 + ly;
-    const bool active = ix < NX && iy >= 1 && iy <= NY - 2;
-    const long long i = (long long)ix * NY + iy;
-    double F[9], G[9];
-    if (active) {
-#pragma unroll
-        for (int k = 0; k < 9; k++) { F[k] = f[k * n + i]; G[k] = g[k * n + i]; }
-        double s = 0.0;
-#pragma unroll
-        for (int k = 0; k < 9; k++) s += G[k];
-        phi_s[lx + 1][ly + 1] = s;
-    } else {
-        frame_phi(lx + 1, ly + 1);       // wall rows and the wrap column of a partial tile
-    }
-    constexpr int kRing = 2 * 34 + 2 * TS;
-    for (int r = threadIdx.x; r < kRing; r += 32 * TS) {
-        if (r < 34) frame_phi(0, r);
-        else if (r < 68) frame_phi(TS + 1, r - 34);
-        else if (r < 68 + TS) frame_phi(r - 68 + 1, 0);
-        else frame_phi(r - 68 - TS + 1, 33);
-    }
-    __syncthreads();
-    if (WRITE && ix < NX && iy < NY) phase[i] = phi_s[lx + 1][ly + 1];   // wall rows included (binary.cpp:245-249)
-    if (!active) return;
-    const int CX[9] = LBM2_CX, CY[9] = LBM2_CY;
-    double ph9[9];
-#pragma unroll
-    for (int k = 0; k < 9; k++) ph9[k] = phi_s[lx + 1 + CX[k]][ly + 1 + CY[k]];
-    double d, vx, vy;
-    lbm2::b2_collide_core(P, F, G, ph9, d, vx, vy);
-    if (WRITE) { rho[i] = d; ux[i] = vx; uy[i] = vy; }
-    lbm2::b2_push(P, F, G, f2, g2, ix, iy);
-}
-// kernel_variant 5 (measured, not the default: slower than phase pass + collide on B200, see Binary2D::step).
-// One pass per binary-liquid step, the scheme of the D3Q19 k_step_one (csrc/d3q19_step.cuh) in two dimensions: block b
-// collides the 128 nodes [128 b, 128 b + 128) (memory order: iY fast) and also sums the NEXT step's phase field for
-// a block `lag` blocks behind, from the g* values that the blocks before it pushed into the back buffer -- read back
-// while they are still in L2, so HBM does not see g a second time (the phase pass of the two-kernel form costs 88 B
-// per update on top of 288).  Phase blocks are visited in the order D, D+1, ..., nblk-1, 0, ..., D-1 (D = blocks a
-// push can reach to either side): the first columns receive pushes from the last ones across the periodic seam.
-// Ordering between blocks: one release-add per block on the counter of its group of 64 blocks (one counter per
-// 128-byte line), relaxed polls requested first and looked at after the loads; if the producers are not done yet the
-// block collides first and looks again; the second look is bounded and a warp that gives up raises ctrl[0], after
-// which the host-side step recomputes the phase field with k_b2_phase.  Requires nx*ny even (16-byte L2-only copies).
-struct B2OnePlan {
-    int nblk, ntotal, lag, reach, sb;   // collide blocks, blocks in the grid, phase lag, D, blocks per counter group
-    unsigned spin_limit;
-};
-__device__ __forceinline__ unsigned b2_ld_relaxed(const unsigned *p)
-{
-    unsigned v;
-    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];\n" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-__global__ void __launch_bounds__(kThreads) k_b2_phase_repair(lbm2::B2Params P, const double *g, double *phase, const unsigned *ctrl, unsigned *sticky)
-{
-    if (*reinterpret_cast<const volatile unsigned *>(ctrl) == 0u) return;
-    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(sticky, 1u);
-    const long long n = (long long)P.nx * P.ny;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
-        lbm2::b2_phase_thread(P, g, phase, (int)((unsigned)i / (unsigned)P.ny), (int)((unsigned)i % (unsigned)P.ny));
-}
-template <bool WRITE>
-__global__ void __launch_bounds__(128, 4) k_b2_one(lbm2::B2Params P, const double *__restrict__ f, const double *__restrict__ g,
-                                                   const double *__restrict__ phase, double *__restrict__ f2, double *g2,
-                                                   double *phase_next, double *rho, double *uxo, double *uyo, unsigned *ctrl,
-                                                   B2OnePlan L)
-{
-    __shared__ __align__(16) double ps[9 * 128];     // g* of the nodes whose phase field this block sums
-    const int NX = P.nx, NY = P.ny;
-    const long long n = (long long)NX * NY;
-    const int b = (int)blockIdx.x, lane = threadIdx.x & 31, wbase = threadIdx.x & ~31;
-    unsigned *done = ctrl + 32;
-
-    // ---- phase part: which block, which counters ----
-    const int p = b - L.lag;
-    const bool p_block = p >= 0 && p < L.nblk;
-    int jb = p + L.reach;
-    const bool wrapped = jb >= L.nblk;
-    if (wrapped) jb -= L.nblk;
-    // producers: collide blocks [p, p + 2 reach]; across the seam [nblk - reach + jb, nblk) and [0, jb + reach]
-    const int a0 = wrapped ? L.nblk - L.reach + jb : p, a1 = min(L.nblk - 1, wrapped ? L.nblk - 1 : p + 2 * L.reach);
-    const int b0 = 0, b1 = jb + L.reach >= L.nblk ? jb + L.reach - L.nblk : (wrapped ? jb + L.reach : -1);
-    int grp = -1;
-    if (lane < 16) { const int gq = a0 / L.sb + lane; if (gq <= a1 / L.sb) grp = gq; }
-    else { const int gq = b0 / L.sb + (lane - 16); if (b1 >= 0 && gq <= b1 / L.sb) grp = gq; }
-    const bool need = p_block && grp >= 0;
-    const unsigned want = need ? (unsigned)min(L.sb, L.ntotal - grp * L.sb) : 0u;
-    const unsigned *cnt = done + (size_t)max(grp, 0) * 32;
-    unsigned seen = need ? b2_ld_relaxed(cnt) : 0u;
-
-    // ---- collide part: loads ----
-    const long long i = (long long)b * 128 + threadIdx.x;
-    const int ix = (int)(i / NY), iy = (int)(i % NY);
-    const bool active = b < L.nblk && i < n && iy >= 1 && iy <= NY - 2;
-    double F[9], G[9], ph9[9];
-    if (active) {
-        const int CX[9] = LBM2_CX, CY[9] = LBM2_CY;
-#pragma unroll
-        for (int k = 0; k < 9; k++) {
-            F[k] = __ldg(f + k * n + i);
-            G[k] = __ldg(g + k * n + i);
-            const int x2 = (ix + CX[k] + NX) % NX, y2 = iy + CY[k];
-            ph9[k] = __ldg(phase + (long long)x2 * NY + y2);
-        }
-    }
-    // ---- phase part, first chance ----
-    const long long jbase = (long long)jb * 128 + wbase;            // this warp's 32 nodes
-    bool p_warp = p_block && jbase < n;
-    auto copy_rows = [&]() {
-        // 9 directions x 16 chunks of 16 bytes for the warp's 32 nodes: lane -> (direction lane/16 + 2 j, chunk lane%16)
-        const int k0 = lane >> 4, e = (lane & 15) * 2;
-        if (jbase + e < n) {
-            const double *sp = g2 + k0 * n + jbase + e;
-            double *dp = ps + k0 * 128 + wbase + e;
-#pragma unroll
-            for (int j = 0; j < 5; j++) {
-                if (k0 + 2 * j < 9) {
-                    const unsigned sa = (unsigned)__cvta_generic_to_shared(dp);
-                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(sa), "l"(sp) : "memory");
-                }
-                sp += 2 * n;
-                dp += 2 * 128;
-            }
-        }
-    };
-    const bool early = p_warp && __all_sync(0xffffffffu, seen >= want);
-    if (early) copy_rows();
-    asm volatile("cp.async.commit_group;\n" ::: "memory");
-
-    // ---- collide part: arithmetic and push ----
-    if (active) {
-        double d, vx, vy;
-        lbm2::b2_collide_core(P, F, G, ph9, d, vx, vy);
-        if (WRITE) { rho[i] = d; uxo[i] = vx; uyo[i] = vy; }
-        lbm2::b2_push(P, F, G, f2, g2, ix, iy);
-    }
-
-    // ---- phase part, second chance (bounded), then the sums ----
-    if (p_warp && !early) {
-        unsigned spins = 0;
-        bool ok;
-        for (;;) {
-            if (need) seen = b2_ld_relaxed(cnt);
-            ok = __all_sync(0xffffffffu, seen >= want);
-            if (ok || ++spins > L.spin_limit) break;
-            if (__any_sync(0xffffffffu, lane == 0 && b2_ld_relaxed(ctrl) != 0u)) break;
-            __nanosleep(200);
-        }
-        if (ok) {
-            copy_rows();
-            asm volatile("cp.async.commit_group;\n" ::: "memory");
-        } else {
-            if (lane == 0) atomicOr(ctrl, 1u);
-            p_warp = false;
-        }
-    }
-    asm volatile("cp.async.wait_group 0;\n" ::: "memory");
-    __syncwarp();
-    const long long j = (long long)jb * 128 + threadIdx.x;
-    if (p_warp && j < n) {
-        const int jy = (int)(j % NY);
-        if (jy >= 1 && jy <= NY - 2) {
-            double ph = 0.0;                                   // binary.cpp:239-250, ascending k
-#pragma unroll
-            for (int k = 0; k < 9; k++) ph += ps[k * 128 + threadIdx.x];
-            phase_next[j] = ph;
-            if (jy == 1) phase_next[j - 1] = ph - P.wall_gradient;
-            if (jy == NY - 2) phase_next[j + 1] = ph - P.wall_gradient;
-        }
-    }
-    // publish the end of this block's collide part
-    __syncthreads();
-    if (threadIdx.x == 0) asm volatile("red.release.gpu.global.add.u32 [%0], %1;\n" ::"l"(done + (size_t)(b / L.sb) * 32), "r"(1u) : "memory");
-}
 // kernel_variant 0 (the default): one pass per binary-liquid step by MARCHING.  A block owns 128 consecutive rows (iY, the fast
 // index) and walks over `xc` consecutive columns (iX).  The phase field lives only in shared memory, as a ring of four
 // columns of 128 + 2 values; before column x is collided the block has summed the phase values of column x + 1 from
@@ -618,6 +418,8 @@ public:
     ShanChen(Runtime &rt, const lbm_config &cfg) : Model2D(rt, cfg, 1) {}
     lbm_status setup()
     {
+        if (cfg_.kernel_variant != 0 && cfg_.kernel_variant != 1)
+            return rt_.fail(LBM_EINVAL, "Shan-Chen: kernel_variant must be 0 (fused tile kernel) or 1 (density pass + collide)");
         LBM_TRY(alloc_common());
         P_ = lbm2::sc_params(cfg_.nx, cfg_.ny, cfg_.tau, cfg_.g);
         LBM_CUDA(rt_, rt_.dev_alloc(&aux_, n_ * sizeof(double)));   // psi
@@ -631,21 +433,14 @@ public:
     }
     lbm_status step(int nsteps) override
     {
-        // kernel_variant 1: the two-kernel form (density pass + collide); otherwise the fused tile kernel:
-        // 0 = 32x4 tile capped at 64 registers, 8 blocks/SM (fastest measured: 2.12 ms at 8192^2); 2 = 32x16;
-        // 3 = 32x8 at 64 registers (2.27 ms); 5 = 32x8 uncapped, 3 blocks/SM (2.58 ms).  A marching kernel (128 columns
-        // per block walking over 64 rows, psi in a shared-memory ring -- the scheme that took the binary model from
-        // 3.94 to 3.42 ms) was bit-exact and ran in 2.03 ms against 1.98 ms for the tile kernel: not kept.
+        // kernel_variant 0 (default): the fused tile kernel, 32x4 tile capped at 64 registers, 8 blocks/SM (1.98 ms at
+        // 8192^2); 1: the two-kernel form (density pass + collide), the cross-check.  Measured and removed:
+        // tiles of 32x16 and 32x8 (2.27 - 2.58 ms); a marching kernel (128 columns per block walking over 64 rows, psi
+        // in a shared-memory ring -- the scheme that took the binary model from 3.94 to 3.42 ms): bit-exact, 2.03 ms.
         if (cfg_.kernel_variant != 1) {
             for (int t = 0; t < nsteps; t++) {
-                const bool w = t == nsteps - 1;
                 rt_.about_to_launch();
-                switch (cfg_.kernel_variant) {
-                case 2: launch_fused<32, 16, 1>(w); break;
-                case 3: launch_fused<32, 8, 4>(w); break;
-                case 5: launch_fused<32, 8, 3>(w); break;
-                default: launch_fused<32, 4, 8>(w); break;
-                }
+                launch_fused<32, 4, 8>(t == nsteps - 1);
                 LBM_TRY(rt_.launched("k_sc_fused"));
                 cur_ = 1 - cur_;
             }
@@ -683,87 +478,21 @@ public:
     lbm_status setup()
     {
         if (cfg_.ny < 4) return rt_.fail(LBM_EINVAL, "binary D2Q9: ny must be at least 4");
+        if (cfg_.kernel_variant != 0 && cfg_.kernel_variant != 1)
+            return rt_.fail(LBM_EINVAL, "binary D2Q9: kernel_variant must be 0 (marching kernel, one pass) or 1 (phase pass + collide)");
         LBM_TRY(alloc_common());
         P_ = lbm2::B2Params{cfg_.nx, cfg_.ny, cfg_.aconst, cfg_.kconst, cfg_.gammaconst, cfg_.wall_gradient,
                             cfg_.tau_gas, cfg_.tau_liq - cfg_.tau_gas, 1.0 / cfg_.tau_phi};
-        return setup_one_pass();
+        return LBM_OK;
     }
     bool has_field(int f) const override { return f == LBM_RHO || f == LBM_PHASE || f == LBM_UX || f == LBM_UY; }
     lbm_status init() override
     {
-        next_valid_ = false;
         k_b2_wallphase<<<blocks_for(cfg_.nx), kThreads, 0, rt_.stream>>>(P_, fields_[LBM_PHASE]);
         LBM_TRY(rt_.launched("k_b2_wallphase"));
         k_b2_init<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, fields_[LBM_PHASE], f_[0], g_[0], f_[1], g_[1],
                                                                fields_[LBM_RHO], fields_[LBM_UX], fields_[LBM_UY]);
         return rt_.launched("k_b2_init");
-    }
-    template <int TS, int MINB>
-    void launch_fused(bool write)
-    {
-        const dim3 grid((cfg_.ny + 31) / 32, (cfg_.nx + TS - 1) / TS);
-        auto kern = write ? k_b2_fused<TS, MINB, true> : k_b2_fused<TS, MINB, false>;
-        kern<<<grid, 32 * TS, 0, rt_.stream>>>(P_, f_[cur_], g_[cur_], f_[1 - cur_], g_[1 - cur_], fields_[LBM_PHASE], fields_[LBM_RHO],
-                                               fields_[LBM_UX], fields_[LBM_UY]);
-    }
-    // one-pass step (k_b2_one): eligible when the 16-byte copies are aligned (nx*ny even) and the grid is not so small
-    // that a block's producers wrap around the whole domain
-    lbm_status setup_one_pass()
-    {
-        if (cfg_.kernel_variant != 5) return LBM_OK;
-        const int nblk = (int)((n_ + 127) / 128), reach = 1 + cfg_.ny / 128;
-        if (n_ % 2 != 0 || nblk <= 4 * reach + 2 || 2 * reach / 64 + 2 > 16) return LBM_OK;
-        int per_sm = 4, sms = 148;
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_b2_one<false>, 128, 0);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, rt_.device);
-        one_.nblk = nblk; one_.reach = reach; one_.sb = 64;
-        one_.lag = std::max((int)(1.5 * std::max(per_sm, 1) * sms), 2 * reach + 2);
-        one_.ntotal = nblk + one_.lag;
-        one_.spin_limit = 4000;
-        ctrl_words_ = (size_t)((one_.ntotal + one_.sb - 1) / one_.sb) * 32 + 64;
-        LBM_CUDA(rt_, rt_.dev_alloc(&ctrl_, ctrl_words_ * sizeof(unsigned)));
-        LBM_CUDA(rt_, rt_.dev_alloc(&phase_next_, n_ * sizeof(double)));
-        LBM_CUDA(rt_, cudaMemsetAsync(phase_next_, 0, n_ * sizeof(double), rt_.stream));
-        LBM_CUDA(rt_, cudaMemsetAsync(ctrl_, 0, ctrl_words_ * sizeof(unsigned), rt_.stream));
-        one_pass_ = true;
-        return LBM_OK;
-    }
-    ~Binary2D() override
-    {
-        cudaSetDevice(rt_.device);
-        rt_.dev_free(ctrl_);
-        rt_.dev_free(phase_next_);
-    }
-    unsigned long long fallbacks() override
-    {
-        unsigned v = 0;
-        if (ctrl_ && cudaMemcpyAsync(&v, ctrl_ + ctrl_words_ - 1, sizeof v, cudaMemcpyDeviceToHost, rt_.stream) == cudaSuccess)
-            cudaStreamSynchronize(rt_.stream);
-        return v;
-    }
-    lbm_status step_one_pass(int nsteps)
-    {
-        for (int t = 0; t < nsteps; t++) {
-            const bool w = t == nsteps - 1;
-            if (!next_valid_) {
-                rt_.about_to_launch();
-                k_b2_phase<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, g_[cur_], fields_[LBM_PHASE]);
-                LBM_TRY(rt_.launched("k_b2_phase"));
-            } else {
-                std::swap(fields_[LBM_PHASE], phase_next_);      // what the last step summed is what this one reads (and shows)
-            }
-            LBM_CUDA(rt_, cudaMemsetAsync(ctrl_, 0, (ctrl_words_ - 1) * sizeof(unsigned), rt_.stream));
-            rt_.about_to_launch();
-            auto kern = w ? k_b2_one<true> : k_b2_one<false>;
-            kern<<<one_.ntotal, 128, 0, rt_.stream>>>(P_, f_[cur_], g_[cur_], fields_[LBM_PHASE], f_[1 - cur_], g_[1 - cur_], phase_next_,
-                                                      fields_[LBM_RHO], fields_[LBM_UX], fields_[LBM_UY], ctrl_, one_);
-            LBM_TRY(rt_.launched("k_b2_one"));
-            k_b2_phase_repair<<<296, kThreads, 0, rt_.stream>>>(P_, g_[1 - cur_], phase_next_, ctrl_, ctrl_ + ctrl_words_ - 1);
-            LBM_TRY(rt_.launched("k_b2_phase_repair"));
-            next_valid_ = true;
-            cur_ = 1 - cur_;
-        }
-        return LBM_OK;
     }
     lbm_status step_march(int nsteps)
     {
@@ -788,47 +517,22 @@ public:
     }
     lbm_status step(int nsteps) override
     {
-        if (one_pass_) return step_one_pass(nsteps);
         // kernel_variant 0 (default): the marching kernel, one pass with the phase field in shared memory: 3.42 ms at
         // 8192^2 = 0.86 of the measured HBM peak (columns per block 32 / 64 / 128 / 256: 3.41 / 3.42 / 3.45 / 3.47 ms)
         if (cfg_.kernel_variant == 0) return step_march(nsteps);
-        // kernel_variant 6 and 1 (and 5 on grids the one-pass kernel does not take): phase pass + collide, round 1's
-        // default (3.94 ms at 8192^2; the lagging one-pass kernel, variant 5: 4.68 ms -- it moves 303 instead of 376 B per
-        // update, but this collision is short enough that the phase part's extra instructions cost more than its bytes;
-        // a staged, streamed form of the collide kernel at 5 / 6 / 8 blocks per SM: 4.29 / 4.19 / 4.79 ms -- the register
-        // form already moves its 288 B per update at 5.9 TB/s, occupancy is not what limits it).  The fused
-        // tile kernel is kept as variants 2 (8 columns x 32 rows, 5.37 ms), 3 (4 x 32 capped at 96 registers, 4.52 ms)
-        // and 4 (4 x 32, 5.08 ms): unlike Shan-Chen's, this collision needs ~125 registers, so the fused form gains
-        // no occupancy and pays for the ring and the barrier.
-        if (cfg_.kernel_variant >= 2 && cfg_.kernel_variant <= 4) {
-            for (int t = 0; t < nsteps; t++) {
-                const bool w = t == nsteps - 1;
-                rt_.about_to_launch();
-                switch (cfg_.kernel_variant) {
-                case 2: launch_fused<8, 2>(w); break;
-                case 3: launch_fused<4, 5>(w); break;
-                default: launch_fused<4, 4>(w); break;
-                }
-                LBM_TRY(rt_.launched("k_b2_fused"));
-                cur_ = 1 - cur_;
-            }
-            return LBM_OK;
-        }
+        // kernel_variant 1: phase pass + collide with 128-thread blocks, round 1's default and the cross-check of the
+        // marching kernel (3.94 ms; 256-thread blocks: 4.23 ms).  What else was built, measured and removed (DESIGN.md 4
+        // has the numbers, the history the code): a lagging one-pass kernel in the manner of the D3Q19 k_step_one
+        // (4.68 ms), a staged, streamed form of the collide kernel (4.19 - 4.79 ms), shared-memory tile kernels
+        // (4.52 - 5.37 ms).
         for (int t = 0; t < nsteps; t++) {
             rt_.about_to_launch();
             k_b2_phase<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, g_[cur_], fields_[LBM_PHASE]);
             LBM_TRY(rt_.launched("k_b2_phase"));
             rt_.about_to_launch();
-            const bool w = t == nsteps - 1;
-            if (cfg_.kernel_variant != 1) {     // 128-thread blocks (4.11 ms at 8192^2; variant 1, 256 threads: 4.23 ms)
-                auto kern = w ? k_b2_collide<true, 128> : k_b2_collide<false, 128>;
-                kern<<<(unsigned)((n_ + 127) / 128), 128, 0, rt_.stream>>>(P_, f_[cur_], g_[cur_], fields_[LBM_PHASE], f_[1 - cur_], g_[1 - cur_],
-                                                                          fields_[LBM_RHO], fields_[LBM_UX], fields_[LBM_UY]);
-            } else {
-                auto kern = w ? k_b2_collide<true, 256> : k_b2_collide<false, 256>;
-                kern<<<(unsigned)((n_ + 255) / 256), 256, 0, rt_.stream>>>(P_, f_[cur_], g_[cur_], fields_[LBM_PHASE], f_[1 - cur_], g_[1 - cur_],
-                                                                  fields_[LBM_RHO], fields_[LBM_UX], fields_[LBM_UY]);
-            }
+            auto kern = t == nsteps - 1 ? k_b2_collide<true, 128> : k_b2_collide<false, 128>;
+            kern<<<(unsigned)((n_ + 127) / 128), 128, 0, rt_.stream>>>(P_, f_[cur_], g_[cur_], fields_[LBM_PHASE], f_[1 - cur_], g_[1 - cur_],
+                                                                      fields_[LBM_RHO], fields_[LBM_UX], fields_[LBM_UY]);
             LBM_TRY(rt_.launched("k_b2_collide"));
             cur_ = 1 - cur_;
         }
@@ -837,7 +541,6 @@ public:
     // wall rows are never streamed into, so a load must reach both buffers
     lbm_status after_set_populations(int set) override
     {
-        next_valid_ = false;
         double *src = set == 0 ? f_[cur_] : g_[cur_], *dst = set == 0 ? f_[1 - cur_] : g_[1 - cur_];
         return rt_.cuda(cudaMemcpyAsync(dst, src, 9 * n_ * sizeof(double), cudaMemcpyDeviceToDevice, rt_.stream), "copy populations");
     }
@@ -846,11 +549,6 @@ public:
 private:
     lbm2::B2Params P_{};
     bool march_ready_ = false;
-    bool one_pass_ = false, next_valid_ = false;   // next_valid_: phase_next_ holds the phase field of the front populations
-    B2OnePlan one_{};
-    unsigned *ctrl_ = nullptr;                     // [0] give-up flag, [32 + 32 i] counter of group i, [last] fallback count
-    size_t ctrl_words_ = 0;
-    double *phase_next_ = nullptr;
 };
 
 class Mrt : public Model2D {
@@ -858,6 +556,8 @@ public:
     Mrt(Runtime &rt, const lbm_config &cfg) : Model2D(rt, cfg, 1) {}
     lbm_status setup()
     {
+        if (cfg_.kernel_variant != 0 && cfg_.kernel_variant != 1)
+            return rt_.fail(LBM_EINVAL, "MRT: kernel_variant must be 0 (in place, one population array) or 1 (two arrays)");
         LBM_TRY(alloc_common());
         aa_ = cfg_.kernel_variant != 1;      // default: in-place AA streaming; 1: two arrays, push streaming
         if (aa_) { rt_.dev_free(f_[1]); f_[1] = nullptr; }      // the point of the in-place form: one population array
@@ -935,6 +635,7 @@ public:
     ~Trt() override { rt_.dev_free(links_); }
     lbm_status setup()
     {
+        if (cfg_.kernel_variant != 0) return rt_.fail(LBM_EINVAL, "TRT diffusion: kernel_variant must be 0");
         LBM_TRY(alloc_common());
         P_ = lbm2::TrtParams{cfg_.nx, cfg_.ny, 2.0 - cfg_.omega, cfg_.omega, cfg_.ce, cfg_.conc_wall};   // cylinder.cpp:38-40
         LBM_CUDA(rt_, rt_.dev_alloc(&links_, n_ * sizeof(unsigned short)));
@@ -1014,6 +715,7 @@ public:
     ~BinaryShape() override { rt_.dev_free(links_); }
     lbm_status setup()
     {
+        if (cfg_.kernel_variant != 0) return rt_.fail(LBM_EINVAL, "curved-solid binary liquid: kernel_variant must be 0");
         LBM_TRY(alloc_common());
         P_ = lbm2::BsParams{cfg_.nx, cfg_.ny, cfg_.aconst, cfg_.kconst, cfg_.gammaconst, cfg_.wall_gradient, cfg_.tau_gas,
                             cfg_.tau_liq - cfg_.tau_gas, 1.0 / cfg_.tau_phi, cfg_.force[0], cfg_.force[1]};
@@ -1064,25 +766,15 @@ public:
             k_bs_phase<<<blocks_for(n_), kThreads, 0, rt_.stream>>>(P_, g_[cur_], links_, fields_[LBM_PHASE]);
             LBM_TRY(rt_.launched("k_bs_phase"));
             rt_.about_to_launch();
-            // (A marching kernel in the manner of k_b2_march -- sums of g in a shared-memory ring of rows y-2 .. y+2, the
-            // phase value of a bounce-back neighbour looked up through its link word -- ran in 4.16 ms against 3.96 ms
-            // for these two passes: the per-neighbour link loads and look-ups cost more than the phase pass.  Not kept.)
-            // kernel_variant 0 (default): 128 threads x 4 blocks/SM (128 registers), 4.27 ms at 8192^2; 1: 128 threads x 3
-            // (168 registers, no spills), 4.75 ms; 2: 256 threads x 2 (128 registers), 4.45 ms
+            // 128 threads x 4 blocks/SM (128 registers): 3.96 ms at 8192^2.  Measured and removed: 128 x 3 (168 registers,
+            // 4.75 ms at the time), 256 x 2 (4.45 ms), and a marching kernel in the manner of k_b2_march -- sums of g in a
+            // shared-memory ring of rows y-2 .. y+2, the phase value of a bounce-back neighbour looked up through its
+            // link word -- at 4.16 ms: the per-neighbour look-ups and the solid nodes it walks over cost more than the
+            // phase pass.
             const bool w = t == nsteps - 1;
-            if (cfg_.kernel_variant == 1) {
-                auto kern = w ? k_bs_collide<true, 128, 3> : k_bs_collide<false, 128, 3>;
-                kern<<<(unsigned)((n_ + 127) / 128), 128, 0, rt_.stream>>>(P_, f_[cur_], g_[cur_], fields_[LBM_PHASE], links_, f_[1 - cur_],
-                                                                          g_[1 - cur_], fields_[LBM_RHO], fields_[LBM_UX], fields_[LBM_UY]);
-            } else if (cfg_.kernel_variant != 2) {
-                auto kern = w ? k_bs_collide<true, 128, 4> : k_bs_collide<false, 128, 4>;
-                kern<<<(unsigned)((n_ + 127) / 128), 128, 0, rt_.stream>>>(P_, f_[cur_], g_[cur_], fields_[LBM_PHASE], links_, f_[1 - cur_],
-                                                                          g_[1 - cur_], fields_[LBM_RHO], fields_[LBM_UX], fields_[LBM_UY]);
-            } else {
-                auto kern = w ? k_bs_collide<true, 256, 2> : k_bs_collide<false, 256, 2>;
-                kern<<<(unsigned)((n_ + 255) / 256), 256, 0, rt_.stream>>>(P_, f_[cur_], g_[cur_], fields_[LBM_PHASE], links_, f_[1 - cur_],
-                                                                  g_[1 - cur_], fields_[LBM_RHO], fields_[LBM_UX], fields_[LBM_UY]);
-            }
+            auto kern = w ? k_bs_collide<true, 128, 4> : k_bs_collide<false, 128, 4>;
+            kern<<<(unsigned)((n_ + 127) / 128), 128, 0, rt_.stream>>>(P_, f_[cur_], g_[cur_], fields_[LBM_PHASE], links_, f_[1 - cur_],
+                                                                      g_[1 - cur_], fields_[LBM_RHO], fields_[LBM_UX], fields_[LBM_UY]);
             LBM_TRY(rt_.launched("k_bs_collide"));
             cur_ = 1 - cur_;
         }

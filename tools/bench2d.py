@@ -75,7 +75,7 @@ def measure(n=8192, steps=20, alternatives=True, peak=None):
         ctx.close()
     del rho
     ph = np.tile(api.binary2d_initial_phase().reshape(128, 128), (n // 128, n // 128)).ravel()
-    for variant, label in ((0, "binary_d2q9"), (3, "binary_d2q9 (fused tile 4x32, 96 regs)")):
+    for variant, label in ((0, "binary_d2q9"), (1, "binary_d2q9 (phase pass + collide)")):
         if variant and not alternatives:
             continue
         cfg = api.binary2d_config(n, n)
