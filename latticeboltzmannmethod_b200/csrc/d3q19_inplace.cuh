@@ -3,12 +3,15 @@
 // (lattice.hpp:842-855) on top of Lattice::collide_stream / updateMacro (lattice.hpp:4-108, 377-688).
 //
 // The per-thread address rules and the reasons why they are race-free are in d3q19_threads.h (aa_loc and friends);
-// the CPU unit test runs those.  Here: the kernels.  One slab per context, z periodic inside it: blocks address the
-// planes below and above explicitly, populations need no ghost planes.
+// the CPU unit test runs those.  Here: the kernels.  A slab that holds the whole grid takes z periodic by addressing
+// (Geom::zwrap): blocks address the planes below and above explicitly, populations need no ghost planes.  A slab of
+// several uses its two ghost planes as the places beyond its z faces; Slab3D::aa_exchange moves them (five directions
+// per face) after every sub-step.
 //
 //   k_aa_phase / k_aa_core (k_aa_collide for the TRT and MRT extensions)   two passes: phase field, then collide in place
 //   k_aa_one + k_aa_repair                                                 one pass, see below
 //   k_aa_swap                                                              odd half of the cycle <-> streamed populations
+//   k_aa_merge                                                             several slabs: second half of the exchange after an odd step
 #ifndef LBM_D3Q19_INPLACE_CUH
 #define LBM_D3Q19_INPLACE_CUH
 
