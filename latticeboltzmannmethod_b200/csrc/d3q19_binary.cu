@@ -234,7 +234,7 @@ public:
     // (k_phase, then the collide kernels); 1 two-pass with the plain whole-plane collide kernel (the cross-check).
     // The TRT extension exists in the array form of the collision only and always takes the two-pass path.
     // 2 and 6: in-place (AA-pattern) streaming on ONE population array (d3q19_inplace.cuh) -- half the population
-    // memory; one slab per context (z periodic inside it), any collision operator.  2: one pass (the phase field of
+    // memory; any collision operator; on several slabs only five directions per z face travel (aa_exchange).  2: one pass (the phase field of
     // the step runs ahead of the collision inside the same launch; BGK -- the extensions take the two-pass form);
     // 6: two passes (phase field, then collide in place).
     bool aa() const { return cfg_.kernel_variant == 2 || cfg_.kernel_variant == 6; }

@@ -334,8 +334,9 @@ LBM_HD void collide_push_thread_streamed(const Geom &g, const Params &P, const p
 //       F[opp(m)] = A[loc(x, m)];  collide;   A[loc(x, m)] = F*[m]          -- lands where the two-array push puts it
 // Every thread loads and stores the same 19 places, no two threads share one: no second array, no race.  With
 // slot(x, m) = (x, opp(m)) in an even and loc(x, m) in an odd step both read F[opp(m)] = A[slot(x, m)] and write
-// A[slot(x, m)] = F*[m].  z is periodic inside the one slab this variant runs on: the planes below and above come as
-// explicit offsets, no ghost planes of populations are needed.
+// A[slot(x, m)] = F*[m].  The planes below and above come as explicit offsets: inside a slab that holds the whole grid
+// z is periodic by addressing and no ghost planes of populations are needed; a slab of several uses its ghost planes
+// as the places beyond its z faces (the halo exchange moves them, see aa_crossed_face below).
 struct AaPlanes {
     long long zm, z0, zp;   // element offsets of plane z-1, z, z+1 (19 * pitch each) from the start of the array
 };
