@@ -234,8 +234,9 @@ k_aa_one(Geom g, Params P, pop_t *f, pop_t *gq, double *phi, FieldsOut o, unsign
     const int NX = g.nx, NY = g.ny, nz = g.nz, nplane = NX * NY;
     const int t = (int)blockIdx.y, strip = (int)blockIdx.z;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int c = t - A.L;                                  // plane this block collides
-    const bool c_step = c >= 0 && c < nz;
+    const AaSchedule sched = aa_schedule(g.zwrap, nz, A.L, t);
+    const int c = sched.collide_plane;                      // plane this block collides (-1: none)
+    const bool c_step = c >= 0;
     const int bbase = (strip * A.sb + (int)blockIdx.x) * 128;   // first node of the phase segment
     const int cbase = bbase - A.dshift * 128;                   // first node of the collide segment
 
@@ -245,9 +246,8 @@ k_aa_one(Geom g, Params P, pop_t *f, pop_t *gq, double *phi, FieldsOut o, unsign
     unsigned seen = A.full;
     const unsigned *cnt = done;
     if (c_step && lane < 6) {
-        // plane-step at which the phase field of plane c - 1 + j was summed
-        const int q = g.zwrap ? (c + lane % 3) % nz : c - 1 + lane % 3, sdep = strip - lane / 3;
-        need = sdep >= 0 && q >= 0 && q < nz && (lane < 3 || (int)blockIdx.x < 2 * A.dshift);
+        const int j = lane % 3, q = j == 0 ? sched.dep[0] : (j == 1 ? sched.dep[1] : sched.dep[2]), sdep = strip - lane / 3;
+        need = sdep >= 0 && q >= 0 && (lane < 3 || (int)blockIdx.x < 2 * A.dshift);
         cnt = done + (size_t)(sdep * nz + (need ? q : 0)) * LAG_PAD;
         if (need) seen = lag_ld_relaxed(cnt);
     }
@@ -275,9 +275,9 @@ k_aa_one(Geom g, Params P, pop_t *f, pop_t *gq, double *phi, FieldsOut o, unsign
     // ---- phase part, requests: the g values of plane-sequence element t (nothing in this launch has touched these
     // places yet) into this thread's second column; summed at the very end of the block, when they have long arrived
     const int pidx = bbase + (int)threadIdx.x;
-    const int pz = g.zwrap ? (t == 0 ? nz - 1 : t - 1) : t;
+    const int pz = sched.phase_plane;
     int px = 0, py = 0;
-    bool do_p = t < nz && pidx < nplane;
+    bool do_p = pz >= 0 && pidx < nplane;
     if (do_p) {
         px = (int)((unsigned)pidx % (unsigned)NX);
         py = (int)((unsigned)pidx / (unsigned)NX);

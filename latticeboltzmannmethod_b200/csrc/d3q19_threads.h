@@ -448,6 +448,29 @@ LBM_HD bool aa_crossed_face(const Geom &g, int k, int ix, int iy)
     return !((CX[k] == -1 && ix == g.nx - 2) || (CY[k] == -1 && iy == g.ny - 2));
 }
 
+// Plane-step arithmetic of the one-pass in-place kernel (k_aa_one, d3q19_inplace.cuh), host/device so that the CPU test
+// can check it: at plane-step t a block sums the phase field of owned plane `phase_plane` and collides owned plane
+// `collide_plane` (-1: none), whose phase stencil needs the phase parts of plane-steps dep[0..2] (-1: not summed in this
+// launch -- a ghost plane of a slab, which the exchange has filled).  One slab holding the whole grid (zwrap): phase
+// planes in the order nz-1, 0, 1, .., nz-2 (the plane below plane 0 first); a slab of several: 0 .. nz-1.  The
+// collision trails by L >= 3 plane-steps, so every dependency is an earlier plane-step and a plane's own phase part
+// (which reads the plane's pre-collision values) comes before its collision.
+struct AaSchedule {
+    int phase_plane, collide_plane, dep[3];
+};
+LBM_HD AaSchedule aa_schedule(int zwrap, int nz, int L, int t)
+{
+    AaSchedule s;
+    s.phase_plane = t < nz ? (zwrap ? (t == 0 ? nz - 1 : t - 1) : t) : -1;
+    const int c = t - L;
+    s.collide_plane = c >= 0 && c < nz ? c : -1;
+    for (int j = 0; j < 3; j++) {
+        const int q = zwrap ? (c + j) % nz : c - 1 + j;     // plane-step at which plane c - 1 + j was summed
+        s.dep[j] = s.collide_plane >= 0 && q >= 0 && q < nz ? q : -1;
+    }
+    return s;
+}
+
 // Turns an array of the odd half (post-collision values in the opposite slots) into the streamed populations and
 // back, in place: the streamed value of (x, k) sits at loc(x, opp(k)), and loc(., opp(.)) is an involution on the
 // places, so the two places of every pair swap contents.  The thread of the lower address does the swap.

@@ -344,3 +344,35 @@ extern "C" long long emu3_aa_slabs_vs_whole(Emu *whole, int nslabs, int steps)
                     }
     return bad;
 }
+
+// ---- the plane-step arithmetic of k_aa_one (aa_schedule): number of rule violations over a whole launch ----
+extern "C" int emu3_aa_schedule_violations(int zwrap, int nz, int L)
+{
+    std::vector<int> phase_step(nz, -1), collide_step(nz, -1);
+    int bad = 0;
+    const int steps = nz + L;
+    for (int t = 0; t < steps; t++) {
+        const AaSchedule s = aa_schedule(zwrap, nz, L, t);
+        if (s.phase_plane >= 0) { bad += s.phase_plane >= nz || phase_step[s.phase_plane] != -1; phase_step[s.phase_plane] = t; }
+        if (s.collide_plane >= 0) { bad += s.collide_plane >= nz || collide_step[s.collide_plane] != -1; collide_step[s.collide_plane] = t; }
+    }
+    for (int p = 0; p < nz; p++) {
+        bad += phase_step[p] < 0 || collide_step[p] < 0;          // every plane summed once and collided once
+        bad += !(phase_step[p] < collide_step[p]);                // its own phase part reads its pre-collision values
+    }
+    for (int t = 0; t < steps; t++) {
+        const AaSchedule s = aa_schedule(zwrap, nz, L, t);
+        if (s.collide_plane < 0) continue;
+        for (int d = -1; d <= 1; d++) {                            // the three planes of the phase stencil
+            int p = s.collide_plane + d;
+            if (zwrap) p = (p + nz) % nz;
+            if (p < 0 || p >= nz) continue;                        // a ghost plane of a slab: filled before the launch
+            bool found = false;
+            for (int j = 0; j < 3; j++) found = found || (s.dep[j] >= 0 && s.dep[j] == phase_step[p]);
+            bad += !found;
+            bad += !(phase_step[p] < t);                           // summed at an earlier plane-step
+        }
+        for (int j = 0; j < 3; j++) bad += s.dep[j] >= nz || (s.dep[j] >= 0 && !(s.dep[j] < t));
+    }
+    return bad;
+}

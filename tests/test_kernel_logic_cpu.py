@@ -96,6 +96,21 @@ def test_d3q19_in_place_slab_protocol_matches_one_slab(emu_libs, nslabs, steps):
     L.emu3_destroy(e)
 
 
+@pytest.mark.parametrize("zwrap", [1, 0])
+def test_d3q19_in_place_one_pass_schedule(emu_libs, zwrap):
+    """aa_schedule (the plane-step arithmetic of k_aa_one): over a whole launch every owned plane is summed once and
+    collided once, a plane's phase part comes before its collision, and every plane of a collision's phase stencil was
+    summed at an earlier plane-step that is among the dependencies the block waits for -- one periodic slab and a slab
+    of several, slabs from 2 planes up, every lag the library can choose."""
+    L = C.CDLL(emu_libs["d3q19"])
+    L.emu3_aa_schedule_violations.argtypes = [C.c_int] * 3
+    for nz in list(range(2, 12)) + [52, 512, 1024]:
+        for lag in (3, 4, 5, 17, 40):
+            assert L.emu3_aa_schedule_violations(zwrap, nz, lag) == 0, (nz, lag)
+    # a lag that is too short is caught (the check has teeth): the periodic order needs 3 plane-steps, a slab's order 2
+    assert L.emu3_aa_schedule_violations(zwrap, 8, 2 if zwrap else 1) > 0
+
+
 def _emu2(path):
     L = C.CDLL(path)
     L.emusc_create.restype = C.c_void_p
