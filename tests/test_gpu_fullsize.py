@@ -3,7 +3,8 @@ oracle run is affordable: size-independent properties instead.
   * z is periodic and every node runs the same arithmetic, so moving the initial bubble by s planes must move every
     field by s planes -- bit for bit;
   * the order parameter and the mass are conserved (bounce-back and mirror planes lose nothing; the body force adds
-    momentum, not mass)."""
+    momentum, not mass);
+  * the in-place step on one population array must leave exactly the fields of the default two-array step."""
 import numpy as np
 import pytest
 
@@ -11,8 +12,9 @@ pytestmark = pytest.mark.gpu
 N, WIDTH, STEPS, SHIFT = 512, 114, 6, 37
 
 
-def _run(api, shift):
+def _run(api, shift, variant=0):
     cfg = api.microchannel_config("quarter", N, N, N)
+    cfg.kernel_variant = variant
     ctx = api.Context(cfg)
     x = np.arange(N)[None, :] <= N - WIDTH - 1
     y = np.arange(N)[:, None] <= N - WIDTH - 1
@@ -55,6 +57,11 @@ def test_z_translation_invariance_and_conservation_at_bench_size():
     for k in keep:
         for z in zs:
             assert np.array_equal(keep[k][z], b[k][(z + SHIFT) % N]), (k, z)
+    # the same run in place on ONE population array (kernel_variant 2, one pass): every field of every node, bit for bit
+    c, _, f1 = _run(api, SHIFT, variant=2)
+    assert f1["mass"] == e1["mass"] and f1["phase_mass"] == e1["phase_mass"] and not f1["has_nan"]
+    for k in b:
+        assert np.array_equal(b[k], c[k]), ("in place", k)
 
 
 @pytest.mark.parametrize("variant,omega,omega_bulk", [("gs", 1.2, 0.8), ("hermite", 0.9, 0.1)])
